@@ -1,0 +1,324 @@
+// cat_math.cuh -- scalar device math shared by every kernel of libcatenary_b200 (sm_100a).
+//
+// CatMath<double>: IEEE fp64 (1e-9 parity mode).  CatMath<float>: fp32 fast mode (1e-4) on the
+// FFMA pipe + MUFU (sin.approx / ex2.approx / lg2.approx / rcp / rsqrt).
+// Reference formulas are cited per function (paths relative to the reference checkout).
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+template <typename T> struct CatMath;
+
+template <> struct CatMath<double> {
+  typedef double real;
+  static __device__ __forceinline__ double sin_(double x) { return sin(x); }
+  static __device__ __forceinline__ double cos_(double x) { return cos(x); }
+  static __device__ __forceinline__ void sincos_(double x, double* s, double* c) { sincos(x, s, c); }
+  static __device__ __forceinline__ double tanh_(double x) { return tanh(x); }
+  static __device__ __forceinline__ double exp_(double x) { return exp(x); }
+  static __device__ __forceinline__ double log_(double x) { return log(x); }
+  static __device__ __forceinline__ double sqrt_(double x) { return sqrt(x); }
+  static __device__ __forceinline__ double abs_(double x) { return fabs(x); }
+  static __device__ __forceinline__ double rcp_(double x) { return 1.0 / x; }
+  static __device__ __forceinline__ double div_(double a, double b) { return a / b; }
+  static __device__ __forceinline__ double min_(double a, double b) { return fmin(a, b); }
+  static __device__ __forceinline__ double max_(double a, double b) { return fmax(a, b); }
+  static __device__ __forceinline__ double fma_(double a, double b, double c) { return fma(a, b, c); }
+  template <int N> static __device__ __forceinline__ double ipow(double x) {
+    double r = x;
+#pragma unroll
+    for (int i = 1; i < N; ++i) r *= x;
+    return r;
+  }
+  // |du| <= step_tol * min(u,1) ends the Halley iteration: the step AFTER that one is cubic in it
+  static __device__ __forceinline__ double step_tol() { return 1e-5; }
+  static __device__ __forceinline__ double nan_() { return __longlong_as_double(0x7ff8000000000000LL); }
+  static __device__ __forceinline__ double inf_() { return __longlong_as_double(0x7ff0000000000000LL); }
+};
+
+template <> struct CatMath<float> {
+  typedef float real;
+  static __device__ __forceinline__ float sin_(float x) { return __sinf(x); }
+  static __device__ __forceinline__ float cos_(float x) { return __cosf(x); }
+  static __device__ __forceinline__ void sincos_(float x, float* s, float* c) { __sincosf(x, s, c); }
+  static __device__ __forceinline__ float tanh_(float x) {
+    float r;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+  }
+  static __device__ __forceinline__ float exp_(float x) { return __expf(x); }
+  static __device__ __forceinline__ float log_(float x) { return __logf(x); }
+  static __device__ __forceinline__ float sqrt_(float x) { return __fsqrt_rn(x); }
+  static __device__ __forceinline__ float abs_(float x) { return fabsf(x); }
+  static __device__ __forceinline__ float rcp_(float x) { return __frcp_rn(x); }
+  static __device__ __forceinline__ float div_(float a, float b) { return __fdividef(a, b); }
+  static __device__ __forceinline__ float min_(float a, float b) { return fminf(a, b); }
+  static __device__ __forceinline__ float max_(float a, float b) { return fmaxf(a, b); }
+  static __device__ __forceinline__ float fma_(float a, float b, float c) { return fmaf(a, b, c); }
+  template <int N> static __device__ __forceinline__ float ipow(float x) {
+    float r = x;
+#pragma unroll
+    for (int i = 1; i < N; ++i) r *= x;
+    return r;
+  }
+  static __device__ __forceinline__ float step_tol() { return 2e-3f; }
+  static __device__ __forceinline__ float nan_() { return __int_as_float(0x7fc00000); }
+  static __device__ __forceinline__ float inf_() { return __int_as_float(0x7f800000); }
+};
+
+// ------------------------------------------------------------------------------------------
+// Catenary parameter.  Reference: main_fun.py:423  f(C) = C^2 (L^2 - dH^2) - 4 sinh^2(l C / 2).
+// With u = C l / 2 and r = sqrt(L^2 - dH^2) / l the root satisfies sinh(u)/u = r.  We solve
+//   g(u) = (sinh(u) - u) - e u = 0,   e = r - 1 > 0
+// by Halley's method (g' = cosh(u) - 1 - e, g'' = sinh(u); one exp per iteration) and return
+// sinh(u), cosh(u) at the root so the lowest point needs no further transcendental.
+// ------------------------------------------------------------------------------------------
+template <typename T> struct CatRoot {
+  T u, sh, ch;   // u = C l / 2, sinh(u), cosh(u)
+};
+
+// sinh(u)-u, cosh(u)-1, sinh(u) for u > 0.  Series below 1 (no cancellation), exp above.
+template <typename T, typename M>
+__device__ __forceinline__ void cat_hyp(T u, T& sm, T& cm, T& sh) {
+  if (u < T(1)) {
+    const T w = u * u;
+    // sinh(u) - u = u w / 6 * (1 + w/20 (1 + w/42 (1 + w/72 (1 + w/110 (1 + w/156 (1 + w/210 (1 + w/272)))))))
+    T p = M::fma_(w, T(1.0 / 272.0), T(1));
+    p = M::fma_(w * T(1.0 / 210.0), p, T(1));
+    p = M::fma_(w * T(1.0 / 156.0), p, T(1));
+    p = M::fma_(w * T(1.0 / 110.0), p, T(1));
+    p = M::fma_(w * T(1.0 / 72.0), p, T(1));
+    p = M::fma_(w * T(1.0 / 42.0), p, T(1));
+    p = M::fma_(w * T(1.0 / 20.0), p, T(1));
+    sm = u * w * T(1.0 / 6.0) * p;
+    // cosh(u) - 1 = w / 2 * (1 + w/12 (1 + w/30 (1 + w/56 (1 + w/90 (1 + w/132 (1 + w/182 (1 + w/240)))))))
+    T q = M::fma_(w, T(1.0 / 240.0), T(1));
+    q = M::fma_(w * T(1.0 / 182.0), q, T(1));
+    q = M::fma_(w * T(1.0 / 132.0), q, T(1));
+    q = M::fma_(w * T(1.0 / 90.0), q, T(1));
+    q = M::fma_(w * T(1.0 / 56.0), q, T(1));
+    q = M::fma_(w * T(1.0 / 30.0), q, T(1));
+    q = M::fma_(w * T(1.0 / 12.0), q, T(1));
+    cm = w * T(0.5) * q;
+    sh = sm + u;
+  } else {
+    const T E = M::exp_(u);
+    const T Ei = M::rcp_(E);
+    sh = T(0.5) * (E - Ei);
+    sm = sh - u;
+    cm = T(0.5) * (E + Ei) - T(1);
+  }
+}
+
+// cold-start guess, max relative error 6.4% over e in [1e-13, 1e13]
+template <typename T, typename M>
+__device__ __forceinline__ T cat_u_guess(T e) {
+  if (e < T(2)) return M::sqrt_(M::div_(T(6) * e, M::fma_(T(0.3), e, T(1))));
+  const T lr = M::log_(T(2) * (T(1) + e));
+  return lr + M::log_(lr + M::log_(M::max_(lr, T(1))));
+}
+
+// e = r - 1 > 0 required.  u0 > 0: warm start (previous step's root), else cold start.
+template <typename T, typename M>
+__device__ __forceinline__ CatRoot<T> cat_solve_u(T e, T u0) {
+  T u = (u0 > T(0)) ? u0 : cat_u_guess<T, M>(e);
+  T sm, cm, sh, du;
+  int it = 0;
+  bool more;
+  do {
+    cat_hyp<T, M>(u, sm, cm, sh);
+    const T g = sm - e * u;
+    const T gp = cm - e;
+    const T den = T(2) * gp * gp - g * sh;
+    if (gp > T(0) && den > T(0)) {
+      du = M::div_(T(2) * g * gp, den);          // Halley
+    } else if (gp > T(0)) {
+      du = M::div_(g, gp);                       // Newton
+    } else {
+      du = -(T(0.5) * u + T(0.1));               // left of the minimum of g: move right
+    }
+    if (du >= u) du = T(0.5) * u;                // keep u > 0
+    u -= du;
+    more = M::abs_(du) > M::step_tol() * M::min_(u, T(1));
+  } while (more && ++it < 60);
+  // sinh/cosh at the updated u from the values at u+du (|du| <= 1e-5: 4th-order remainder)
+  const T ch = cm + T(1);
+  const T d2 = du * du * T(0.5);
+  const T d3 = du * T(1.0 / 3.0);
+  CatRoot<T> r;
+  r.u = u;
+  r.sh = sh - ch * du + d2 * (sh - ch * d3);
+  r.ch = ch - sh * du + d2 * (ch - sh * d3);
+  return r;
+}
+
+// Catenary terms of one span: horizontal l, vertical dH = zB - zA, cable L.
+// C is NaN outside the reference's domain: brentq on [c_lo, c_hi] (main_fun.py:425) raises when
+// f(c_lo), f(c_hi) have the same sign -> nan (main_fun.py:427-428).  f > 0 exactly on (0, root),
+// so the sign test is c_lo < root < c_hi with a root existing iff L^2 - dH^2 > l^2.
+// z_low_rel is the lowest point relative to the mean end height:
+//   z_low = (zA+zB)/2 - (L/2) coth(u) + l/(2u)   if |dH| <= L tanh(u)  (vertex inside the span,
+//   equivalent to 0 <= l/2 - atanh(dH/L)/C <= l), else min(zA, zB).
+template <typename T> struct CatSpan {
+  T C;        // NaN when outside the domain
+  T u;        // root (valid even if C is out of [c_lo,c_hi]); 0 when no root exists
+  T sh, ch;
+  bool inside;
+};
+
+template <typename T, typename M>
+__device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, T u_warm) {
+  CatSpan<T> s;
+  const T s2 = (L - dH) * (L + dH);
+  const T sq = M::sqrt_(M::max_(s2, T(0)));
+  const T e = M::div_(s2 - l * l, l * (sq + l));
+  if (!(s2 > T(0)) || !(e > T(0)) || !(l > T(0))) {
+    s.C = M::nan_();
+    s.u = T(0);
+    s.sh = T(0);
+    s.ch = T(1);
+    s.inside = false;
+    return s;
+  }
+  const CatRoot<T> r = cat_solve_u<T, M>(e, u_warm);
+  const T C = M::div_(T(2) * r.u, l);
+  s.u = r.u;
+  s.sh = r.sh;
+  s.ch = r.ch;
+  s.C = (C > c_lo && C < c_hi) ? C : M::nan_();
+  s.inside = M::abs_(dH) * r.ch <= L * r.sh;
+  return s;
+}
+
+// lowest z of the span (world frame), SURVEY.md 8a "per-step catenary terms"
+template <typename T, typename M>
+__device__ __forceinline__ T cat_z_low(const CatSpan<T>& s, T l, T L, T zA, T zB) {
+  const T zmin = M::min_(zA, zB);
+  if (!(s.C == s.C) || !s.inside) return zmin;
+  // (zA+zB)/2 + (l sh - L ch u) / (2 sh u)
+  return T(0.5) * (zA + zB) + M::div_(l * s.sh - L * s.ch * s.u, T(2) * s.sh * s.u);
+}
+
+// ------------------------------------------------------------------------------------------
+// Rodrigues rotation, main_fun.py:18-35 (axis re-normalised on every call, as the reference does)
+// ------------------------------------------------------------------------------------------
+template <typename T, typename M>
+__device__ __forceinline__ void cat_rodrigues(const T v[3], const T axis_in[3], T c, T s, T out[3]) {
+  const T n = M::sqrt_(axis_in[0] * axis_in[0] + axis_in[1] * axis_in[1] + axis_in[2] * axis_in[2]);
+  const T k[3] = {M::div_(axis_in[0], n), M::div_(axis_in[1], n), M::div_(axis_in[2], n)};
+  const T cx = k[1] * v[2] - k[2] * v[1];
+  const T cy = k[2] * v[0] - k[0] * v[2];
+  const T cz = k[0] * v[1] - k[1] * v[0];
+  const T dot = k[0] * v[0] + k[1] * v[1] + k[2] * v[2];
+  const T omc = T(1) - c;
+  out[0] = v[0] * c + cx * s + k[0] * dot * omc;
+  out[1] = v[1] * c + cy * s + k[1] * dot * omc;
+  out[2] = v[2] * c + cz * s + k[2] * dot * omc;
+}
+
+// theta rotation axis, main_fun.py:75-89 (fallbacks below 1e-9)
+template <typename T, typename M>
+__device__ __forceinline__ void cat_theta_axis(const T conn[3], T axis[3]) {
+  T px = conn[0], py = conn[1];
+  const T n = M::sqrt_(px * px + py * py);
+  if (n < T(1e-9)) {
+    px = T(1);
+    py = T(0);
+  } else {
+    px = M::div_(px, n);
+    py = M::div_(py, n);
+  }
+  // cross((px,py,0),(0,0,1)) = (py, -px, 0)
+  T ax = py, ay = -px;
+  const T n2 = M::sqrt_(ax * ax + ay * ay);
+  if (n2 < T(1e-9)) {
+    axis[0] = T(0);
+    axis[1] = T(1);
+    axis[2] = T(0);
+  } else {
+    axis[0] = M::div_(ax, n2);
+    axis[1] = M::div_(ay, n2);
+    axis[2] = T(0);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// 18-column features, simple.py:26-41, then StandardScaler (test_temp.py:49).
+// All 18 are written; the generated equations read a few and the compiler drops the rest.
+// ------------------------------------------------------------------------------------------
+template <typename T, typename M>
+__device__ __forceinline__ void cat_features18(const T P0[3], const T P1[3], const T V1[3], const T A1[3],
+                                               T th, T ga, T thp, T gap, T (&x)[18]) {
+  const T rx = P1[0] - P0[0], ry = P1[1] - P0[1], rz = P1[2] - P0[2];
+  const T nrm = M::sqrt_(rx * rx + ry * ry + rz * rz);
+  const T inv = M::rcp_(nrm + T(1e-8));
+  const T ux = rx * inv, uy = ry * inv, uz = rz * inv;
+  const T nv = M::sqrt_(V1[0] * V1[0] + V1[1] * V1[1] + V1[2] * V1[2]) + T(1e-8);
+  const T dot = V1[0] * ux + V1[1] * uy + V1[2] * uz;
+  x[0] = P1[0]; x[1] = P1[1]; x[2] = P1[2];
+  x[3] = V1[0]; x[4] = V1[1]; x[5] = V1[2];
+  x[6] = A1[0]; x[7] = A1[1]; x[8] = A1[2];
+  x[9] = ux; x[10] = uy; x[11] = uz;
+  x[12] = M::min_(M::max_(nrm, T(1e-5)), T(10));
+  x[13] = M::min_(M::max_(M::div_(dot, nv), T(-1)), T(1));
+  x[14] = th; x[15] = ga; x[16] = thp; x[17] = gap;
+}
+
+// ------------------------------------------------------------------------------------------
+// (cost, index) pairs with np.argmin ordering: NaN beats everything, then lower cost, then
+// lower index (first minimum; fully_augmented_catenary.py:21 semantics).
+// ------------------------------------------------------------------------------------------
+struct CatBest {
+  double cost;
+  long long idx;
+};
+
+__host__ __device__ __forceinline__ bool cat_better(double ca, long long ia, double cb, long long ib) {
+  const bool na = ca != ca, nb = cb != cb;
+  if (na != nb) return na;
+  if (na) return ia < ib;
+  if (ca < cb) return true;
+  if (ca > cb) return false;
+  return ia < ib;
+}
+
+// ------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al. 2011) -- counter-based RNG for on-device control sampling
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cat_philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                  uint32_t k0, uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ k0;
+    c1 = lo1;
+    c2 = hi0 ^ c3 ^ k1;
+    c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// three clipped normals scaled by sigma, keyed by (seed, problem, global k, h)
+template <typename T, typename M>
+__device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t problem, uint64_t k, uint32_t h,
+                                                   const T sigma[3], T clip, T out[3]) {
+  uint32_t r[4];
+  cat_philox4x32_10((uint32_t)k, (uint32_t)(k >> 32), h, problem, (uint32_t)seed, (uint32_t)(seed >> 32), r);
+  const T s = T(2.3283064365386963e-10);   // 2^-32
+  const T u0 = (T(r[0]) + T(0.5)) * s, u1 = (T(r[1]) + T(0.5)) * s;
+  const T u2 = (T(r[2]) + T(0.5)) * s, u3 = (T(r[3]) + T(0.5)) * s;
+  const T ra = M::sqrt_(T(-2) * M::log_(u0)), rb = M::sqrt_(T(-2) * M::log_(u2));
+  T sa, ca, cb, sb;
+  M::sincos_(T(6.283185307179586) * u1, &sa, &ca);
+  M::sincos_(T(6.283185307179586) * u3, &sb, &cb);
+  const T z0 = M::min_(M::max_(ra * ca, -clip), clip);
+  const T z1 = M::min_(M::max_(ra * sa, -clip), clip);
+  const T z2 = M::min_(M::max_(rb * cb, -clip), clip);
+  out[0] = z0 * sigma[0];
+  out[1] = z1 * sigma[1];
+  out[2] = z2 * sigma[2];
+}

@@ -1,0 +1,191 @@
+/* catenary_b200.h -- C ABI of libcatenary_b200.so (sm_100a).
+ *
+ * The reference (eather0056/Catenary-Model-Estimation-and-MPC-Control-for-ROV-Tethered-Systems)
+ * is pure Python and has no FFI: its boundary for this path is a set of module-level functions
+ * and one callable class.  Each entry point below names the reference interface it replaces
+ * (file:line relative to the reference checkout).  INTEGRATION.md shows the ctypes stub a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *  - return 0 (CAT_OK) on success, a negative CAT_E* code otherwise; never throws, never aborts.
+ *    cat_last_error(ctx) gives a message valid until the next call on that ctx.
+ *  - numerical failure is DATA, as in the reference: solve -> NaN (main_fun.py:427-428),
+ *    shape outside the solve domain -> valid[i] = 0 (callers substitute [A,B], main_fun.py:67-69).
+ *  - the caller owns every buffer.  Un-suffixed functions take HOST pointers and do the
+ *    host<->device copies on the ctx stream; *_dev functions take DEVICE pointers, enqueue on the
+ *    ctx stream and return without synchronising (cat_sync to wait).
+ *  - one ctx = one device + one stream; calls on one ctx are serialised by the caller.
+ *  - there is NO CPU fallback: without a CUDA device cat_init fails with CAT_ECUDA.
+ */
+#ifndef CATENARY_B200_H
+#define CATENARY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CAT_ABI_VERSION 1
+
+enum {
+  CAT_OK = 0,
+  CAT_EINVAL = -1,   /* bad argument (null pointer, negative size, bad enum) */
+  CAT_ECUDA = -2,    /* CUDA runtime error (message in cat_last_error) */
+  CAT_ENOMEM = -3,   /* device or pinned allocation failed */
+  CAT_ENODEV = -4    /* no usable CUDA device */
+};
+
+/* which outputs of transform_catenary (main_fun.py:111) to write, in this order */
+enum {
+  CAT_OUT_ORIGINAL = 1,
+  CAT_OUT_THETA_ROTATED = 2,
+  CAT_OUT_THETA_ALIGNED = 4,
+  CAT_OUT_FINAL = 8
+};
+
+/* flags of CatMpcParams */
+enum {
+  CAT_MPC_RNG_CONTROLS = 1   /* controls == NULL: sample on device (Philox4x32-10) */
+};
+
+/* Shared parameters of one sampling-MPC step (builder-defined composition).
+ * Plain-old-data, passed by pointer from the host, by value to the kernel. */
+typedef struct CatMpcParams {
+  int64_t K;            /* candidates per problem evaluated by THIS call (the local shard) */
+  int64_t k_offset;     /* global index of local candidate 0 (multi-GPU shards; RNG counter, best_idx) */
+  int32_t H;            /* horizon steps */
+  int32_t n_problems;   /* >= 1; fleet mode when > 1 */
+  int32_t flags;        /* CAT_MPC_* */
+  int32_t problem_offset; /* global index of local problem 0 (fleet shards; RNG counter) */
+  double dt;            /* s */
+  double L;             /* cable length, m (catenary.py:10) */
+  double w_trk, w_du, w_len, w_sag, w_ang;
+  double rho, z_floor, margin;
+  double c_lo, c_hi;    /* bracket of main_fun.py:425: C outside (c_lo,c_hi) is "nan" */
+  double nan_penalty;
+  uint64_t seed;        /* RNG key */
+  double sigma[3];      /* mm/s, per axis */
+  double clip;          /* in sigmas */
+} CatMpcParams;
+
+/* Per-problem initial state (fully_augmented_catenary.py:11-15 for the nominal pose). */
+typedef struct CatMpcProblem {
+  double P0[3];         /* anchor, m */
+  double P1[3];         /* ROV attach point, m */
+  double V1[3];         /* mm/s (simple.py:18 leaves velocities in data units) */
+  double A1[3];         /* mm/s^2 */
+  double theta, gamma, theta_prev, gamma_prev;   /* rad */
+} CatMpcProblem;
+
+/* ---- context ------------------------------------------------------------------------- */
+int cat_abi_version(void);
+int cat_init(int device, void** ctx);
+int cat_destroy(void* ctx);
+int cat_sync(void* ctx);
+const char* cat_last_error(void* ctx);
+/* number of kernels this ctx has launched so far (bench.py's gpu_launches) */
+int64_t cat_launch_count(void* ctx);
+/* the ctx stream (cudaStream_t) for callers that enqueue their own work around *_dev calls */
+void* cat_stream(void* ctx);
+/* run subsequent calls of this ctx on a caller-owned stream (NULL restores the ctx stream) */
+int cat_set_stream(void* ctx, void* cuda_stream);
+/* pinned host memory for the un-suffixed (host-pointer) entry points */
+int cat_host_alloc(void* ctx, size_t bytes, void** out);
+int cat_host_free(void* ctx, void* p);
+/* device event timing on the ctx stream (bench.py; torch.cuda.Event only sees torch's stream) */
+int cat_timer_start(void* ctx);
+int cat_timer_stop_ms(void* ctx, float* ms);   /* records, synchronises, returns elapsed */
+
+/* ---- catenary parameter: replaces main_fun.solve_catenary (main_fun.py:418-431) -------
+ * C_out[i] = root C in (1e-6, 10) of C^2 (L^2 - dH^2) - 4 sinh^2(l C / 2) = 0, NaN where the
+ * reference's brentq bracket has no sign change.  L_stride = 0 broadcasts L[0]. */
+int cat_solve_param_f64(void* ctx, int64_t n, const double* l, const double* dH,
+                        const double* L, int64_t L_stride, double* C_out);
+int cat_solve_param_f32(void* ctx, int64_t n, const float* l, const float* dH,
+                        const float* L, int64_t L_stride, float* C_out);
+int cat_solve_param_dev_f64(void* ctx, int64_t n, const double* l, const double* dH,
+                            const double* L, int64_t L_stride, double* C_out);
+int cat_solve_param_dev_f32(void* ctx, int64_t n, const float* l, const float* dH,
+                            const float* L, int64_t L_stride, float* C_out);
+
+/* ---- curve shapes: replaces Catenary.__call__ (pympc, call sites catenary.py:25,51) +
+ *      main_fun.transform_catenary (main_fun.py:38-111) + rodrigues_rotation (main_fun.py:18-35)
+ * A, B: AoS (n,3).  L: n values or one (L_stride 0).  theta, gamma: n values, or NULL (= 0).
+ * which: bitmask of CAT_OUT_*; out holds popcount(which) consecutive blocks, each AoS
+ * (n, n_pts, 3), in the enum's order.  C_out (n) and valid (n) may be NULL.
+ * valid bit 0: original span A->B is in the solve domain; bit 1: rotated span A->B' is.
+ * A block whose span is outside the domain holds the straight chord sampled at n_pts points. */
+int cat_shape_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L,
+                  int64_t L_stride, const double* theta, const double* gamma, int32_t n_pts,
+                  int32_t which, double* out, double* C_out, uint8_t* valid);
+int cat_shape_f32(void* ctx, int64_t n, const float* A, const float* B, const float* L,
+                  int64_t L_stride, const float* theta, const float* gamma, int32_t n_pts,
+                  int32_t which, float* out, float* C_out, uint8_t* valid);
+int cat_shape_dev_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L,
+                      int64_t L_stride, const double* theta, const double* gamma, int32_t n_pts,
+                      int32_t which, double* out, double* C_out, uint8_t* valid);
+int cat_shape_dev_f32(void* ctx, int64_t n, const float* A, const float* B, const float* L,
+                      int64_t L_stride, const float* theta, const float* gamma, int32_t n_pts,
+                      int32_t which, float* out, float* C_out, uint8_t* valid);
+/* lowest sample of each curve: replaces np.argmin(curve[:,2]) (fully_augmented_catenary.py:20-22).
+ * curves AoS (n, n_pts, 3) on the host; idx_out (n) first-minimum index, pt_out (n,3). */
+int cat_lowest_point_f64(void* ctx, int64_t n, int32_t n_pts, const double* curves,
+                         int64_t* idx_out, double* pt_out);
+
+/* ---- equations + open-loop integrators ------------------------------------------------
+ * eq_id indexes the generated hall-of-fame table (cat_equation_count/info); the shipped pair is
+ * cat_equation_shipped(0) = dtheta_dt, cat_equation_shipped(1) = dgamma_dt. */
+int cat_equation_count(void);
+int cat_equation_shipped(int which);
+int cat_equation_info(int eq_id, int* is_gamma, int* complexity, uint32_t* live_mask);
+/* replaces PySRRegressor.predict on (already scaled) features: X (n,18) row-major -> out (n) */
+int cat_predict_f64(void* ctx, int64_t n, const double* X, int eq_id, int apply_scaler, double* out);
+int cat_predict_f32(void* ctx, int64_t n, const float* X, int eq_id, int apply_scaler, float* out);
+/* replaces rk4_integration (simulate_rk4_theta_gamma.py:52-68): X (n_traj,T,18), time (T),
+ * y0 (n_traj) -> y_out (n_traj,T).  method 0 = RK4 (k2 == k3 as in the reference),
+ * 1 = explicit Euler (main_fun.integrate_theta_gamma, main_fun.py:735-764). */
+int cat_rk4_open_f64(void* ctx, int64_t n_traj, int64_t T, const double* X, const double* time,
+                     const double* y0, int eq_id, int method, double* y_out);
+int cat_rk4_open_f32(void* ctx, int64_t n_traj, int64_t T, const float* X, const float* time,
+                     const float* y0, int eq_id, int method, float* y_out);
+/* replaces extract_features (simple.py:15-41) on columns already in SI/data units:
+ * P0,P1 (T,3) m; V1 (T,3) mm/s; time, theta, gamma (T) -> X (T,18); scaled if apply_scaler. */
+int cat_features_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
+                     const double* time, const double* theta, const double* gamma,
+                     int apply_scaler, double* X_out);
+
+/* ---- fused closed-loop sampling-MPC step (new composition) --------
+ * problems: n_problems structs.  controls: [n_problems][H][3][K] (SoA over candidates, mm/s) or
+ * NULL with CAT_MPC_RNG_CONTROLS.  p_ref: [n_problems][H][3] (m).
+ * best_cost / best_idx: n_problems values (best_idx is GLOBAL: k_offset + local index, first
+ * minimum, NaN wins like np.argmin).  costs: [n_problems][K] or NULL. */
+int cat_mpc_step_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+                     const double* controls, const double* p_ref,
+                     double* best_cost, int64_t* best_idx, double* costs);
+int cat_mpc_step_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+                     const float* controls, const double* p_ref,
+                     double* best_cost, int64_t* best_idx, float* costs);
+/* device-pointer variants: problems, controls, p_ref, best_cost, best_idx, costs all on device */
+int cat_mpc_step_dev_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+                         const double* controls, const double* p_ref,
+                         double* best_cost, int64_t* best_idx, double* costs);
+int cat_mpc_step_dev_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+                         const float* controls, const double* p_ref,
+                         double* best_cost, int64_t* best_idx, float* costs);
+/* materialise the on-device RNG controls ([n_problems][H][3][K], device pointer) */
+int cat_sample_controls_dev_f64(void* ctx, const CatMpcParams* p, double* controls);
+/* deterministic reduce of per-shard winners gathered from G ranks (cost[g], idx[g]):
+ * lowest cost, ties -> lowest global index, NaN wins.  Host arrays. */
+int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx,
+                           double* best_cost, int64_t* best_idx);
+
+/* ---- peak microbenchmarks for the roofline denominators (bench.py) -------------------
+ * kind 0 = DFMA, 1 = FFMA, 2 = MUFU.EX2; returns operations per second (FMA = 1 op). */
+int cat_measure_peak(void* ctx, int kind, double* ops_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CATENARY_B200_H */
