@@ -1,0 +1,280 @@
+// cat_kernels_mpc.cuh -- fused closed-loop sampling-MPC step (sm_100a).
+//
+// One thread per candidate control sequence.  The whole horizon runs in registers:
+//   kinematics -> 18 features (simple.py:26-41) -> StandardScaler (test_temp.py:49) ->
+//   RK4 stages of the generated d(theta)/dt, d(gamma)/dt (simulate_rk4_theta_gamma.py:61-66) ->
+//   catenary parameter from (l, dH, L) (main_fun.py:423, warm-started from the previous step) ->
+//   lowest point -> per-step cost -> running sum.
+// Then a (cost, index) argmin: warp shuffle -> shared memory -> one slot per block -> the last
+// block of each problem (atomic ticket) folds the slots.  Ordering is np.argmin's
+// (fully_augmented_catenary.py:21): first minimum, NaN wins.
+//
+// The composition itself (closed loop, cost, argmin) has no reference counterpart; its definition
+// is oracle/catenary_oracle.py::mpc_rollout_costs and this file follows that function line by line.
+#pragma once
+#include "cat_math.cuh"
+#include "gen/dyn_eqs.cuh"
+#include "../../include/catenary_b200.h"
+
+#define CAT_MPC_BLOCK 128
+
+// Kernel-side parameters in the compute type.  Derived constants are formed on the host in
+// double exactly as the oracle forms them (dt/1000, dt/6, rho*L, z_floor+margin).
+template <typename T> struct CatMpcDev {
+  long long K, k_offset;
+  long long sk, sh, sa, sp;   // control strides in elements: candidate, step, axis, problem
+  int H, n_problems, flags, problem_offset;
+  int eq_theta, eq_gamma;
+  T dt, dt_mm, dt6, L, w_trk, w_du, w_len, w_sag, w_ang, rhoL, z_thr, c_lo, c_hi, pen, clip;
+  T sigma[3];
+  unsigned long long seed;
+};
+
+template <typename T, bool GENERIC>
+__device__ __forceinline__ void cat_eval_pair(const CatMpcDev<T>& q, const T (&x)[18], T& ft, T& fg) {
+  typedef CatMath<T> M;
+  if constexpr (GENERIC) {
+    ft = cat_eval_equation<T, M>(q.eq_theta, x);
+    fg = cat_eval_equation<T, M>(q.eq_gamma, x);
+  } else {
+    ft = cat_dtheta_dt<T, M>(x);
+    fg = cat_dgamma_dt<T, M>(x);
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ void cat_scale18(T (&x)[18]) {
+#pragma unroll
+  for (int j = 0; j < 18; ++j) x[j] = (x[j] - CatScaler<T>::mean(j)) * CatScaler<T>::inv_scale(j);
+}
+
+// block-wide (cost, idx) argmin; result valid in thread 0
+__device__ __forceinline__ CatBest cat_block_argmin(double cost, long long idx) {
+  __shared__ double s_cost[CAT_MPC_BLOCK / 32];
+  __shared__ long long s_idx[CAT_MPC_BLOCK / 32];
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const double oc = __shfl_xor_sync(0xffffffffu, cost, off);
+    const long long oi = __shfl_xor_sync(0xffffffffu, idx, off);
+    if (cat_better(oc, oi, cost, idx)) {
+      cost = oc;
+      idx = oi;
+    }
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) {
+    s_cost[w] = cost;
+    s_idx[w] = idx;
+  }
+  __syncthreads();
+  if (w == 0) {
+    const int nw = blockDim.x >> 5;
+    cost = (lane < nw) ? s_cost[lane] : __longlong_as_double(0x7ff0000000000000LL);
+    idx = (lane < nw) ? s_idx[lane] : 0x7fffffffffffffffLL;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const double oc = __shfl_xor_sync(0xffffffffu, cost, off);
+      const long long oi = __shfl_xor_sync(0xffffffffu, idx, off);
+      if (cat_better(oc, oi, cost, idx)) {
+        cost = oc;
+        idx = oi;
+      }
+    }
+  }
+  CatBest b;
+  b.cost = cost;
+  b.idx = idx;
+  return b;
+}
+
+template <typename T, bool GENERIC>
+__global__ void __launch_bounds__(CAT_MPC_BLOCK)
+k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, const T* __restrict__ controls,
+              const double* __restrict__ p_ref, T* __restrict__ costs, CatBest* __restrict__ block_best,
+              unsigned int* __restrict__ tickets, double* __restrict__ best_cost,
+              long long* __restrict__ best_idx) {
+  typedef CatMath<T> M;
+  const int prob = blockIdx.y;
+  const long long k = (long long)blockIdx.x * CAT_MPC_BLOCK + threadIdx.x;
+  const bool live = k < q.K;
+  const long long kk = live ? k : q.K - 1;   // idle lanes shadow the last candidate (no divergence, no OOB)
+
+  const CatMpcProblem* pb = problems + prob;
+  const T P0[3] = {T(pb->P0[0]), T(pb->P0[1]), T(pb->P0[2])};
+  T P[3] = {T(pb->P1[0]), T(pb->P1[1]), T(pb->P1[2])};
+  T V[3] = {T(pb->V1[0]), T(pb->V1[1]), T(pb->V1[2])};
+  T A[3] = {T(pb->A1[0]), T(pb->A1[1]), T(pb->A1[2])};
+  T th = T(pb->theta), ga = T(pb->gamma), thp = T(pb->theta_prev), gap = T(pb->gamma_prev);
+  T J = T(0);
+  T u_warm = T(0);
+
+  const bool rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
+  const T* uc = rng ? nullptr : controls + (long long)prob * q.sp + kk * q.sk;
+  const double* pr = p_ref + (long long)prob * q.H * 3;
+
+  for (int h = 0; h < q.H; ++h) {
+    T Vn[3];
+    if (rng) {
+      cat_sample_control<T, M>(q.seed, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
+                               (uint32_t)h, q.sigma, q.clip, Vn);
+    } else {
+      Vn[0] = uc[h * q.sh];
+      Vn[1] = uc[h * q.sh + q.sa];
+      Vn[2] = uc[h * q.sh + 2 * q.sa];
+    }
+    T Pn[3], An[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      Pn[a] = P[a] + Vn[a] * q.dt_mm;
+      An[a] = M::div_(Vn[a] - V[a], q.dt);
+    }
+    // ---- RK4 step of both angle ODEs (simulate_rk4_theta_gamma.py:61-66; k3 == k2) ----
+    T x0[18], x1[18], xm[18];
+    cat_features18<T, M>(P0, P, V, A, th, ga, thp, gap, x0);
+    cat_scale18<T>(x0);
+    T k1t, k1g, k2t, k2g, k4t, k4g;
+    cat_eval_pair<T, GENERIC>(q, x0, k1t, k1g);
+    cat_features18<T, M>(P0, Pn, Vn, An, th + q.dt * k1t, ga + q.dt * k1g, th, ga, x1);
+    cat_scale18<T>(x1);
+#pragma unroll
+    for (int j = 0; j < 18; ++j) xm[j] = (x0[j] + x1[j]) * T(0.5);
+    cat_eval_pair<T, GENERIC>(q, xm, k2t, k2g);
+    cat_eval_pair<T, GENERIC>(q, x1, k4t, k4g);
+    const T thn = th + q.dt6 * (k1t + T(2) * k2t + T(2) * k2t + k4t);
+    const T gan = ga + q.dt6 * (k1g + T(2) * k2g + T(2) * k2g + k4g);
+    // ---- catenary terms of the new pose (main_fun.py:423) ----
+    const T rx = Pn[0] - P0[0], ry = Pn[1] - P0[1], rz = Pn[2] - P0[2];
+    const T l2 = rx * rx + ry * ry;
+    const T l = M::sqrt_(l2);
+    const T d = M::sqrt_(l2 + rz * rz);
+    const CatSpan<T> sp = cat_span<T, M>(l, rz, q.L, q.c_lo, q.c_hi, u_warm);
+    u_warm = sp.u;
+    const T z_low = cat_z_low<T, M>(sp, l, q.L, P0[2], P0[2] + rz);
+    // ---- cost, association as in the oracle ----
+    const T ex = Pn[0] - T(pr[3 * h]), ey = Pn[1] - T(pr[3 * h + 1]), ez = Pn[2] - T(pr[3 * h + 2]);
+    const T dvx = Vn[0] - V[0], dvy = Vn[1] - V[1], dvz = Vn[2] - V[2];
+    const T over = M::max_(T(0), d - q.rhoL);
+    const T deep = M::max_(T(0), q.z_thr - z_low);
+    T c = q.w_trk * (ex * ex + ey * ey + ez * ez);
+    c = c + q.w_du * (dvx * dvx + dvy * dvy + dvz * dvz);
+    c = c + q.w_len * (over * over);
+    c = c + q.w_sag * (deep * deep);
+    c = c + q.w_ang * (thn * thn + gan * gan);
+    if (!(sp.C == sp.C)) c = c + q.pen;
+    J = J + c;
+    thp = th;
+    gap = ga;
+    th = thn;
+    ga = gan;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      P[a] = Pn[a];
+      V[a] = Vn[a];
+      A[a] = An[a];
+    }
+  }
+
+  if (live && costs) costs[(long long)prob * q.K + k] = J;
+
+  // ---- argmin over the candidates of this problem ----
+  const double jc = live ? (double)J : __longlong_as_double(0x7ff0000000000000LL);
+  const long long ji = live ? (q.k_offset + k) : 0x7fffffffffffffffLL;
+  const CatBest b = cat_block_argmin(jc, ji);
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) {
+    block_best[(long long)prob * gridDim.x + blockIdx.x] = b;
+    __threadfence();
+    const unsigned int t = atomicAdd(&tickets[prob], 1u);
+    s_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double bc = __longlong_as_double(0x7ff0000000000000LL);
+  long long bi = 0x7fffffffffffffffLL;
+  const volatile CatBest* slots = block_best + (long long)prob * gridDim.x;
+  for (unsigned int s = threadIdx.x; s < gridDim.x; s += CAT_MPC_BLOCK) {
+    const double oc = slots[s].cost;
+    const long long oi = slots[s].idx;
+    if (cat_better(oc, oi, bc, bi)) {
+      bc = oc;
+      bi = oi;
+    }
+  }
+  __syncthreads();   // s_cost/s_idx of cat_block_argmin are reused
+  const CatBest r = cat_block_argmin(bc, bi);
+  if (threadIdx.x == 0) {
+    best_cost[prob] = r.cost;
+    best_idx[prob] = r.idx;
+    tickets[prob] = 0u;   // ready for the next launch / graph replay
+  }
+}
+
+// materialise the on-device RNG controls: out[p][h][a][k] (SoA over candidates)
+template <typename T>
+__global__ void __launch_bounds__(256) k_sample_controls(const CatMpcDev<T> q, T* __restrict__ out) {
+  typedef CatMath<T> M;
+  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= q.K) return;
+  const int h = blockIdx.y, prob = blockIdx.z;
+  T v[3];
+  cat_sample_control<T, M>(q.seed, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + k), (uint32_t)h,
+                           q.sigma, q.clip, v);
+  T* o = out + (((long long)prob * q.H + h) * 3) * q.K + k;
+  o[0] = v[0];
+  o[q.K] = v[1];
+  o[2 * q.K] = v[2];
+}
+
+// ------------------------------------------------------------------------------------------
+// Peak microbenchmarks for the roofline denominators (MEASURED_PEAKS.json has HBM and bf16 only)
+// kind 0: DFMA, 1: FFMA, 2: MUFU.EX2.  8 independent chains per thread.
+// ------------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(256) k_peak(int iters, double* sink) {
+  if (KIND == 0) {
+    double a[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = 1.0 + 1e-9 * (threadIdx.x + j);
+    const double m = 1.0000001, c = 1e-12;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = fma(a[j], m, c);
+    }
+    double s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += a[j];
+    if (s == 12345.678) sink[0] = s;
+  } else if (KIND == 1) {
+    float a[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = 1.0f + 1e-6f * (threadIdx.x + j);
+    const float m = 1.0001f, c = 1e-6f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = fmaf(a[j], m, c);
+    }
+    float s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += a[j];
+    if (s == 12345.678f) sink[0] = s;
+  } else {
+    float a[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = 0.5f + 1e-3f * (threadIdx.x + j);
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a[j]));
+    }
+    float s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += a[j];
+    if (s == 12345.678f) sink[0] = s;
+  }
+}

@@ -1,0 +1,717 @@
+// catenary_b200.cu -- C ABI of libcatenary_b200.so (include/catenary_b200.h), sm_100a only.
+//
+// Host side of the boundary: context (device, stream, scratch), host<->device staging for the
+// host-pointer entry points, kernel launches.  No CPU fallback anywhere: every compute entry point
+// launches a CUDA kernel or fails with CAT_ECUDA.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/catenary_b200.h"
+#include "cat_kernels_dyn.cuh"
+#include "cat_kernels_geom.cuh"
+#include "cat_kernels_mpc.cuh"
+
+namespace {
+
+enum { SLOT_A = 0, SLOT_B, SLOT_C, SLOT_D, SLOT_E, SLOT_F, SLOT_G, SLOT_H, SLOT_BEST, SLOT_TICKET, N_SLOTS };
+
+struct CatCtx {
+  int device;
+  cudaStream_t own_stream;
+  cudaStream_t aux_stream;    // second lane of the chunked shape pipeline
+  cudaStream_t stream;        // stream in use (own_stream or a caller-owned one)
+  cudaEvent_t ev0, ev1, ev_aux;
+  std::string err;
+  int64_t launches;
+  void* slot[N_SLOTS];
+  size_t cap[N_SLOTS];
+  int sm_count;
+};
+
+int fail(CatCtx* c, int code, const char* what, cudaError_t e = cudaSuccess) {
+  if (c) {
+    c->err = what;
+    if (e != cudaSuccess) {
+      c->err += ": ";
+      c->err += cudaGetErrorString(e);
+    }
+  }
+  return code;
+}
+
+#define CU(call)                                              \
+  do {                                                        \
+    cudaError_t e__ = (call);                                 \
+    if (e__ != cudaSuccess) return fail(c, CAT_ECUDA, #call, e__); \
+  } while (0)
+
+#define NEED(cond)                                            \
+  do {                                                        \
+    if (!(cond)) return fail(c, CAT_EINVAL, "invalid argument: " #cond); \
+  } while (0)
+
+int bind(CatCtx* c) {
+  CU(cudaSetDevice(c->device));
+  return CAT_OK;
+}
+
+// grow-only device scratch; zero-filled when (re)allocated if zero == true
+int scratch(CatCtx* c, int s, size_t bytes, void** out, bool zero = false) {
+  if (bytes == 0) bytes = 16;
+  if (c->cap[s] < bytes) {
+    if (c->slot[s]) {
+      CU(cudaStreamSynchronize(c->stream));
+      CU(cudaFree(c->slot[s]));
+      c->slot[s] = nullptr;
+      c->cap[s] = 0;
+    }
+    size_t want = bytes + (bytes >> 2);
+    cudaError_t e = cudaMalloc(&c->slot[s], want);
+    if (e != cudaSuccess) {
+      want = bytes;
+      e = cudaMalloc(&c->slot[s], want);
+    }
+    if (e != cudaSuccess) {
+      c->slot[s] = nullptr;
+      return fail(c, CAT_ENOMEM, "cudaMalloc", e);
+    }
+    c->cap[s] = want;
+    if (zero) CU(cudaMemsetAsync(c->slot[s], 0, want, c->stream));
+  }
+  *out = c->slot[s];
+  return CAT_OK;
+}
+
+#define SCRATCH(slot_, bytes_, ptr_)                                   \
+  do {                                                                 \
+    void* p__ = nullptr;                                               \
+    int rc__ = scratch(c, slot_, (size_t)(bytes_), &p__);              \
+    if (rc__ != CAT_OK) return rc__;                                   \
+    ptr_ = reinterpret_cast<decltype(ptr_)>(p__);                      \
+  } while (0)
+
+#define LAUNCHED()                                                     \
+  do {                                                                 \
+    ++c->launches;                                                     \
+    cudaError_t e__ = cudaGetLastError();                              \
+    if (e__ != cudaSuccess) return fail(c, CAT_ECUDA, "kernel launch", e__); \
+  } while (0)
+
+inline unsigned int nblk(long long n, int b) { return (unsigned int)((n + b - 1) / b); }
+
+const double kCLo = 1e-6, kCHi = 10.0;   // bracket of main_fun.py:425
+
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+int solve_param_dev(CatCtx* c, int64_t n, const T* l, const T* dH, const T* L, int64_t L_stride, T* C_out) {
+  if (n == 0) return CAT_OK;
+  k_solve_param<T><<<nblk(n, 256), 256, 0, c->stream>>>(n, l, dH, L, L_stride, T(kCLo), T(kCHi), C_out);
+  LAUNCHED();
+  return CAT_OK;
+}
+
+template <typename T>
+int solve_param_host(CatCtx* c, int64_t n, const T* l, const T* dH, const T* L, int64_t L_stride, T* C_out) {
+  NEED(n >= 0 && (n == 0 || (l && dH && L && C_out)) && (L_stride == 0 || L_stride == 1));
+  if (n == 0) return CAT_OK;
+  int rc = bind(c);
+  if (rc) return rc;
+  T *dl, *dh, *dL, *dC;
+  const size_t nb = (size_t)n * sizeof(T);
+  SCRATCH(SLOT_A, nb, dl);
+  SCRATCH(SLOT_B, nb, dh);
+  SCRATCH(SLOT_C, L_stride ? nb : sizeof(T), dL);
+  SCRATCH(SLOT_D, nb, dC);
+  CU(cudaMemcpyAsync(dl, l, nb, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dh, dH, nb, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dL, L, L_stride ? nb : sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  rc = solve_param_dev<T>(c, n, dl, dh, dL, L_stride, dC);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(C_out, dC, nb, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+int shape_dev_on(CatCtx* c, cudaStream_t st, int64_t n, const T* A, const T* B, const T* L, int64_t L_stride,
+                 const T* theta, const T* gamma, int32_t n_pts, int32_t which, T* out, T* C_out, uint8_t* valid) {
+  if (n == 0) return CAT_OK;
+  k_shape<T><<<nblk(n, CAT_SHAPE_TILE), CAT_SHAPE_TILE, 0, st>>>(n, A, B, L, L_stride, theta, gamma, n_pts, which,
+                                                                 T(kCLo), T(kCHi), out, C_out, valid);
+  LAUNCHED();
+  return CAT_OK;
+}
+
+inline int popcount4(int w) { return (w & 1) + ((w >> 1) & 1) + ((w >> 2) & 1) + ((w >> 3) & 1); }
+
+template <typename T>
+int shape_host(CatCtx* c, int64_t n, const T* A, const T* B, const T* L, int64_t L_stride, const T* theta,
+               const T* gamma, int32_t n_pts, int32_t which, T* out, T* C_out, uint8_t* valid) {
+  NEED(n >= 0 && n_pts >= 1 && which > 0 && which < 16 && (L_stride == 0 || L_stride == 1));
+  NEED(n == 0 || (A && B && L && out));
+  if (n == 0) return CAT_OK;
+  int rc = bind(c);
+  if (rc) return rc;
+  const int nout = popcount4(which);
+  // chunked two-lane pipeline: lane j owns its own scratch; H2D, kernel, D2H are in-order per lane and the
+  // two lanes overlap each other (copy engine of one with the SMs of the other).
+  const int64_t chunk = 65536;
+  const size_t blk_elems = (size_t)chunk * n_pts * 3;
+  struct Lane {
+    T *A, *B, *L, *th, *ga, *out, *C;
+    uint8_t* v;
+  } lane[2];
+  const int slots[2][4] = {{SLOT_A, SLOT_B, SLOT_C, SLOT_D}, {SLOT_E, SLOT_F, SLOT_G, SLOT_H}};
+  for (int j = 0; j < 2; ++j) {
+    // one input arena per lane: A(3) B(3) L(1) th(1) ga(1) C(1) = 10 values per config, + valid bytes
+    T* in;
+    SCRATCH(slots[j][0], (size_t)chunk * 10 * sizeof(T), in);
+    lane[j].A = in;
+    lane[j].B = in + 3 * chunk;
+    lane[j].L = in + 6 * chunk;
+    lane[j].th = in + 7 * chunk;
+    lane[j].ga = in + 8 * chunk;
+    lane[j].C = in + 9 * chunk;
+    SCRATCH(slots[j][1], (size_t)chunk, lane[j].v);
+    const int64_t need = (n < chunk) ? n : chunk;
+    SCRATCH(slots[j][2], (size_t)need * n_pts * 3 * sizeof(T) * nout, lane[j].out);
+    if (n <= chunk) break;
+  }
+  (void)blk_elems;
+  cudaStream_t st[2] = {c->stream, c->aux_stream};
+  CU(cudaEventRecord(c->ev_aux, c->stream));
+  CU(cudaStreamWaitEvent(c->aux_stream, c->ev_aux, 0));
+  int ci = 0;
+  for (int64_t base = 0; base < n; base += chunk, ++ci) {
+    const int j = ci & 1;
+    const int64_t m = (n - base < chunk) ? (n - base) : chunk;
+    Lane& ln = lane[j];
+    CU(cudaMemcpyAsync(ln.A, A + 3 * base, (size_t)m * 3 * sizeof(T), cudaMemcpyHostToDevice, st[j]));
+    CU(cudaMemcpyAsync(ln.B, B + 3 * base, (size_t)m * 3 * sizeof(T), cudaMemcpyHostToDevice, st[j]));
+    CU(cudaMemcpyAsync(ln.L, L + (L_stride ? base : 0), (L_stride ? (size_t)m : 1) * sizeof(T),
+                       cudaMemcpyHostToDevice, st[j]));
+    if (theta) CU(cudaMemcpyAsync(ln.th, theta + base, (size_t)m * sizeof(T), cudaMemcpyHostToDevice, st[j]));
+    if (gamma) CU(cudaMemcpyAsync(ln.ga, gamma + base, (size_t)m * sizeof(T), cudaMemcpyHostToDevice, st[j]));
+    rc = shape_dev_on<T>(c, st[j], m, ln.A, ln.B, ln.L, L_stride, theta ? ln.th : nullptr,
+                         gamma ? ln.ga : nullptr, n_pts, which, ln.out, ln.C, ln.v);
+    if (rc) return rc;
+    const size_t blk_dev = (size_t)m * n_pts * 3;          // elements per output block of this chunk
+    const size_t blk_host = (size_t)n * n_pts * 3;         // elements per output block of the caller
+    for (int o = 0; o < nout; ++o)
+      CU(cudaMemcpyAsync(out + o * blk_host + (size_t)base * n_pts * 3, ln.out + o * blk_dev,
+                         blk_dev * sizeof(T), cudaMemcpyDeviceToHost, st[j]));
+    if (C_out) CU(cudaMemcpyAsync(C_out + base, ln.C, (size_t)m * sizeof(T), cudaMemcpyDeviceToHost, st[j]));
+    if (valid) CU(cudaMemcpyAsync(valid + base, ln.v, (size_t)m, cudaMemcpyDeviceToHost, st[j]));
+  }
+  CU(cudaStreamSynchronize(c->aux_stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+int predict_host(CatCtx* c, int64_t n, const T* X, int eq_id, int apply_scaler, T* out) {
+  NEED(n >= 0 && eq_id >= 0 && eq_id < CAT_N_EQUATIONS && (n == 0 || (X && out)));
+  if (n == 0) return CAT_OK;
+  int rc = bind(c);
+  if (rc) return rc;
+  T *dX, *dO;
+  SCRATCH(SLOT_A, (size_t)n * 18 * sizeof(T), dX);
+  SCRATCH(SLOT_B, (size_t)n * sizeof(T), dO);
+  CU(cudaMemcpyAsync(dX, X, (size_t)n * 18 * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  k_predict<T><<<nblk(n, 256), 256, 0, c->stream>>>(n, dX, eq_id, apply_scaler, dO);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dO, (size_t)n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+template <typename T>
+int rk4_open_host(CatCtx* c, int64_t n_traj, int64_t T_len, const T* X, const T* time, const T* y0, int eq_id,
+                  int method, T* y_out) {
+  NEED(n_traj >= 0 && T_len >= 0 && eq_id >= 0 && eq_id < CAT_N_EQUATIONS && (method == 0 || method == 1));
+  if (n_traj == 0 || T_len == 0) return CAT_OK;
+  NEED(X && time && y0 && y_out);
+  int rc = bind(c);
+  if (rc) return rc;
+  T *dX, *dt, *dy0, *dinc, *dy;
+  const size_t rows = (size_t)n_traj * T_len;
+  SCRATCH(SLOT_A, rows * 18 * sizeof(T), dX);
+  SCRATCH(SLOT_B, (size_t)T_len * sizeof(T), dt);
+  SCRATCH(SLOT_C, (size_t)n_traj * sizeof(T), dy0);
+  SCRATCH(SLOT_D, rows * sizeof(T), dinc);
+  SCRATCH(SLOT_E, rows * sizeof(T), dy);
+  CU(cudaMemcpyAsync(dX, X, rows * 18 * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dt, time, (size_t)T_len * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dy0, y0, (size_t)n_traj * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  if (T_len > 1) {
+    const long long work = (long long)n_traj * (T_len - 1);
+    k_rk4_increments<T><<<nblk(work, 256), 256, 0, c->stream>>>(n_traj, T_len, dX, dt, eq_id, method, dinc);
+    LAUNCHED();
+  }
+  k_rk4_accumulate<T><<<nblk(n_traj, 128), 128, 0, c->stream>>>(n_traj, T_len, dy0, dinc, dy);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(y_out, dy, rows * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
+  NEED(p != nullptr);
+  NEED(p->K >= 1 && p->H >= 1 && p->n_problems >= 1 && p->n_problems <= 65535);
+  NEED(p->eq_theta >= -1 && p->eq_theta < CAT_N_EQUATIONS && p->eq_gamma >= -1 && p->eq_gamma < CAT_N_EQUATIONS);
+  NEED(p->dt > 0 && p->L > 0);
+  q.K = p->K;
+  q.k_offset = p->k_offset;
+  q.H = p->H;
+  q.n_problems = p->n_problems;
+  q.flags = p->flags;
+  q.problem_offset = p->problem_offset;
+  q.eq_theta = p->eq_theta < 0 ? CAT_EQ_DTHETA_SHIPPED : p->eq_theta;
+  q.eq_gamma = p->eq_gamma < 0 ? CAT_EQ_DGAMMA_SHIPPED : p->eq_gamma;
+  if (p->flags & CAT_MPC_CONTROLS_AOS) {   // [problem][K][H][3]
+    q.sa = 1;
+    q.sh = 3;
+    q.sk = 3LL * p->H;
+    q.sp = 3LL * p->H * p->K;
+  } else {                                  // [problem][H][3][K]
+    q.sk = 1;
+    q.sa = p->K;
+    q.sh = 3LL * p->K;
+    q.sp = 3LL * p->H * p->K;
+  }
+  q.dt = T(p->dt);
+  q.dt_mm = T(p->dt / 1000.0);
+  q.dt6 = T(p->dt / 6);
+  q.L = T(p->L);
+  q.w_trk = T(p->w_trk);
+  q.w_du = T(p->w_du);
+  q.w_len = T(p->w_len);
+  q.w_sag = T(p->w_sag);
+  q.w_ang = T(p->w_ang);
+  q.rhoL = T(p->rho * p->L);
+  q.z_thr = T(p->z_floor + p->margin);
+  q.c_lo = T(p->c_lo);
+  q.c_hi = T(p->c_hi);
+  q.pen = T(p->nan_penalty);
+  q.clip = T(p->clip);
+  for (int a = 0; a < 3; ++a) q.sigma[a] = T(p->sigma[a]);
+  q.seed = p->seed;
+  return CAT_OK;
+}
+
+template <typename T>
+int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
+                 const double* p_ref, double* best_cost, long long* best_idx, T* costs) {
+  CatMpcDev<T> q;
+  int rc = mpc_fill<T>(c, p, q);
+  if (rc) return rc;
+  const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
+  NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
+  const dim3 grid(nblk(q.K, CAT_MPC_BLOCK), (unsigned)q.n_problems, 1);
+  CatBest* bb;
+  unsigned int* tk;
+  {
+    void* pp = nullptr;
+    rc = scratch(c, SLOT_BEST, (size_t)grid.x * grid.y * sizeof(CatBest), &pp);
+    if (rc) return rc;
+    bb = (CatBest*)pp;
+    rc = scratch(c, SLOT_TICKET, (size_t)65536 * sizeof(unsigned int), &pp, true);
+    if (rc) return rc;
+    tk = (unsigned int*)pp;
+  }
+  const bool shipped = (q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED);
+  if (shipped)
+    k_mpc_rollout<T, false><<<grid, CAT_MPC_BLOCK, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
+                                                                   best_cost, best_idx);
+  else
+    k_mpc_rollout<T, true><<<grid, CAT_MPC_BLOCK, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
+                                                                  best_cost, best_idx);
+  LAUNCHED();
+  return CAT_OK;
+}
+
+template <typename T>
+int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
+                  const double* p_ref, double* best_cost, int64_t* best_idx, T* costs) {
+  NEED(p != nullptr && p->K >= 1 && p->H >= 1 && p->n_problems >= 1);
+  const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
+  NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
+  int rc = bind(c);
+  if (rc) return rc;
+  const size_t np = (size_t)p->n_problems;
+  const size_t n_ctl = rng ? 0 : np * (size_t)p->H * 3 * (size_t)p->K;
+  CatMpcProblem* d_prob;
+  T* d_ctl = nullptr;
+  double* d_ref;
+  double* d_bc;
+  long long* d_bi;
+  T* d_costs = nullptr;
+  SCRATCH(SLOT_A, np * sizeof(CatMpcProblem), d_prob);
+  if (!rng) SCRATCH(SLOT_B, n_ctl * sizeof(T), d_ctl);
+  SCRATCH(SLOT_C, np * (size_t)p->H * 3 * sizeof(double), d_ref);
+  SCRATCH(SLOT_D, np * 16, d_bc);
+  d_bi = (long long*)(d_bc + np);
+  if (costs) SCRATCH(SLOT_E, np * (size_t)p->K * sizeof(T), d_costs);
+  CU(cudaMemcpyAsync(d_prob, problems, np * sizeof(CatMpcProblem), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_ref, p_ref, np * (size_t)p->H * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if (!rng) CU(cudaMemcpyAsync(d_ctl, controls, n_ctl * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  rc = mpc_step_dev<T>(c, p, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(best_cost, d_bc, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(best_idx, d_bi, np * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+  if (costs)
+    CU(cudaMemcpyAsync(costs, d_costs, np * (size_t)p->K * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+}  // namespace
+
+#define CTX()                          \
+  CatCtx* c = (CatCtx*)ctx;            \
+  if (!c) return CAT_EINVAL
+
+// =============================================================================================
+extern "C" {
+
+int cat_abi_version(void) { return CAT_ABI_VERSION; }
+
+int cat_init(int device, void** ctx) {
+  if (!ctx) return CAT_EINVAL;
+  *ctx = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    return CAT_ENODEV;
+  }
+  if (device < 0 || device >= n) return CAT_EINVAL;
+  CatCtx* c = new (std::nothrow) CatCtx();
+  if (!c) return CAT_ENOMEM;
+  c->device = device;
+  c->launches = 0;
+  std::memset(c->slot, 0, sizeof(c->slot));
+  std::memset(c->cap, 0, sizeof(c->cap));
+  bool ok = cudaSetDevice(device) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaEventCreate(&c->ev0) == cudaSuccess && cudaEventCreate(&c->ev1) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&c->ev_aux, cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device) == cudaSuccess;
+  if (!ok) {
+    cudaGetLastError();
+    delete c;
+    return CAT_ECUDA;
+  }
+  c->stream = c->own_stream;
+  *ctx = c;
+  return CAT_OK;
+}
+
+int cat_destroy(void* ctx) {
+  CTX();
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->own_stream);
+  cudaStreamSynchronize(c->aux_stream);
+  for (int s = 0; s < N_SLOTS; ++s)
+    if (c->slot[s]) cudaFree(c->slot[s]);
+  cudaEventDestroy(c->ev0);
+  cudaEventDestroy(c->ev1);
+  cudaEventDestroy(c->ev_aux);
+  cudaStreamDestroy(c->own_stream);
+  cudaStreamDestroy(c->aux_stream);
+  delete c;
+  return CAT_OK;
+}
+
+int cat_sync(void* ctx) {
+  CTX();
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+const char* cat_last_error(void* ctx) {
+  CatCtx* c = (CatCtx*)ctx;
+  return c ? c->err.c_str() : "null context";
+}
+
+int64_t cat_launch_count(void* ctx) {
+  CatCtx* c = (CatCtx*)ctx;
+  return c ? c->launches : -1;
+}
+
+void* cat_stream(void* ctx) {
+  CatCtx* c = (CatCtx*)ctx;
+  return c ? (void*)c->stream : nullptr;
+}
+
+int cat_set_stream(void* ctx, void* cuda_stream) {
+  CTX();
+  c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+  return CAT_OK;
+}
+
+int cat_host_alloc(void* ctx, size_t bytes, void** out) {
+  CTX();
+  NEED(out != nullptr);
+  int rc = bind(c);
+  if (rc) return rc;
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 16, cudaHostAllocDefault);
+  if (e != cudaSuccess) return fail(c, CAT_ENOMEM, "cudaHostAlloc", e);
+  return CAT_OK;
+}
+
+int cat_host_free(void* ctx, void* p) {
+  CTX();
+  if (p) CU(cudaFreeHost(p));
+  return CAT_OK;
+}
+
+int cat_timer_start(void* ctx) {
+  CTX();
+  CU(cudaEventRecord(c->ev0, c->stream));
+  return CAT_OK;
+}
+
+int cat_timer_stop_ms(void* ctx, float* ms) {
+  CTX();
+  NEED(ms != nullptr);
+  CU(cudaEventRecord(c->ev1, c->stream));
+  CU(cudaEventSynchronize(c->ev1));
+  CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+  return CAT_OK;
+}
+
+// ---- catenary parameter -----------------------------------------------------------------------
+int cat_solve_param_f64(void* ctx, int64_t n, const double* l, const double* dH, const double* L,
+                        int64_t L_stride, double* C_out) {
+  CTX();
+  return solve_param_host<double>(c, n, l, dH, L, L_stride, C_out);
+}
+int cat_solve_param_f32(void* ctx, int64_t n, const float* l, const float* dH, const float* L, int64_t L_stride,
+                        float* C_out) {
+  CTX();
+  return solve_param_host<float>(c, n, l, dH, L, L_stride, C_out);
+}
+int cat_solve_param_dev_f64(void* ctx, int64_t n, const double* l, const double* dH, const double* L,
+                            int64_t L_stride, double* C_out) {
+  CTX();
+  NEED(n >= 0 && (n == 0 || (l && dH && L && C_out)) && (L_stride == 0 || L_stride == 1));
+  int rc = bind(c);
+  if (rc) return rc;
+  return solve_param_dev<double>(c, n, l, dH, L, L_stride, C_out);
+}
+int cat_solve_param_dev_f32(void* ctx, int64_t n, const float* l, const float* dH, const float* L,
+                            int64_t L_stride, float* C_out) {
+  CTX();
+  NEED(n >= 0 && (n == 0 || (l && dH && L && C_out)) && (L_stride == 0 || L_stride == 1));
+  int rc = bind(c);
+  if (rc) return rc;
+  return solve_param_dev<float>(c, n, l, dH, L, L_stride, C_out);
+}
+
+// ---- shapes -------------------------------------------------------------------------------------
+int cat_shape_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L, int64_t L_stride,
+                  const double* theta, const double* gamma, int32_t n_pts, int32_t which, double* out,
+                  double* C_out, uint8_t* valid) {
+  CTX();
+  return shape_host<double>(c, n, A, B, L, L_stride, theta, gamma, n_pts, which, out, C_out, valid);
+}
+int cat_shape_f32(void* ctx, int64_t n, const float* A, const float* B, const float* L, int64_t L_stride,
+                  const float* theta, const float* gamma, int32_t n_pts, int32_t which, float* out, float* C_out,
+                  uint8_t* valid) {
+  CTX();
+  return shape_host<float>(c, n, A, B, L, L_stride, theta, gamma, n_pts, which, out, C_out, valid);
+}
+int cat_shape_dev_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L, int64_t L_stride,
+                      const double* theta, const double* gamma, int32_t n_pts, int32_t which, double* out,
+                      double* C_out, uint8_t* valid) {
+  CTX();
+  NEED(n >= 0 && n_pts >= 1 && which > 0 && which < 16 && (L_stride == 0 || L_stride == 1));
+  NEED(n == 0 || (A && B && L && out));
+  int rc = bind(c);
+  if (rc) return rc;
+  return shape_dev_on<double>(c, c->stream, n, A, B, L, L_stride, theta, gamma, n_pts, which, out, C_out, valid);
+}
+int cat_shape_dev_f32(void* ctx, int64_t n, const float* A, const float* B, const float* L, int64_t L_stride,
+                      const float* theta, const float* gamma, int32_t n_pts, int32_t which, float* out,
+                      float* C_out, uint8_t* valid) {
+  CTX();
+  NEED(n >= 0 && n_pts >= 1 && which > 0 && which < 16 && (L_stride == 0 || L_stride == 1));
+  NEED(n == 0 || (A && B && L && out));
+  int rc = bind(c);
+  if (rc) return rc;
+  return shape_dev_on<float>(c, c->stream, n, A, B, L, L_stride, theta, gamma, n_pts, which, out, C_out, valid);
+}
+
+int cat_lowest_point_f64(void* ctx, int64_t n, int32_t n_pts, const double* curves, int64_t* idx_out,
+                         double* pt_out) {
+  CTX();
+  NEED(n >= 0 && n_pts >= 1 && (n == 0 || (curves && idx_out && pt_out)));
+  if (n == 0) return CAT_OK;
+  int rc = bind(c);
+  if (rc) return rc;
+  double *dc, *dp;
+  long long* di;
+  const size_t nb = (size_t)n * n_pts * 3 * sizeof(double);
+  SCRATCH(SLOT_A, nb, dc);
+  SCRATCH(SLOT_B, (size_t)n * sizeof(long long), di);
+  SCRATCH(SLOT_C, (size_t)n * 3 * sizeof(double), dp);
+  CU(cudaMemcpyAsync(dc, curves, nb, cudaMemcpyHostToDevice, c->stream));
+  k_lowest_point<double><<<nblk(n * 32, 256), 256, 0, c->stream>>>(n, n_pts, dc, di, dp);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(idx_out, di, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(pt_out, dp, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+// ---- equations / integrators ----------------------------------------------------------------------
+int cat_equation_count(void) { return CAT_N_EQUATIONS; }
+int cat_equation_shipped(int which) {
+  return which == 0 ? CAT_EQ_DTHETA_SHIPPED : which == 1 ? CAT_EQ_DGAMMA_SHIPPED : -1;
+}
+int cat_equation_info(int eq_id, int* is_gamma, int* complexity, uint32_t* live_mask) {
+  if (eq_id < 0 || eq_id >= CAT_N_EQUATIONS) return CAT_EINVAL;
+  if (is_gamma) *is_gamma = CAT_EQ_TABLE[eq_id].is_gamma;
+  if (complexity) *complexity = CAT_EQ_TABLE[eq_id].complexity;
+  if (live_mask) *live_mask = CAT_EQ_TABLE[eq_id].live_mask;
+  return CAT_OK;
+}
+
+int cat_predict_f64(void* ctx, int64_t n, const double* X, int eq_id, int apply_scaler, double* out) {
+  CTX();
+  return predict_host<double>(c, n, X, eq_id, apply_scaler, out);
+}
+int cat_predict_f32(void* ctx, int64_t n, const float* X, int eq_id, int apply_scaler, float* out) {
+  CTX();
+  return predict_host<float>(c, n, X, eq_id, apply_scaler, out);
+}
+int cat_rk4_open_f64(void* ctx, int64_t n_traj, int64_t T, const double* X, const double* time, const double* y0,
+                     int eq_id, int method, double* y_out) {
+  CTX();
+  return rk4_open_host<double>(c, n_traj, T, X, time, y0, eq_id, method, y_out);
+}
+int cat_rk4_open_f32(void* ctx, int64_t n_traj, int64_t T, const float* X, const float* time, const float* y0,
+                     int eq_id, int method, float* y_out) {
+  CTX();
+  return rk4_open_host<float>(c, n_traj, T, X, time, y0, eq_id, method, y_out);
+}
+
+int cat_features_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1, const double* time,
+                     const double* theta, const double* gamma, int apply_scaler, double* X_out) {
+  CTX();
+  NEED(T >= 0 && (T == 0 || (P0 && P1 && V1 && time && theta && gamma && X_out)));
+  if (T == 0) return CAT_OK;
+  int rc = bind(c);
+  if (rc) return rc;
+  double* in;   // P0(3) P1(3) V1(3) time theta gamma = 12 per row
+  double* dX;
+  SCRATCH(SLOT_A, (size_t)T * 12 * sizeof(double), in);
+  SCRATCH(SLOT_B, (size_t)T * 18 * sizeof(double), dX);
+  double *dP0 = in, *dP1 = in + 3 * T, *dV1 = in + 6 * T, *dt = in + 9 * T, *dth = in + 10 * T, *dga = in + 11 * T;
+  CU(cudaMemcpyAsync(dP0, P0, (size_t)T * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dP1, P1, (size_t)T * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dV1, V1, (size_t)T * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dt, time, (size_t)T * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dth, theta, (size_t)T * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dga, gamma, (size_t)T * 8, cudaMemcpyHostToDevice, c->stream));
+  k_features<double><<<nblk(T, 256), 256, 0, c->stream>>>(T, dP0, dP1, dV1, dt, dth, dga, apply_scaler, dX);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(X_out, dX, (size_t)T * 18 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+// ---- sampling MPC -------------------------------------------------------------------------------------
+int cat_mpc_step_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems, const double* controls,
+                     const double* p_ref, double* best_cost, int64_t* best_idx, double* costs) {
+  CTX();
+  return mpc_step_host<double>(c, p, problems, controls, p_ref, best_cost, best_idx, costs);
+}
+int cat_mpc_step_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems, const float* controls,
+                     const double* p_ref, double* best_cost, int64_t* best_idx, float* costs) {
+  CTX();
+  return mpc_step_host<float>(c, p, problems, controls, p_ref, best_cost, best_idx, costs);
+}
+int cat_mpc_step_dev_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems, const double* controls,
+                         const double* p_ref, double* best_cost, int64_t* best_idx, double* costs) {
+  CTX();
+  int rc = bind(c);
+  if (rc) return rc;
+  return mpc_step_dev<double>(c, p, problems, controls, p_ref, best_cost, (long long*)best_idx, costs);
+}
+int cat_mpc_step_dev_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems, const float* controls,
+                         const double* p_ref, double* best_cost, int64_t* best_idx, float* costs) {
+  CTX();
+  int rc = bind(c);
+  if (rc) return rc;
+  return mpc_step_dev<float>(c, p, problems, controls, p_ref, best_cost, (long long*)best_idx, costs);
+}
+
+int cat_sample_controls_dev_f64(void* ctx, const CatMpcParams* p, double* controls) {
+  CTX();
+  CatMpcDev<double> q;
+  int rc = mpc_fill<double>(c, p, q);
+  if (rc) return rc;
+  NEED(controls != nullptr && p->H <= 65535);
+  rc = bind(c);
+  if (rc) return rc;
+  const dim3 grid(nblk(q.K, 256), (unsigned)q.H, (unsigned)q.n_problems);
+  k_sample_controls<double><<<grid, 256, 0, c->stream>>>(q, controls);
+  LAUNCHED();
+  return CAT_OK;
+}
+
+int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx, double* best_cost, int64_t* best_idx) {
+  if (n <= 0 || !cost || !idx || !best_cost || !best_idx) return CAT_EINVAL;
+  double bc = cost[0];
+  long long bi = idx[0];
+  for (int g = 1; g < n; ++g)
+    if (cat_better(cost[g], idx[g], bc, bi)) {
+      bc = cost[g];
+      bi = idx[g];
+    }
+  *best_cost = bc;
+  *best_idx = bi;
+  return CAT_OK;
+}
+
+// ---- roofline denominators --------------------------------------------------------------------------
+int cat_measure_peak(void* ctx, int kind, double* ops_per_s) {
+  CTX();
+  NEED(ops_per_s != nullptr && kind >= 0 && kind <= 2);
+  int rc = bind(c);
+  if (rc) return rc;
+  double* sink;
+  SCRATCH(SLOT_A, 64, sink);
+  const int blocks = c->sm_count * 8, threads = 256, iters = 4096;
+  float best_ms = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {
+    CU(cudaEventRecord(c->ev0, c->stream));
+    if (kind == 0)
+      k_peak<0><<<blocks, threads, 0, c->stream>>>(iters, sink);
+    else if (kind == 1)
+      k_peak<1><<<blocks, threads, 0, c->stream>>>(iters, sink);
+    else
+      k_peak<2><<<blocks, threads, 0, c->stream>>>(iters, sink);
+    LAUNCHED();
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaEventSynchronize(c->ev1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    if (rep > 0 && ms < best_ms) best_ms = ms;
+  }
+  const double ops = (double)blocks * threads * (double)iters * 64.0;
+  *ops_per_s = ops / (best_ms * 1e-3);
+  return CAT_OK;
+}
+
+}  // extern "C"

@@ -29,6 +29,12 @@ extern "C" {
 
 #define CAT_ABI_VERSION 1
 
+#if defined(CAT_BUILD_SHARED) && defined(__GNUC__)
+#define CAT_API __attribute__((visibility("default")))
+#else
+#define CAT_API
+#endif
+
 enum {
   CAT_OK = 0,
   CAT_EINVAL = -1,   /* bad argument (null pointer, negative size, bad enum) */
@@ -47,7 +53,8 @@ enum {
 
 /* flags of CatMpcParams */
 enum {
-  CAT_MPC_RNG_CONTROLS = 1   /* controls == NULL: sample on device (Philox4x32-10) */
+  CAT_MPC_RNG_CONTROLS = 1,  /* controls == NULL: sample on device (Philox4x32-10) */
+  CAT_MPC_CONTROLS_AOS = 2   /* controls are [n_problems][K][H][3] (the oracle's (K,H,3)) instead of SoA */
 };
 
 /* Shared parameters of one sampling-MPC step (builder-defined composition).
@@ -59,6 +66,8 @@ typedef struct CatMpcParams {
   int32_t n_problems;   /* >= 1; fleet mode when > 1 */
   int32_t flags;        /* CAT_MPC_* */
   int32_t problem_offset; /* global index of local problem 0 (fleet shards; RNG counter) */
+  int32_t eq_theta;     /* generated equation id of d(theta)/dt, -1 = shipped (eq_dtheta_dt.txt) */
+  int32_t eq_gamma;     /* generated equation id of d(gamma)/dt, -1 = shipped (eq_dgamma_dt.txt) */
   double dt;            /* s */
   double L;             /* cable length, m (catenary.py:10) */
   double w_trk, w_du, w_len, w_sag, w_ang;
@@ -80,34 +89,34 @@ typedef struct CatMpcProblem {
 } CatMpcProblem;
 
 /* ---- context ------------------------------------------------------------------------- */
-int cat_abi_version(void);
-int cat_init(int device, void** ctx);
-int cat_destroy(void* ctx);
-int cat_sync(void* ctx);
-const char* cat_last_error(void* ctx);
+CAT_API int cat_abi_version(void);
+CAT_API int cat_init(int device, void** ctx);
+CAT_API int cat_destroy(void* ctx);
+CAT_API int cat_sync(void* ctx);
+CAT_API const char* cat_last_error(void* ctx);
 /* number of kernels this ctx has launched so far (bench.py's gpu_launches) */
-int64_t cat_launch_count(void* ctx);
+CAT_API int64_t cat_launch_count(void* ctx);
 /* the ctx stream (cudaStream_t) for callers that enqueue their own work around *_dev calls */
-void* cat_stream(void* ctx);
+CAT_API void* cat_stream(void* ctx);
 /* run subsequent calls of this ctx on a caller-owned stream (NULL restores the ctx stream) */
-int cat_set_stream(void* ctx, void* cuda_stream);
+CAT_API int cat_set_stream(void* ctx, void* cuda_stream);
 /* pinned host memory for the un-suffixed (host-pointer) entry points */
-int cat_host_alloc(void* ctx, size_t bytes, void** out);
-int cat_host_free(void* ctx, void* p);
+CAT_API int cat_host_alloc(void* ctx, size_t bytes, void** out);
+CAT_API int cat_host_free(void* ctx, void* p);
 /* device event timing on the ctx stream (bench.py; torch.cuda.Event only sees torch's stream) */
-int cat_timer_start(void* ctx);
-int cat_timer_stop_ms(void* ctx, float* ms);   /* records, synchronises, returns elapsed */
+CAT_API int cat_timer_start(void* ctx);
+CAT_API int cat_timer_stop_ms(void* ctx, float* ms);   /* records, synchronises, returns elapsed */
 
 /* ---- catenary parameter: replaces main_fun.solve_catenary (main_fun.py:418-431) -------
  * C_out[i] = root C in (1e-6, 10) of C^2 (L^2 - dH^2) - 4 sinh^2(l C / 2) = 0, NaN where the
  * reference's brentq bracket has no sign change.  L_stride = 0 broadcasts L[0]. */
-int cat_solve_param_f64(void* ctx, int64_t n, const double* l, const double* dH,
+CAT_API int cat_solve_param_f64(void* ctx, int64_t n, const double* l, const double* dH,
                         const double* L, int64_t L_stride, double* C_out);
-int cat_solve_param_f32(void* ctx, int64_t n, const float* l, const float* dH,
+CAT_API int cat_solve_param_f32(void* ctx, int64_t n, const float* l, const float* dH,
                         const float* L, int64_t L_stride, float* C_out);
-int cat_solve_param_dev_f64(void* ctx, int64_t n, const double* l, const double* dH,
+CAT_API int cat_solve_param_dev_f64(void* ctx, int64_t n, const double* l, const double* dH,
                             const double* L, int64_t L_stride, double* C_out);
-int cat_solve_param_dev_f32(void* ctx, int64_t n, const float* l, const float* dH,
+CAT_API int cat_solve_param_dev_f32(void* ctx, int64_t n, const float* l, const float* dH,
                             const float* L, int64_t L_stride, float* C_out);
 
 /* ---- curve shapes: replaces Catenary.__call__ (pympc, call sites catenary.py:25,51) +
@@ -117,42 +126,42 @@ int cat_solve_param_dev_f32(void* ctx, int64_t n, const float* l, const float* d
  * (n, n_pts, 3), in the enum's order.  C_out (n) and valid (n) may be NULL.
  * valid bit 0: original span A->B is in the solve domain; bit 1: rotated span A->B' is.
  * A block whose span is outside the domain holds the straight chord sampled at n_pts points. */
-int cat_shape_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L,
+CAT_API int cat_shape_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L,
                   int64_t L_stride, const double* theta, const double* gamma, int32_t n_pts,
                   int32_t which, double* out, double* C_out, uint8_t* valid);
-int cat_shape_f32(void* ctx, int64_t n, const float* A, const float* B, const float* L,
+CAT_API int cat_shape_f32(void* ctx, int64_t n, const float* A, const float* B, const float* L,
                   int64_t L_stride, const float* theta, const float* gamma, int32_t n_pts,
                   int32_t which, float* out, float* C_out, uint8_t* valid);
-int cat_shape_dev_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L,
+CAT_API int cat_shape_dev_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L,
                       int64_t L_stride, const double* theta, const double* gamma, int32_t n_pts,
                       int32_t which, double* out, double* C_out, uint8_t* valid);
-int cat_shape_dev_f32(void* ctx, int64_t n, const float* A, const float* B, const float* L,
+CAT_API int cat_shape_dev_f32(void* ctx, int64_t n, const float* A, const float* B, const float* L,
                       int64_t L_stride, const float* theta, const float* gamma, int32_t n_pts,
                       int32_t which, float* out, float* C_out, uint8_t* valid);
 /* lowest sample of each curve: replaces np.argmin(curve[:,2]) (fully_augmented_catenary.py:20-22).
  * curves AoS (n, n_pts, 3) on the host; idx_out (n) first-minimum index, pt_out (n,3). */
-int cat_lowest_point_f64(void* ctx, int64_t n, int32_t n_pts, const double* curves,
+CAT_API int cat_lowest_point_f64(void* ctx, int64_t n, int32_t n_pts, const double* curves,
                          int64_t* idx_out, double* pt_out);
 
 /* ---- equations + open-loop integrators ------------------------------------------------
  * eq_id indexes the generated hall-of-fame table (cat_equation_count/info); the shipped pair is
  * cat_equation_shipped(0) = dtheta_dt, cat_equation_shipped(1) = dgamma_dt. */
-int cat_equation_count(void);
-int cat_equation_shipped(int which);
-int cat_equation_info(int eq_id, int* is_gamma, int* complexity, uint32_t* live_mask);
+CAT_API int cat_equation_count(void);
+CAT_API int cat_equation_shipped(int which);
+CAT_API int cat_equation_info(int eq_id, int* is_gamma, int* complexity, uint32_t* live_mask);
 /* replaces PySRRegressor.predict on (already scaled) features: X (n,18) row-major -> out (n) */
-int cat_predict_f64(void* ctx, int64_t n, const double* X, int eq_id, int apply_scaler, double* out);
-int cat_predict_f32(void* ctx, int64_t n, const float* X, int eq_id, int apply_scaler, float* out);
+CAT_API int cat_predict_f64(void* ctx, int64_t n, const double* X, int eq_id, int apply_scaler, double* out);
+CAT_API int cat_predict_f32(void* ctx, int64_t n, const float* X, int eq_id, int apply_scaler, float* out);
 /* replaces rk4_integration (simulate_rk4_theta_gamma.py:52-68): X (n_traj,T,18), time (T),
  * y0 (n_traj) -> y_out (n_traj,T).  method 0 = RK4 (k2 == k3 as in the reference),
  * 1 = explicit Euler (main_fun.integrate_theta_gamma, main_fun.py:735-764). */
-int cat_rk4_open_f64(void* ctx, int64_t n_traj, int64_t T, const double* X, const double* time,
+CAT_API int cat_rk4_open_f64(void* ctx, int64_t n_traj, int64_t T, const double* X, const double* time,
                      const double* y0, int eq_id, int method, double* y_out);
-int cat_rk4_open_f32(void* ctx, int64_t n_traj, int64_t T, const float* X, const float* time,
+CAT_API int cat_rk4_open_f32(void* ctx, int64_t n_traj, int64_t T, const float* X, const float* time,
                      const float* y0, int eq_id, int method, float* y_out);
 /* replaces extract_features (simple.py:15-41) on columns already in SI/data units:
  * P0,P1 (T,3) m; V1 (T,3) mm/s; time, theta, gamma (T) -> X (T,18); scaled if apply_scaler. */
-int cat_features_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
+CAT_API int cat_features_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
                      const double* time, const double* theta, const double* gamma,
                      int apply_scaler, double* X_out);
 
@@ -161,29 +170,29 @@ int cat_features_f64(void* ctx, int64_t T, const double* P0, const double* P1, c
  * NULL with CAT_MPC_RNG_CONTROLS.  p_ref: [n_problems][H][3] (m).
  * best_cost / best_idx: n_problems values (best_idx is GLOBAL: k_offset + local index, first
  * minimum, NaN wins like np.argmin).  costs: [n_problems][K] or NULL. */
-int cat_mpc_step_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+CAT_API int cat_mpc_step_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
                      const double* controls, const double* p_ref,
                      double* best_cost, int64_t* best_idx, double* costs);
-int cat_mpc_step_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+CAT_API int cat_mpc_step_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
                      const float* controls, const double* p_ref,
                      double* best_cost, int64_t* best_idx, float* costs);
 /* device-pointer variants: problems, controls, p_ref, best_cost, best_idx, costs all on device */
-int cat_mpc_step_dev_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+CAT_API int cat_mpc_step_dev_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
                          const double* controls, const double* p_ref,
                          double* best_cost, int64_t* best_idx, double* costs);
-int cat_mpc_step_dev_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+CAT_API int cat_mpc_step_dev_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
                          const float* controls, const double* p_ref,
                          double* best_cost, int64_t* best_idx, float* costs);
 /* materialise the on-device RNG controls ([n_problems][H][3][K], device pointer) */
-int cat_sample_controls_dev_f64(void* ctx, const CatMpcParams* p, double* controls);
+CAT_API int cat_sample_controls_dev_f64(void* ctx, const CatMpcParams* p, double* controls);
 /* deterministic reduce of per-shard winners gathered from G ranks (cost[g], idx[g]):
  * lowest cost, ties -> lowest global index, NaN wins.  Host arrays. */
-int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx,
+CAT_API int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx,
                            double* best_cost, int64_t* best_idx);
 
 /* ---- peak microbenchmarks for the roofline denominators (bench.py) -------------------
  * kind 0 = DFMA, 1 = FFMA, 2 = MUFU.EX2; returns operations per second (FMA = 1 op). */
-int cat_measure_peak(void* ctx, int kind, double* ops_per_s);
+CAT_API int cat_measure_peak(void* ctx, int kind, double* ops_per_s);
 
 #ifdef __cplusplus
 }
