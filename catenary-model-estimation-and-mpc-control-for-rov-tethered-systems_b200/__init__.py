@@ -1,0 +1,15 @@
+"""catenary-b200: the catenary tether shape solve + RK4 theta/gamma rollout + sampling-MPC step of
+eather0056/Catenary-Model-Estimation-and-MPC-Control-for-ROV-Tethered-Systems as hand-written CUDA (sm_100a)
+behind the reference's Python call surface.  NumPy in / NumPy out through a C ABI (include/catenary_b200.h).
+There is no CPU fallback: importing works anywhere, calling needs the built library and a CUDA device."""
+from ._lib import (CatenaryLibraryError, LIB_PATH, OUT_FINAL, OUT_ORIGINAL, OUT_THETA_ALIGNED,
+                   OUT_THETA_ROTATED, PROBLEM_DTYPE)
+from .context import Context, default_context
+from .dynamics import (EquationModel, equation_id, equation_table, extract_features, integrate_theta_gamma,
+                       predict, rk4_integration)
+from .geometry import (Catenary, catenary_shapes, lowest_point, rodrigues_rotation, solve_catenary, span_terms,
+                       transform_catenary)
+from .mpc import (circle_reference, default_mpc_params, make_params, make_problems, mpc_fleet_step,
+                  mpc_sample_step, reduce_winners)
+
+__all__ = [n for n in dir() if not n.startswith("_")]

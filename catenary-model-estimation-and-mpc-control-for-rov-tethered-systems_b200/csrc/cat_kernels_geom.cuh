@@ -251,3 +251,52 @@ __global__ void __launch_bounds__(256) k_lowest_point(long long n, int n_pts, co
     pt_out[3 * w + 2] = c[3 * bi + 2];
   }
 }
+
+// rodrigues_rotation (main_fun.py:18-35) batched: out[i] = R(axis[i*as], angle[i*gs]) v[i].
+// axis_stride / angle_stride 0 broadcast one axis / one angle over all vectors (the per-point loops
+// of transform_catenary, main_fun.py:96-99,106-109).  origin (3 values, may be NULL) is subtracted
+// before and added after the rotation (A + R (pt - A)).
+template <typename T>
+__global__ void __launch_bounds__(256) k_rodrigues(long long n, const T* __restrict__ v, const T* __restrict__ axis,
+                                                   long long axis_stride, const T* __restrict__ angle,
+                                                   long long angle_stride, const T* __restrict__ origin,
+                                                   T* __restrict__ out) {
+  typedef CatMath<T> M;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const T o[3] = {origin ? origin[0] : T(0), origin ? origin[1] : T(0), origin ? origin[2] : T(0)};
+  const T vv[3] = {v[3 * i] - o[0], v[3 * i + 1] - o[1], v[3 * i + 2] - o[2]};
+  const T* ax = axis + 3 * i * axis_stride;
+  const T k[3] = {ax[0], ax[1], ax[2]};
+  T s, c;
+  M::sincos_(angle[i * angle_stride], &s, &c);
+  T r[3];
+  cat_rodrigues<T, M>(vv, k, c, s, r);
+  out[3 * i] = o[0] + r[0];
+  out[3 * i + 1] = o[1] + r[1];
+  out[3 * i + 2] = o[2] + r[2];
+}
+
+// Span terms used by Catenary.__call__'s scalar outputs and by the tension feature:
+// C (main_fun.py:423), horizontal offset of the lowest point from A, lowest z relative to zA
+// (SURVEY.md 8a), tension w l / (2 sinh(C l / 2)) with the nan -> w l / 2 fallback (main_fun.py:302-305).
+template <typename T>
+__global__ void __launch_bounds__(256) k_span_terms(long long n, const T* __restrict__ l, const T* __restrict__ dH,
+                                                    const T* __restrict__ L, long long L_stride, T c_lo, T c_hi,
+                                                    T w, T* __restrict__ C_out, T* __restrict__ x_low,
+                                                    T* __restrict__ z_low, T* __restrict__ tension) {
+  typedef CatMath<T> M;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const T li = l[i], hi = dH[i], Li = L[i * L_stride];
+  const CatSpan<T> s = cat_span<T, M>(li, hi, Li, c_lo, c_hi, T(0));
+  if (C_out) C_out[i] = s.C;
+  const bool ok = s.C == s.C;
+  if (x_low) {
+    // l/2 - atanh(dH/L)/C = (l / 2u) (u - atanh(dH/L))
+    const T at = T(0.5) * M::log_(M::div_(Li + hi, Li - hi));
+    x_low[i] = ok ? M::div_(li * (s.u - at), T(2) * s.u) : M::nan_();
+  }
+  if (z_low) z_low[i] = cat_z_low<T, M>(s, li, Li, T(0), hi);
+  if (tension) tension[i] = ok ? M::div_(w * li, T(2) * s.sh) : w * li * T(0.5);
+}

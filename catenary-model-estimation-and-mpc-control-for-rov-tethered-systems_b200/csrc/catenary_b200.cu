@@ -517,6 +517,60 @@ int cat_solve_param_dev_f32(void* ctx, int64_t n, const float* l, const float* d
   return solve_param_dev<float>(c, n, l, dH, L, L_stride, C_out);
 }
 
+int cat_span_terms_f64(void* ctx, int64_t n, const double* l, const double* dH, const double* L, int64_t L_stride,
+                       double w, double* C_out, double* x_low, double* z_low, double* tension) {
+  CTX();
+  NEED(n >= 0 && (n == 0 || (l && dH && L)) && (L_stride == 0 || L_stride == 1));
+  if (n == 0) return CAT_OK;
+  int rc = bind(c);
+  if (rc) return rc;
+  const size_t nb = (size_t)n * sizeof(double);
+  double *in, *o;
+  SCRATCH(SLOT_A, 3 * nb, in);
+  SCRATCH(SLOT_B, 4 * nb, o);
+  CU(cudaMemcpyAsync(in, l, nb, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(in + n, dH, nb, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(in + 2 * n, L, L_stride ? nb : sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_span_terms<double><<<nblk(n, 256), 256, 0, c->stream>>>(n, in, in + n, in + 2 * n, L_stride, kCLo, kCHi, w,
+                                                           C_out ? o : nullptr, x_low ? o + n : nullptr,
+                                                           z_low ? o + 2 * n : nullptr,
+                                                           tension ? o + 3 * n : nullptr);
+  LAUNCHED();
+  if (C_out) CU(cudaMemcpyAsync(C_out, o, nb, cudaMemcpyDeviceToHost, c->stream));
+  if (x_low) CU(cudaMemcpyAsync(x_low, o + n, nb, cudaMemcpyDeviceToHost, c->stream));
+  if (z_low) CU(cudaMemcpyAsync(z_low, o + 2 * n, nb, cudaMemcpyDeviceToHost, c->stream));
+  if (tension) CU(cudaMemcpyAsync(tension, o + 3 * n, nb, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+int cat_rodrigues_f64(void* ctx, int64_t n, const double* v, const double* axis, int64_t axis_stride,
+                      const double* angle, int64_t angle_stride, const double* origin, double* out) {
+  CTX();
+  NEED(n >= 0 && (n == 0 || (v && axis && angle && out)));
+  NEED((axis_stride == 0 || axis_stride == 1) && (angle_stride == 0 || angle_stride == 1));
+  if (n == 0) return CAT_OK;
+  int rc = bind(c);
+  if (rc) return rc;
+  const size_t nb = (size_t)n * sizeof(double);
+  double *dv, *dax, *dan, *dor, *dout;
+  SCRATCH(SLOT_A, 3 * nb, dv);
+  SCRATCH(SLOT_B, axis_stride ? 3 * nb : 24, dax);
+  SCRATCH(SLOT_C, angle_stride ? nb : 8, dan);
+  SCRATCH(SLOT_D, 24, dor);
+  SCRATCH(SLOT_E, 3 * nb, dout);
+  CU(cudaMemcpyAsync(dv, v, 3 * nb, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dax, axis, axis_stride ? 3 * nb : 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dan, angle, angle_stride ? nb : 8, cudaMemcpyHostToDevice, c->stream));
+  if (origin) CU(cudaMemcpyAsync(dor, origin, 24, cudaMemcpyHostToDevice, c->stream));
+  k_rodrigues<double><<<nblk(n, 256), 256, 0, c->stream>>>(n, dv, dax, axis_stride, dan, angle_stride,
+                                                          origin ? dor : nullptr, dout);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dout, 3 * nb, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
 // ---- shapes -------------------------------------------------------------------------------------
 int cat_shape_f64(void* ctx, int64_t n, const double* A, const double* B, const double* L, int64_t L_stride,
                   const double* theta, const double* gamma, int32_t n_pts, int32_t which, double* out,

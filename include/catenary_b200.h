@@ -119,6 +119,19 @@ CAT_API int cat_solve_param_dev_f64(void* ctx, int64_t n, const double* l, const
 CAT_API int cat_solve_param_dev_f32(void* ctx, int64_t n, const float* l, const float* dH,
                             const float* L, int64_t L_stride, float* C_out);
 
+/* span terms in one pass: C as above; x_low = horizontal offset of the lowest point from A
+ * (l/2 - atanh(dH/L)/C, NaN where C is NaN); z_low = lowest z relative to zA (min(0,dH) when the vertex is
+ * outside the span or C is NaN); tension = w l / (2 sinh(C l / 2)), NaN C -> w l / 2 (main_fun.py:302-305,
+ * w = cable wet weight, test_cluster.py:23).  Any output pointer may be NULL. */
+CAT_API int cat_span_terms_f64(void* ctx, int64_t n, const double* l, const double* dH, const double* L,
+                               int64_t L_stride, double w, double* C_out, double* x_low, double* z_low,
+                               double* tension);
+/* replaces main_fun.rodrigues_rotation (main_fun.py:18-35), batched: out[i] = origin + R(axis, angle)(v[i] - origin).
+ * v, out (n,3); axis (n,3) or one axis (axis_stride 0); angle n values or one (angle_stride 0);
+ * origin 3 values or NULL. */
+CAT_API int cat_rodrigues_f64(void* ctx, int64_t n, const double* v, const double* axis, int64_t axis_stride,
+                              const double* angle, int64_t angle_stride, const double* origin, double* out);
+
 /* ---- curve shapes: replaces Catenary.__call__ (pympc, call sites catenary.py:25,51) +
  *      main_fun.transform_catenary (main_fun.py:38-111) + rodrigues_rotation (main_fun.py:18-35)
  * A, B: AoS (n,3).  L: n values or one (L_stride 0).  theta, gamma: n values, or NULL (= 0).
