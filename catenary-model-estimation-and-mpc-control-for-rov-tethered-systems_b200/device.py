@@ -1,0 +1,68 @@
+"""Device-resident sampling-MPC step: buffers live in HBM as torch tensors (torch is only the allocator and
+the stream/NCCL plumbing); each ``launch`` is ONE kernel through cat_mpc_step_dev_* on torch's current stream.
+Used by the receding-horizon loop, the multi-GPU shard exchange and bench.py's device-timed leg."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .context import Context
+from .mpc import make_params, make_problems
+
+
+class MpcDeviceStep:
+    def __init__(self, params, p_ref, K, *, controls=None, layout="H3K", sigma=None, seed=0, clip=3.0, k_offset=0,
+                 problems=None, problem_offset=0, keep_costs=False, dtype=np.float64, device=0, ctx=None):
+        import torch
+        self.torch = torch
+        self.dev = torch.device("cuda", device)
+        self.ctx = ctx or Context(device)
+        self.dtype = np.dtype(dtype)
+        tdt = torch.float64 if self.dtype == np.float64 else torch.float32
+        p_ref = np.ascontiguousarray(p_ref, np.float64)
+        if p_ref.ndim == 2:
+            p_ref = p_ref[None]
+        n, H = p_ref.shape[0], p_ref.shape[1]
+        probs = make_problems(params, n) if problems is None else np.ascontiguousarray(problems, _lib.PROBLEM_DTYPE)
+        flags = 0
+        if controls is None:
+            if sigma is None:
+                raise ValueError("controls=None needs sigma")
+            flags |= _lib.MPC_RNG_CONTROLS
+            self.controls = None
+        else:
+            if layout == "KH3":
+                flags |= _lib.MPC_CONTROLS_AOS
+            self.controls = torch.as_tensor(np.ascontiguousarray(controls, self.dtype)).to(self.dev)
+        self.params = make_params(params, K, H, n_problems=n, k_offset=k_offset, problem_offset=problem_offset,
+                                  flags=flags, seed=seed, sigma=(0, 0, 0) if sigma is None else sigma, clip=clip)
+        self.K, self.H, self.n = int(K), int(H), int(n)
+        self.problems = torch.from_numpy(probs.view(np.uint8).reshape(n, -1).copy()).to(self.dev)
+        self.p_ref = torch.from_numpy(p_ref).to(self.dev)
+        # winner = [cost bits (n) | idx (n)] in ONE int64 buffer, so a single 16-byte message per problem
+        # carries it across ranks (distributed.exchange_winner)
+        self.winner = torch.zeros(2 * n, dtype=torch.int64, device=self.dev)
+        self.best_cost = self.winner[:n].view(torch.float64)
+        self.best_idx = self.winner[n:]
+        self.costs = torch.empty((n, K), dtype=tdt, device=self.dev) if keep_costs else None
+        self._fn = self.ctx.lib.cat_mpc_step_dev_f64 if self.dtype == np.float64 else self.ctx.lib.cat_mpc_step_dev_f32
+
+    def set_controls(self, controls_dev):
+        """Swap in another device tensor of candidate controls (same layout and dtype)."""
+        self.controls = controls_dev
+
+    def launch(self):
+        """Enqueue the step on torch's current stream; returns immediately."""
+        torch = self.torch
+        self.ctx.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
+        self.ctx.check(self._fn(self.ctx.handle, C.byref(self.params), self.problems.data_ptr(),
+                                None if self.controls is None else self.controls.data_ptr(), self.p_ref.data_ptr(),
+                                self.best_cost.data_ptr(), self.best_idx.data_ptr(),
+                                None if self.costs is None else self.costs.data_ptr()))
+
+    def result(self):
+        """(best_idx (n,), best_cost (n,)) on the host (one small D2H + sync)."""
+        w = self.winner.cpu().numpy()
+        return w[self.n:].copy(), w[:self.n].view(np.float64).copy()

@@ -1,0 +1,77 @@
+"""Multi-GPU sharding of the sampling-MPC step: one process per GPU (torch.distributed), candidates split into
+contiguous shards, ONE (cost, index) exchange per step.
+
+NCCL has no MINLOC and an fp64 cost + int64 index do not pack into one 64-bit min, so every rank all-gathers
+the 16-byte winners and folds them in rank order with the lowest-global-index tie-break
+(cat_reduce_winners_f64) -- identical on every rank and identical to np.argmin over the concatenated costs.
+The fleet configuration (independent problems) shards problems and needs no communication.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .mpc import reduce_winners
+
+
+def shard_range(total, rank, world):
+    """Contiguous shard [lo, hi) of ``total`` items for ``rank`` of ``world`` (remainder to the low ranks)."""
+    base, rem = divmod(int(total), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def exchange_winner(winner, group=None):
+    """winner: int64 tensor [cost bits, global idx] of this rank (CPU tensor under gloo, CUDA under NCCL).
+    Returns (best_idx, best_cost) of the whole job, the same on every rank."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    gathered = torch.empty(world * 2, dtype=torch.int64, device=winner.device)
+    dist.all_gather_into_tensor(gathered, winner.contiguous(), group=group)
+    g = gathered.cpu().numpy().reshape(world, 2)
+    return reduce_winners(g[:, 0].copy().view(np.float64), g[:, 1].copy())
+
+
+def pack_winner(cost, idx):
+    """Host-side (cost, idx) -> int64[2] tensor (CPU); used by the gloo tests and by callers that already hold
+    the local winner on the host."""
+    import torch
+    a = np.empty(2, np.int64)
+    a[:1].view(np.float64)[0] = cost
+    a[1] = idx
+    return torch.from_numpy(a)
+
+
+class ShardedMpcStep:
+    """Config 4: K_total candidates of ONE problem split across the ranks of the default process group,
+    controls sampled on the device from (seed, global k, h) so no scatter is needed."""
+
+    def __init__(self, params, p_ref, K_total, sigma, *, seed=0, clip=3.0, dtype=np.float64, device=None,
+                 group=None):
+        import torch
+        import torch.distributed as dist
+        from .device import MpcDeviceStep
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        lo, hi = shard_range(K_total, self.rank, self.world)
+        self.lo, self.hi = lo, hi
+        device = torch.cuda.current_device() if device is None else device
+        self.step = MpcDeviceStep(params, p_ref, hi - lo, sigma=sigma, seed=seed, clip=clip, k_offset=lo,
+                                  dtype=dtype, device=device)
+
+    def launch(self):
+        self.step.launch()
+
+    def finish(self):
+        """Exchange the local winners; returns (best_idx, best_cost) of the whole job."""
+        return exchange_winner(self.step.winner, self.group)
+
+    def run(self):
+        self.launch()
+        return self.finish()
+
+
+def fleet_shard(n_problems, rank, world):
+    """Config 5: problems [lo, hi) of this rank; no cross-GPU communication."""
+    return shard_range(n_problems, rank, world)

@@ -1,0 +1,367 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle and the reference-generated golden vectors.
+Tolerances: fp64 1e-9 relative (north_star), fp32 fast mode 1e-4, argmin index exact in fp64."""
+import numpy as np
+import pytest
+
+from conftest import assert_close, golden
+from oracle import catenary_oracle as orc
+
+pytestmark = pytest.mark.gpu
+RTOL64 = 1e-9
+RTOL32 = 1e-4
+SIGMA = np.array(orc.load_model()["scaler_scale"][3:6])      # config 3: sigma of V1 (mm/s)
+
+
+# ---------------------------------------------------------------- geometry
+def test_solve_catenary_golden(cb):
+    g = golden("solve_catenary.npz")
+    assert_close(cb.solve_catenary(g["l"], g["dH"], 3.0), g["ref_C_L3"], 2e-11, 4e-12, "C vs reference brentq")
+    assert_close(cb.solve_catenary(g["l"], g["dH"], g["L"]), g["ref_C"], 2e-11, 4e-12, "C, L per element")
+    c = cb.solve_catenary(1.0, 0.0, 3.0)
+    assert c.shape == () and abs(float(c) - 5.67689276) < 1e-7            # scalar call, np.vectorize shape
+
+
+def test_solve_catenary_oracle_large_and_edges(cb):
+    rng = np.random.default_rng(0)
+    n = 200_000
+    l = rng.uniform(1e-3, 3.3, n)
+    dH = rng.uniform(-3.1, 3.1, n)
+    assert_close(cb.solve_catenary(l, dH, 3.0), orc.solve_catenary(l, dH, 3.0), RTOL64, 0, "C 200k")
+    # empty, zero span, taut, |dH| >= L
+    assert cb.solve_catenary(np.zeros(0), np.zeros(0), 3.0).shape == (0,)
+    edge = cb.solve_catenary(np.array([0.0, 3.0, 1.0, 1.0, 2.999999]), np.array([0.0, 0.0, 3.0, -3.5, 0.0]), 3.0)
+    assert np.isnan(edge[:4]).all() and np.isfinite(edge[4])
+    with np.errstate(all="ignore"):
+        assert_close(edge, orc.solve_catenary(np.array([0.0, 3.0, 1.0, 1.0, 2.999999]),
+                                              np.array([0.0, 0.0, 3.0, -3.5, 0.0]), 3.0), 1e-7, 0, "edges")
+
+
+def test_solve_catenary_fp32(cb):
+    rng = np.random.default_rng(1)
+    l = rng.uniform(0.5, 2.6, 50_000)
+    dH = rng.uniform(-1.0, 1.0, 50_000)
+    assert_close(cb.solve_catenary(l, dH, 3.0, dtype=np.float32), orc.solve_catenary(l, dH, 3.0), RTOL32, 0, "C f32")
+
+
+def test_solve_catenary_residual_property(cb):
+    """Size-independent property at config-2 scale: the returned root satisfies the reference's equation."""
+    rng = np.random.default_rng(2)
+    n = 1 << 20
+    l = rng.uniform(0.4, 2.9, n)
+    dH = rng.uniform(-1.5, 1.5, n)
+    C = cb.solve_catenary(l, dH, 3.0)
+    ok = ~np.isnan(C)
+    assert ok.mean() > 0.5
+    arc = 2 * np.sinh(0.5 * l[ok] * C[ok]) / C[ok]
+    assert np.abs(arc / np.sqrt(9.0 - dH[ok] ** 2) - 1).max() < 1e-12
+
+
+def test_rodrigues_golden(cb):
+    g = golden("rodrigues.npz")
+    assert_close(cb.rodrigues_rotation(g["v"], g["axis"], g["angle"]), g["ref_out"], 1e-12, 1e-14, "rodrigues batch")
+    one = cb.rodrigues_rotation(g["v"][3], g["axis"][3], g["angle"][3])
+    assert one.shape == (3,)
+    assert_close(one, g["ref_out"][3], 1e-12, 1e-14, "rodrigues single")
+
+
+def test_transform_catenary_golden(cb):
+    g = golden("transform_catenary.npz")
+    for i in range(g["A"].shape[0]):
+        res = cb.transform_catenary(g["A"][i], g["B"][i], cb.Catenary(float(g["L"][i])), g["theta"][i], g["gamma"][i])
+        for j in range(4):
+            n = g["n_pts"][i][0 if j == 0 else 1]
+            assert res[j].shape == (n, 3), (i, j)
+            assert_close(res[j], g["ref_curves"][i, j, :n], RTOL64, 1e-12, f"scenario {i} output {j}")
+
+
+def test_transform_catenary_foreign_callable(cb):
+    """Any catenary_fn works (main_fun.py:64-69): curves from the callable, rotations on the device."""
+    g = golden("transform_catenary.npz")
+    for i in (1, 5, 6):
+        res = cb.transform_catenary(g["A"][i], g["B"][i], orc.Catenary(float(g["L"][i])), g["theta"][i], g["gamma"][i])
+        for j in range(4):
+            n = g["n_pts"][i][0 if j == 0 else 1]
+            assert_close(res[j], g["ref_curves"][i, j, :n], RTOL64, 1e-12, f"foreign fn {i}/{j}")
+
+
+def test_catenary_class_surface(cb):
+    a, b = np.zeros(3), np.array([1.0, 1.0, 0.0])          # catenary.py:13-14
+    out = cb.Catenary(length=3.0, reference_frame="ENU")(a, b)
+    ref = orc.Catenary(3.0, "ENU")(a, b)
+    assert len(out) == 4 and out[3].shape == (100, 3)
+    assert_close(out[3], ref[3], RTOL64, 1e-13, "points")
+    assert_close(out[:3], ref[:3], RTOL64, 1e-12, "C,H,D")
+    assert cb.Catenary(3.0)(a, np.array([2.5, 2.0, 0.5]))[3] is None
+    ned = cb.Catenary(3.0, "NED")(a, np.array([1.0, 1.0, 1.0]))
+    assert_close(ned[3], orc.Catenary(3.0, "NED")(a, np.array([1.0, 1.0, 1.0]))[3], RTOL64, 1e-13, "NED")
+    idx, pt = cb.lowest_point(out[3])                       # fully_augmented_catenary.py:20-22
+    assert idx == int(np.argmin(ref[3][:, 2])) and np.allclose(pt, ref[3][idx])
+    with pytest.raises(ValueError):
+        cb.Catenary(3.0, "XYZ")
+
+
+def test_shapes_batch_vs_oracle(cb):
+    rng = np.random.default_rng(0)
+    n = 4000
+    A = rng.normal(size=(n, 3)) * 0.1
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    dist = rng.uniform(0.3, 2.85, n)
+    dist[:40] = rng.uniform(3.0, 3.2, 40)                   # taut -> invalid
+    d[40:80, :2] *= 1e-8                                     # near vertical
+    B = A + d * dist[:, None]
+    L = rng.uniform(2.0, 5.0, n)
+    th, ga = rng.uniform(-0.52, 0.52, n), rng.uniform(-0.52, 0.52, n)
+    curves, C, valid = cb.catenary_shapes(A, B, L, th, ga, which=15)
+    rel = B - A
+    assert_close(C, orc.solve_catenary(np.hypot(rel[:, 0], rel[:, 1]), rel[:, 2], L), RTOL64, 0, "C")
+    assert (valid[:40] & 1 == 0).all()
+    for i in range(0, n, 29):
+        ref = orc.transform_catenary(A[i], B[i], orc.Catenary(L[i]), th[i], ga[i])
+        for j in range(4):
+            got = curves[j][i] if ref[j].shape[0] == 100 else curves[j][i][[0, -1]]
+            assert_close(got, ref[j], RTOL64, 1e-12, f"cfg {i} out {j}")
+    # only 'final' requested == the 4th block of the full request; fp32 mode within 1e-4
+    (fin,), _, _ = cb.catenary_shapes(A, B, L, th, ga)
+    assert np.array_equal(fin, curves[3])
+    (f32,), _, v32 = cb.catenary_shapes(A[80:], B[80:], L[80:], th[80:], ga[80:], dtype=np.float32)
+    good = (valid[80:] == 3) & (v32 == 3)
+    assert good.mean() > 0.5
+    assert np.abs(f32[good] - fin[80:][good]).max() < 2e-4 * 5
+
+
+def test_shapes_config2_scale_properties(cb):
+    """Config 2 (1M x 100) through the chunked host pipeline: endpoints pinned, arc length == L."""
+    rng = np.random.default_rng(0)
+    n = 1 << 20
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    B = d * rng.uniform(1.2, 2.85, n)[:, None]
+    A = np.zeros((n, 3))
+    (orig,), C, valid = cb.catenary_shapes(A, B, 3.0, which=1)
+    ok = (valid & 1) == 1
+    assert ok.mean() > 0.5
+    assert np.abs(orig[:, 0]).max() == 0 and np.abs(orig[:, -1] - B).max() < 1e-12
+    sel = np.flatnonzero(ok)[::1000]
+    seg = np.linalg.norm(np.diff(orig[sel], axis=1), axis=2).sum(1)
+    assert (seg < 3.0 + 1e-9).all() and (seg > 2.97).all()      # 100-point polyline slightly shorter than the cable
+    (fin,), _, _ = cb.catenary_shapes(A[sel], B[sel], 3.0, np.zeros(sel.size), np.zeros(sel.size))
+    assert np.abs(fin - orig[sel]).max() < 1e-12                # theta = gamma = 0 is the identity
+
+
+# ---------------------------------------------------------------- dynamics
+def test_features_golden(cb):
+    g = golden("dynamics.npz")
+    assert_close(cb.extract_features(g), g["ref_X"], RTOL64, 1e-12, "extract_features")
+    assert_close(cb.extract_features(g, scaled=True), g["ref_Xs"], RTOL64, 1e-10, "scaled features")
+
+
+@pytest.mark.parametrize("nm", ["dtheta_dt", "dgamma_dt"])
+def test_integrators_golden(cb, nm):
+    g = golden("dynamics.npz")
+    m = cb.EquationModel(nm)
+    assert_close(m.predict(g["ref_Xs"]), g[f"ref_predict_{nm}"], RTOL64, 1e-13, "predict")
+    assert_close(cb.rk4_integration(m, g["ref_Xs"], g["Time"], 0.05), g[f"ref_rk4_{nm}"], RTOL64, 1e-12, "rk4")
+    assert_close(cb.rk4_integration(m, g["ref_Xs"], g["time_nu"], -0.02), g[f"ref_rk4_nu_{nm}"], RTOL64, 1e-12,
+                 "rk4 non-uniform dt")
+    y32 = cb.rk4_integration(m, g["ref_Xs"], g["Time"], 0.05, dtype=np.float32)
+    assert np.abs(y32 - g[f"ref_rk4_{nm}"]).max() < 1e-4
+
+
+def test_euler_golden_and_edges(cb):
+    g = golden("dynamics.npz")
+    mt, mg = cb.EquationModel("dtheta_dt"), cb.EquationModel("dgamma_dt")
+    th, ga = cb.integrate_theta_gamma(mt, mg, g["ref_Xs"], g["Time"], 0.05, 0.1)
+    assert_close(th, g["ref_euler_theta"], RTOL64, 1e-12, "euler theta")
+    assert_close(ga, g["ref_euler_gamma"], RTOL64, 1e-12, "euler gamma")
+    one = cb.rk4_integration(mt, g["ref_Xs"][:1], g["Time"][:1], 0.3)          # T = 1: just y0
+    assert one.shape == (1,) and one[0] == 0.3
+    with pytest.raises(ValueError):
+        cb.rk4_integration(mt, g["ref_Xs"][:, :17], g["Time"], 0.0)
+
+
+def test_config1_rollout_and_batch(cb):
+    """Config 1: 5,000-step open-loop RK4 of both ODEs, and 64 trajectories at once."""
+    rng = np.random.default_rng(42)
+    X = rng.normal(size=(64, 5000, 18))
+    t = np.arange(5000) * 0.05
+    for nm in ("dtheta_dt", "dgamma_dt"):
+        y = cb.rk4_integration(cb.EquationModel(nm), X, t, np.linspace(-0.1, 0.1, 64))
+        for i in (0, 63):
+            want = orc.rk4_integration_vec(orc.EquationModel(nm), X[i], t, np.linspace(-0.1, 0.1, 64)[i])
+            assert_close(y[i], want, RTOL64, 1e-11, f"config1 {nm} traj {i}")
+
+
+def test_every_hall_of_fame_equation(cb):
+    rng = np.random.default_rng(3)
+    X = rng.normal(size=(2000, 18))
+    tab = cb.equation_table()
+    assert len(tab) == 37
+    for i, nm, cx, live in tab:
+        assert_close(cb.predict(X, i), orc.equation(nm, cx)(X), RTOL64, 1e-13, f"{nm} c{cx}")
+    raw = rng.normal(size=(100, 18)) * np.array(orc.load_model()["scaler_scale"]) + np.array(orc.load_model()["scaler_mean"])
+    i = cb.equation_id("dtheta_dt")
+    assert_close(cb.predict(raw, i, apply_scaler=True), orc.equation("dtheta_dt")(orc.scale_features(raw)), RTOL64,
+                 1e-12, "apply_scaler")
+
+
+# ---------------------------------------------------------------- sampling MPC
+def _controls(K, H, seed=1234):
+    rng = np.random.default_rng(seed)
+    return np.clip(rng.normal(size=(K, H, 3)), -3, 3) * SIGMA
+
+
+def test_mpc_small_all_layouts(cb):
+    K, H = 3000, 50                                         # ragged: not a multiple of the block size
+    U = _controls(K, H)
+    p = cb.default_mpc_params()
+    pref = cb.circle_reference(H, p["dt"])
+    Jo, traj = orc.mpc_rollout_costs(orc.default_mpc_params(), U, pref, return_traj=True)
+    bi, bc, J = cb.mpc_sample_step(p, U, pref)
+    assert_close(J, Jo, RTOL64, 0, "costs AoS")
+    assert bi == int(np.argmin(Jo)) and bc == J[bi]
+    bi2, bc2, J2 = cb.mpc_sample_step(p, np.ascontiguousarray(U.transpose(1, 2, 0)), pref, layout="H3K")
+    assert np.array_equal(J, J2) and bi2 == bi              # layout does not change a single bit
+    bi3, _, none = cb.mpc_sample_step(p, U, pref, return_costs=False)
+    assert none is None and bi3 == bi
+    b32, c32, J32 = cb.mpc_sample_step(p, U.astype(np.float32), pref, dtype=np.float32)
+    assert_close(J32, Jo, RTOL32, 0, "costs f32")
+
+
+def test_mpc_config3_full_size(cb):
+    """Config 3: 65,536 candidates x horizon 50 -- costs within 1e-9, argmin index exact."""
+    K, H = 65536, 50
+    U = _controls(K, H)
+    p = cb.default_mpc_params()
+    pref = cb.circle_reference(H, p["dt"])
+    Jo = orc.mpc_rollout_costs(orc.default_mpc_params(), U, pref)
+    bi, bc, J = cb.mpc_sample_step(p, U, pref)
+    assert_close(J, Jo, RTOL64, 0, "config 3 costs")
+    assert bi == int(np.argmin(Jo))
+    assert abs(bc - Jo[bi]) <= RTOL64 * abs(Jo[bi])
+
+
+def test_mpc_constraints_active(cb):
+    """Poses that trigger every cost term: cable nearly taut (length penalty, nan C penalty) and a deep sag
+    below the seabed clearance."""
+    K, H = 2048, 30
+    U = _controls(K, H, 7) * 4.0
+    for over in (dict(P1=(1.9, 1.9, -0.9)), dict(P1=(0.4, 0.3, -0.6), z_floor=-1.2), dict(P1=(1.0, 1.0, -1.0), L=2.0),
+                 dict(P1=(0.05, 0.0, -1.0)), dict(dt=0.05)):
+        po = orc.default_mpc_params(**over)
+        pref = cb.circle_reference(H, po["dt"])
+        Jo = orc.mpc_rollout_costs(po, U, pref)
+        bi, bc, J = cb.mpc_sample_step(cb.default_mpc_params(**over), U, pref)
+        assert_close(J, Jo, RTOL64, 0, f"costs {over}")
+        assert bi == int(np.argmin(Jo)), over
+
+
+def test_mpc_other_equations(cb):
+    K, H = 1024, 40
+    U = _controls(K, H, 3)
+    pref = cb.circle_reference(H, 0.01)
+    for tcx, gcx in ((19, 7), (8, 5), (25, 9)):
+        try:
+            po = orc.default_mpc_params(theta_cx=tcx, gamma_cx=gcx)
+            Jo = orc.mpc_rollout_costs(po, U, pref)
+        except StopIteration:
+            continue
+        _, _, J = cb.mpc_sample_step(cb.default_mpc_params(theta_cx=tcx, gamma_cx=gcx), U, pref)
+        assert_close(J, Jo, RTOL64, 0, f"eq pair {tcx},{gcx}")
+
+
+def test_mpc_argmin_ties_and_nan(cb):
+    """np.argmin order: duplicates -> first index; identical candidates across blocks."""
+    K, H = 1000, 10
+    U = _controls(K, H, 9)
+    U[900] = U[17]
+    U[500] = U[17]
+    p = cb.default_mpc_params(w_trk=0.0, w_ang=0.0, w_len=0.0, w_sag=0.0)      # cost = control effort only
+    pref = cb.circle_reference(H, 0.01)
+    U[17] *= 0.0
+    U[500] *= 0.0
+    U[900] *= 0.0
+    bi, bc, J = cb.mpc_sample_step(p, U, pref)
+    assert J[17] == J[500] == J[900] == 0.0 and bi == 17 and bc == 0.0
+    U[300, 3, 1] = np.nan
+    bi, bc, J = cb.mpc_sample_step(p, U, pref)
+    assert bi == 300 and np.isnan(bc)                        # NaN wins like np.argmin
+
+
+def test_mpc_device_rng_matches_oracle_philox(cb):
+    K, H = 4096, 50
+    p = cb.default_mpc_params()
+    pref = cb.circle_reference(H, p["dt"])
+    Uo = orc.sample_controls(1234, np.arange(K), H, SIGMA)
+    Jo = orc.mpc_rollout_costs(orc.default_mpc_params(), Uo, pref)
+    bi, bc, J = cb.mpc_sample_step(p, None, pref, K=K, sigma=SIGMA, seed=1234)
+    assert_close(J, Jo, RTOL64, 0, "rng costs")
+    assert bi == int(np.argmin(Jo))
+    # shards of the same job (k_offset) reproduce slices of it: the multi-GPU path on one GPU
+    winners = []
+    for lo in range(0, K, 1024):
+        i, c, Js = cb.mpc_sample_step(p, None, pref, K=1024, sigma=SIGMA, seed=1234, k_offset=lo)
+        assert np.array_equal(Js, J[lo:lo + 1024])
+        winners.append((c, i))
+    gi, gc = cb.reduce_winners([w[0] for w in winners], [w[1] for w in winners])
+    assert gi == bi and gc == bc
+
+
+def test_mpc_fleet(cb):
+    """Config 5 semantics at reduced size: independent problems, segmented argmin, no cross-talk."""
+    n, K, H = 6, 1500, 20
+    rng = np.random.default_rng(10_000)
+    p = cb.default_mpc_params()
+    poses = np.array([1.0, 1.0, -1.0]) + rng.normal(size=(n, 3)) * 0.15
+    prm = dict(p, P1=poses, theta=rng.uniform(-0.2, 0.2, n), gamma=rng.uniform(-0.2, 0.2, n))
+    prm["theta_prev"], prm["gamma_prev"] = prm["theta"], prm["gamma"]
+    problems = cb.make_problems(prm, n)
+    pref = np.stack([cb.circle_reference(H, p["dt"], center=poses[i]) for i in range(n)])
+    bi, bc, J = cb.mpc_fleet_step(p, problems, pref, K, SIGMA, seed=77, return_costs=True, problem_offset=3)
+    for i in range(n):
+        Uo = orc.sample_controls(77, np.arange(K), H, SIGMA, problem=3 + i)
+        po = orc.default_mpc_params(P1=poses[i], theta=prm["theta"][i], gamma=prm["gamma"][i],
+                                    theta_prev=prm["theta"][i], gamma_prev=prm["gamma"][i])
+        Jo = orc.mpc_rollout_costs(po, Uo, pref[i])
+        assert_close(J[i], Jo, RTOL64, 0, f"fleet problem {i}")
+        assert bi[i] == int(np.argmin(Jo)) and bc[i] == J[i, bi[i]]
+
+
+def test_mpc_config4_shard_property(cb):
+    """Large-K property (config-4 shard size, H=100): the device argmin equals np.argmin of the device costs,
+    and a sampled subset of candidates matches the oracle."""
+    K, H = 524288, 100
+    p = cb.default_mpc_params()
+    pref = cb.circle_reference(H, p["dt"])
+    bi, bc, J = cb.mpc_sample_step(p, None, pref, K=K, sigma=SIGMA, seed=5, k_offset=3 * K)
+    assert bi - 3 * K == int(np.argmin(J)) and bc == J[bi - 3 * K]
+    pick = np.arange(0, K, 997)
+    Uo = orc.sample_controls(5, 3 * K + pick, H, SIGMA)
+    assert_close(J[pick], orc.mpc_rollout_costs(orc.default_mpc_params(), Uo, pref), RTOL64, 0, "sampled candidates")
+
+
+def test_device_step_matches_host_call(cb):
+    import importlib
+    dev = importlib.import_module(cb.__name__ + ".device")
+    K, H = 8192, 50
+    U = np.ascontiguousarray(_controls(K, H).transpose(1, 2, 0))
+    p = cb.default_mpc_params()
+    pref = cb.circle_reference(H, p["dt"])
+    bi, bc, J = cb.mpc_sample_step(p, U, pref, layout="H3K")
+    st = dev.MpcDeviceStep(p, pref, K, controls=U, keep_costs=True)
+    for _ in range(3):                                      # relaunch: tickets reset by the kernel itself
+        st.launch()
+    i2, c2 = st.result()
+    assert int(i2[0]) == bi and float(c2[0]) == bc
+    assert np.array_equal(st.costs.cpu().numpy()[0], J)
+
+
+def test_errors_are_values_not_crashes(cb):
+    p = cb.default_mpc_params()
+    with pytest.raises(ValueError):
+        cb.mpc_sample_step(p, np.zeros((4, 5, 2)), cb.circle_reference(5, 0.01))
+    with pytest.raises(ValueError):
+        cb.mpc_sample_step(dict(p, dt=-1.0), np.zeros((4, 5, 3)), cb.circle_reference(5, 0.01))
+    with pytest.raises(ValueError):
+        cb.catenary_shapes(np.zeros((2, 3)), np.zeros((3, 3)), 3.0)
+    assert cb.default_context().launch_count > 0
