@@ -170,12 +170,16 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    sampler.start()
     for i in range(max(args.warmup, 3)):
         one(i)
     barrier()
+    t_wait = time.time()
+    while not sampler.lines and time.time() - t_wait < 5.0:      # nvidia-smi takes ~1 s to print its first sample
+        one(0)
+        torch.cuda.synchronize()
     # ---- device-timed throughput: K steps between two events on the launching stream ----
-    sampler = ClockSampler(local)
-    sampler.start()
     l0 = ctx.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()

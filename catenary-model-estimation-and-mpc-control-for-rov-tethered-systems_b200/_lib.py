@@ -48,7 +48,7 @@ SIGNATURES = {
     "cat_last_error": (C.c_char_p, [_vp]),
     "cat_launch_count": (_i64, [_vp]),
     "cat_stream": (_vp, [_vp]),
-    "cat_set_stream": (_int, [_vp, _vp]),
+    "cat_set_stream": (_int, [_vp, _vp, _int]),
     "cat_host_alloc": (_int, [_vp, C.c_size_t, C.POINTER(_vp)]),
     "cat_host_free": (_int, [_vp, _vp]),
     "cat_timer_start": (_int, [_vp]),

@@ -46,7 +46,12 @@ class Context:
         return self.lib.cat_stream(self.handle)
 
     def set_stream(self, cuda_stream):
-        self.check(self.lib.cat_set_stream(self.handle, C.c_void_p(cuda_stream or 0)))
+        """Run subsequent calls on a caller-owned CUDA stream (an integer handle; 0 = the legacy default
+        stream).  ``None`` restores the context's own stream."""
+        if cuda_stream is None:
+            self.check(self.lib.cat_set_stream(self.handle, None, 1))
+        else:
+            self.check(self.lib.cat_set_stream(self.handle, C.c_void_p(int(cuda_stream)), 0))
 
     def timer_start(self):
         self.check(self.lib.cat_timer_start(self.handle))

@@ -78,7 +78,11 @@ __device__ __forceinline__ void cat_shape_span_setup(const T A[3], const T Bq[3]
 
 template <typename T, typename M>
 __device__ __forceinline__ void cat_shape_point(const T A[3], const CatShapeSpan<T>& sp, T s, bool last, T p[3]) {
-  if (sp.valid) {
+  if (s == T(0)) {          // the curve starts exactly at A (cosh is even: the oracle's z_0 - zA is exactly 0)
+    p[0] = A[0];
+    p[1] = A[1];
+    p[2] = A[2];
+  } else if (sp.valid) {
     p[0] = A[0] + sp.rel[0] * s;
     p[1] = A[1] + sp.rel[1] * s;
     const T t = sp.two_u * s - sp.v_low;

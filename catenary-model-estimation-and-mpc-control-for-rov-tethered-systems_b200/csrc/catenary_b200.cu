@@ -452,9 +452,9 @@ void* cat_stream(void* ctx) {
   return c ? (void*)c->stream : nullptr;
 }
 
-int cat_set_stream(void* ctx, void* cuda_stream) {
+int cat_set_stream(void* ctx, void* cuda_stream, int own) {
   CTX();
-  c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+  c->stream = own ? c->own_stream : (cudaStream_t)cuda_stream;
   return CAT_OK;
 }
 

@@ -98,8 +98,9 @@ CAT_API const char* cat_last_error(void* ctx);
 CAT_API int64_t cat_launch_count(void* ctx);
 /* the ctx stream (cudaStream_t) for callers that enqueue their own work around *_dev calls */
 CAT_API void* cat_stream(void* ctx);
-/* run subsequent calls of this ctx on a caller-owned stream (NULL restores the ctx stream) */
-CAT_API int cat_set_stream(void* ctx, void* cuda_stream);
+/* run subsequent calls of this ctx on a caller-owned stream; own != 0 restores the ctx stream (cuda_stream is
+ * then ignored).  cuda_stream == NULL with own == 0 is the CUDA legacy default stream. */
+CAT_API int cat_set_stream(void* ctx, void* cuda_stream, int own);
 /* pinned host memory for the un-suffixed (host-pointer) entry points */
 CAT_API int cat_host_alloc(void* ctx, size_t bytes, void** out);
 CAT_API int cat_host_free(void* ctx, void* p);

@@ -107,10 +107,10 @@ def test_shapes_batch_vs_oracle(cb):
     d = rng.normal(size=(n, 3))
     d /= np.linalg.norm(d, axis=1, keepdims=True)
     dist = rng.uniform(0.3, 2.85, n)
-    dist[:40] = rng.uniform(3.0, 3.2, 40)                   # taut -> invalid
+    L = rng.uniform(2.0, 5.0, n)
+    dist[:40] = L[:40] * rng.uniform(1.0, 1.05, 40)         # taut -> invalid
     d[40:80, :2] *= 1e-8                                     # near vertical
     B = A + d * dist[:, None]
-    L = rng.uniform(2.0, 5.0, n)
     th, ga = rng.uniform(-0.52, 0.52, n), rng.uniform(-0.52, 0.52, n)
     curves, C, valid = cb.catenary_shapes(A, B, L, th, ga, which=15)
     rel = B - A
