@@ -274,8 +274,14 @@ def run_ours(args):
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     hbm_ach = K * H * BYTES_PER_ROLLOUT_STEP / (k_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            traffic = json.load(fh)["k_mpc_rollout_f64_config3"]["dram_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        pass
     roofline = {"bound": "fp64_fma", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                "frac": ach_tf / peak_tf, "traffic": None, "kernel": "k_mpc_rollout<double,false>",
+                "frac": ach_tf / peak_tf, "traffic": traffic, "kernel": "k_mpc_rollout<double,false>",
                 "kernel_ms": k_ms, "peak_source": "cat_measure_peak(DFMA) measured in this run x 2 flops",
                 "flops_per_rollout_step": FLOPS_PER_ROLLOUT_STEP,
                 "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
