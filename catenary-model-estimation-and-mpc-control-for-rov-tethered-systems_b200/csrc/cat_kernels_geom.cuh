@@ -14,7 +14,7 @@ __global__ void __launch_bounds__(256) k_solve_param(long long n, const T* __res
   typedef CatMath<T> M;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const CatSpan<T> s = cat_span<T, M>(l[i], dH[i], L[i * L_stride], c_lo, c_hi, T(0));
+  const CatSpan<T> s = cat_span<T, M>(l[i], dH[i], L[i * L_stride], c_lo, c_hi, cat_cold<T>());
   C_out[i] = s.C;
 }
 
@@ -58,7 +58,7 @@ __device__ __forceinline__ void cat_shape_span_setup(const T A[3], const T Bq[3]
   sp.Bend[2] = Bq[2];
   const T l = M::sqrt_(sp.rel[0] * sp.rel[0] + sp.rel[1] * sp.rel[1]);
   const T dH = sp.rel[2];
-  const CatSpan<T> s = cat_span<T, M>(l, dH, L, c_lo, c_hi, T(0));
+  const CatSpan<T> s = cat_span<T, M>(l, dH, L, c_lo, c_hi, cat_cold<T>());
   sp.l = l;
   sp.valid = (s.C == s.C) ? 1 : 0;
   if (C_out) *C_out = s.C;
@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(256) k_span_terms(long long n, const T* __rest
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const T li = l[i], hi = dH[i], Li = L[i * L_stride];
-  const CatSpan<T> s = cat_span<T, M>(li, hi, Li, c_lo, c_hi, T(0));
+  const CatSpan<T> s = cat_span<T, M>(li, hi, Li, c_lo, c_hi, cat_cold<T>());
   if (C_out) C_out[i] = s.C;
   const bool ok = s.C == s.C;
   if (x_low) {

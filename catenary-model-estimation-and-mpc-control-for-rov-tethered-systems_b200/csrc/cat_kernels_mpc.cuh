@@ -16,7 +16,7 @@
 #include "gen/dyn_eqs.cuh"
 #include "../../include/catenary_b200.h"
 
-#define CAT_MPC_BLOCK 128
+#define CAT_MPC_BLOCK 128   // maximum; the host launches 64 when the batch is under ~1 wave (better SM balance)
 
 // Kernel-side parameters in the compute type.  Derived constants are formed on the host in
 // double exactly as the oracle forms them (dt/1000, dt/6, rho*L, z_floor+margin).
@@ -25,7 +25,8 @@ template <typename T> struct CatMpcDev {
   long long sk, sh, sa, sp;   // control strides in elements: candidate, step, axis, problem
   int H, n_problems, flags, problem_offset;
   int eq_theta, eq_gamma;
-  T dt, dt_mm, dt6, L, w_trk, w_du, w_len, w_sag, w_ang, rhoL, z_thr, c_lo, c_hi, pen, clip;
+  int carry_t, carry_g;   // equation reads neither column 14 nor 15: k1 of the next step == k4 of this one
+  T dt, dt_mm, dt6, L, w_trk, w_du, w_len, w_sag, w_ang, rhoL, rhoL2, z_thr, c_lo, c_hi, pen, clip;
   T sigma[3];
   unsigned long long seed;
 };
@@ -95,7 +96,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
               long long* __restrict__ best_idx) {
   typedef CatMath<T> M;
   const int prob = blockIdx.y;
-  const long long k = (long long)blockIdx.x * CAT_MPC_BLOCK + threadIdx.x;
+  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = k < q.K;
   const long long kk = live ? k : q.K - 1;   // idle lanes shadow the last candidate (no divergence, no OOB)
 
@@ -106,11 +107,29 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   T A[3] = {T(pb->A1[0]), T(pb->A1[1]), T(pb->A1[2])};
   T th = T(pb->theta), ga = T(pb->gamma), thp = T(pb->theta_prev), gap = T(pb->gamma_prev);
   T J = T(0);
-  T u_warm = T(0);
+  CatWarm<T> warm = cat_cold<T>();
 
   const bool rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
   const T* uc = rng ? nullptr : controls + (long long)prob * q.sp + kk * q.sk;
   const double* pr = p_ref + (long long)prob * q.H * 3;
+
+  // Scaled features and stage-1 slopes of the CURRENT state.  They are carried across steps: the
+  // stage-4 feature row of step h equals the stage-1 row of step h+1 except for the theta/gamma
+  // columns 14, 15 (same P, V, A, theta_prev, gamma_prev), so x0 is x1 with two entries replaced,
+  // and an equation that reads neither column has k1(h+1) == k4(h) bit for bit.
+  T x0[18];
+  cat_features18<T, M>(P0, P, V, A, th, ga, thp, gap, x0);
+  cat_scale18<T>(x0);
+  T k1t, k1g;
+  cat_eval_pair<T, GENERIC>(q, x0, k1t, k1g);
+  bool carry_t, carry_g;
+  if constexpr (GENERIC) {
+    carry_t = q.carry_t != 0;
+    carry_g = q.carry_g != 0;
+  } else {
+    carry_t = (CAT_DTHETA_LIVE_MASK & 0xC000u) == 0;
+    carry_g = (CAT_DGAMMA_LIVE_MASK & 0xC000u) == 0;
+  }
 
   for (int h = 0; h < q.H; ++h) {
     T Vn[3];
@@ -129,15 +148,12 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       An[a] = M::div_(Vn[a] - V[a], q.dt);
     }
     // ---- RK4 step of both angle ODEs (simulate_rk4_theta_gamma.py:61-66; k3 == k2) ----
-    T x0[18], x1[18], xm[18];
-    cat_features18<T, M>(P0, P, V, A, th, ga, thp, gap, x0);
-    cat_scale18<T>(x0);
-    T k1t, k1g, k2t, k2g, k4t, k4g;
-    cat_eval_pair<T, GENERIC>(q, x0, k1t, k1g);
+    T x1[18], xm[18];
     cat_features18<T, M>(P0, Pn, Vn, An, th + q.dt * k1t, ga + q.dt * k1g, th, ga, x1);
     cat_scale18<T>(x1);
 #pragma unroll
     for (int j = 0; j < 18; ++j) xm[j] = (x0[j] + x1[j]) * T(0.5);
+    T k2t, k2g, k4t, k4g;
     cat_eval_pair<T, GENERIC>(q, xm, k2t, k2g);
     cat_eval_pair<T, GENERIC>(q, x1, k4t, k4g);
     const T thn = th + q.dt6 * (k1t + T(2) * k2t + T(2) * k2t + k4t);
@@ -146,14 +162,16 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     const T rx = Pn[0] - P0[0], ry = Pn[1] - P0[1], rz = Pn[2] - P0[2];
     const T l2 = rx * rx + ry * ry;
     const T l = M::sqrt_(l2);
-    const T d = M::sqrt_(l2 + rz * rz);
-    const CatSpan<T> sp = cat_span<T, M>(l, rz, q.L, q.c_lo, q.c_hi, u_warm);
-    u_warm = sp.u;
+    const T d2 = l2 + rz * rz;
+    const CatSpan<T> sp = cat_span<T, M, false>(l, rz, q.L, q.c_lo, q.c_hi, warm);
+    warm = sp.warm;
     const T z_low = cat_z_low<T, M>(sp, l, q.L, P0[2], P0[2] + rz);
     // ---- cost, association as in the oracle ----
     const T ex = Pn[0] - T(pr[3 * h]), ey = Pn[1] - T(pr[3 * h + 1]), ez = Pn[2] - T(pr[3 * h + 2]);
     const T dvx = Vn[0] - V[0], dvy = Vn[1] - V[1], dvz = Vn[2] - V[2];
-    const T over = M::max_(T(0), d - q.rhoL);
+    // max(0, d - rho L): the square root is only taken when the term is active (or d is NaN)
+    T over = T(0);
+    if (!(d2 <= q.rhoL2)) over = M::max_(T(0), M::sqrt_(d2) - q.rhoL);
     const T deep = M::max_(T(0), q.z_thr - z_low);
     T c = q.w_trk * (ex * ex + ey * ey + ez * ez);
     c = c + q.w_du * (dvx * dvx + dvy * dvy + dvz * dvz);
@@ -171,6 +189,20 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       P[a] = Pn[a];
       V[a] = Vn[a];
       A[a] = An[a];
+    }
+    // ---- stage-1 row and slopes of the next step ----
+#pragma unroll
+    for (int j = 0; j < 18; ++j) x0[j] = x1[j];
+    x0[14] = (th - CatScaler<T>::mean(14)) * CatScaler<T>::inv_scale(14);
+    x0[15] = (ga - CatScaler<T>::mean(15)) * CatScaler<T>::inv_scale(15);
+    if (carry_t && carry_g) {
+      k1t = k4t;
+      k1g = k4g;
+    } else {
+      T nt, ng;
+      cat_eval_pair<T, GENERIC>(q, x0, nt, ng);
+      k1t = carry_t ? k4t : nt;
+      k1g = carry_g ? k4g : ng;
     }
   }
 
@@ -193,7 +225,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   double bc = __longlong_as_double(0x7ff0000000000000LL);
   long long bi = 0x7fffffffffffffffLL;
   const volatile CatBest* slots = block_best + (long long)prob * gridDim.x;
-  for (unsigned int s = threadIdx.x; s < gridDim.x; s += CAT_MPC_BLOCK) {
+  for (unsigned int s = threadIdx.x; s < gridDim.x; s += blockDim.x) {
     const double oc = slots[s].cost;
     const long long oi = slots[s].idx;
     if (cat_better(oc, oi, bc, bi)) {

@@ -8,11 +8,98 @@
 #include <math.h>
 #include <stdint.h>
 
+// ------------------------------------------------------------------------------------------
+// fp64 elementary functions written for this path.  CUDA's sin()/exp() re-materialise their
+// 64-bit literals with UMOV pairs, fetch a coefficient table with LDG and carry inf/nan/huge-
+// argument select chains; in the rollout kernel those were 28% of the issue slots (profiles/r1_*).
+// Here every coefficient lives in __constant__ memory, so it is a direct c[bank][off] operand
+// of the DFMA, and the rare cases take one cold branch to the CUDA routine.
+// ------------------------------------------------------------------------------------------
+__constant__ double CAT_SIN_C[10] = {   // sin r = r + r z (c0 + z (c1 + ...)), z = r^2, |r| <= pi/2
+    -1.0 / 6.0,
+    1.0 / 120.0,
+    -1.0 / 5040.0,
+    1.0 / 362880.0,
+    -1.0 / 39916800.0,
+    1.0 / 6227020800.0,
+    -1.0 / 1307674368000.0,
+    1.0 / 355687428096000.0,
+    -1.0 / 121645100408832000.0,
+    1.0 / 51090942171709440000.0};
+__constant__ double CAT_PI_C[5] = {
+    0.31830988618379067154,      // 1/pi
+    6755399441055744.0,          // 1.5 * 2^52: fma(x, 1/pi, magic) rounds x/pi to an integer in the low word
+    3.141592653589793116,        // pi, first 53 bits
+    1.2246467991473532072e-16,   // next 53 bits
+    -2.9947698097183396659e-33}; // next
+__constant__ double CAT_HYP_S[7] = {    // sinh(r)/r - 1 = z (s0 + z (s1 + ...))
+    1.0 / 6.0, 1.0 / 120.0, 1.0 / 5040.0, 1.0 / 362880.0, 1.0 / 39916800.0, 1.0 / 6227020800.0,
+    1.0 / 1307674368000.0};
+__constant__ double CAT_HYP_C[7] = {    // cosh(r) - 1 = z (c0 + z (c1 + ...))
+    1.0 / 2.0, 1.0 / 24.0, 1.0 / 720.0, 1.0 / 40320.0, 1.0 / 3628800.0, 1.0 / 479001600.0,
+    1.0 / 87178291200.0};
+__constant__ double CAT_LN2_C[4] = {
+    1.4426950408889634074,       // 1/ln2
+    6755399441055744.0,
+    0.69314718055994528623,      // ln2 hi
+    2.3190468138462995584e-17};  // ln2 lo
+
+// sin(x), |error| <~ 2 ulp for |x| < 1e5 (the scaled features live in |x| < 1e3); beyond that, and
+// for inf/nan, the CUDA routine.
+__device__ __forceinline__ double cat_sin_f64(double x) {
+  if (!(fabs(x) < 1.0e5)) return sin(x);
+  const double t = fma(x, CAT_PI_C[0], CAT_PI_C[1]);
+  const int q = __double2loint(t);
+  const double qf = t - CAT_PI_C[1];
+  double r = fma(-qf, CAT_PI_C[2], x);
+  r = fma(-qf, CAT_PI_C[3], r);
+  r = fma(-qf, CAT_PI_C[4], r);
+  const double z = r * r;
+  double p = CAT_SIN_C[9];
+#pragma unroll
+  for (int i = 8; i >= 0; --i) p = fma(p, z, CAT_SIN_C[i]);
+  const double v = fma(r * z, p, r);
+  // sin(x) = (-1)^q sin(r)
+  return __hiloint2double(__double2hiint(v) ^ (q << 31), __double2loint(v));
+}
+
+// For u >= 0: sh = sinh u, cm = cosh u - 1, sm = sinh u - u, all without cancellation at small u and
+// without a division: u = k ln2 + r, |r| <= ln2/2;  sinh/cosh(k ln2) are exact combinations of
+// 2^k, 2^-k;  addition theorems.  For k = 0 this IS the series (A = 0, B = 1).
+__device__ __forceinline__ void cat_hyp_f64(double u, double& sm, double& cm, double& sh) {
+  u = fmin(u, 700.0);
+  const double t = fma(u, CAT_LN2_C[0], CAT_LN2_C[1]);
+  const int k = __double2loint(t);
+  const double kf = t - CAT_LN2_C[1];
+  const double r = fma(-kf, CAT_LN2_C[3], fma(-kf, CAT_LN2_C[2], u));
+  const double z = r * r;
+  double S = CAT_HYP_S[6], Cc = CAT_HYP_C[6];
+#pragma unroll
+  for (int i = 5; i >= 0; --i) {
+    S = fma(S, z, CAT_HYP_S[i]);
+    Cc = fma(Cc, z, CAT_HYP_C[i]);
+  }
+  const double rS = r * (z * S);          // sinh r - r
+  const double chr1 = z * Cc;             // cosh r - 1
+  const double shr = rS + r;              // sinh r
+  // 2^(k-1), 2^(-k-1)
+  const double p2 = __hiloint2double((k + 1022) << 20, 0);
+  const double m2 = __hiloint2double((1022 - k) << 20, 0);
+  const double A = p2 - m2;               // sinh(k ln2)   (0 for k = 0)
+  const double Bm1 = (p2 - 0.5) + m2 - 0.5;   // cosh(k ln2) - 1 (exactly 0 for k = 0)
+  // sinh u = A cosh r + B sinh r ; cosh u - 1 = (B - 1) + B (cosh r - 1) + A sinh r
+  const double Ach = fma(A, chr1, A);
+  sh = fma(Bm1, shr, shr) + Ach;
+  cm = fma(Bm1, chr1, chr1) + fma(A, shr, Bm1);
+  // sinh u - u = [A cosh r - k ln2] + (B - 1) sinh r + (sinh r - r)
+  sm = fma(Bm1, shr, rS) + (fma(-kf, CAT_LN2_C[2], Ach) - kf * CAT_LN2_C[3]);
+}
+
 template <typename T> struct CatMath;
 
 template <> struct CatMath<double> {
   typedef double real;
-  static __device__ __forceinline__ double sin_(double x) { return sin(x); }
+  static __device__ __forceinline__ double sin_(double x) { return cat_sin_f64(x); }
   static __device__ __forceinline__ double cos_(double x) { return cos(x); }
   static __device__ __forceinline__ void sincos_(double x, double* s, double* c) { sincos(x, s, c); }
   static __device__ __forceinline__ double tanh_(double x) { return tanh(x); }
@@ -75,39 +162,41 @@ template <> struct CatMath<float> {
 // sinh(u), cosh(u) at the root so the lowest point needs no further transcendental.
 // ------------------------------------------------------------------------------------------
 template <typename T> struct CatRoot {
-  T u, sh, ch;   // u = C l / 2, sinh(u), cosh(u)
+  T u, sh, ch, cm;   // u = C l / 2, sinh(u), cosh(u), cosh(u) - 1
 };
 
-// sinh(u)-u, cosh(u)-1, sinh(u) for u > 0.  Series below 1 (no cancellation), exp above.
+// warm start carried from the previous solve of a slowly moving span: the old root with its
+// sinh / cosh-1 and the e it solved.  u == 0 means "none" (cold start).
+template <typename T> struct CatWarm {
+  T u, sh, cm, e;
+};
+
+// sinh(u)-u, cosh(u)-1, sinh(u) for u > 0.
 template <typename T, typename M>
 __device__ __forceinline__ void cat_hyp(T u, T& sm, T& cm, T& sh) {
-  if (u < T(1)) {
-    const T w = u * u;
-    // sinh(u) - u = u w / 6 * (1 + w/20 (1 + w/42 (1 + w/72 (1 + w/110 (1 + w/156 (1 + w/210 (1 + w/272)))))))
-    T p = M::fma_(w, T(1.0 / 272.0), T(1));
-    p = M::fma_(w * T(1.0 / 210.0), p, T(1));
-    p = M::fma_(w * T(1.0 / 156.0), p, T(1));
-    p = M::fma_(w * T(1.0 / 110.0), p, T(1));
-    p = M::fma_(w * T(1.0 / 72.0), p, T(1));
-    p = M::fma_(w * T(1.0 / 42.0), p, T(1));
-    p = M::fma_(w * T(1.0 / 20.0), p, T(1));
-    sm = u * w * T(1.0 / 6.0) * p;
-    // cosh(u) - 1 = w / 2 * (1 + w/12 (1 + w/30 (1 + w/56 (1 + w/90 (1 + w/132 (1 + w/182 (1 + w/240)))))))
-    T q = M::fma_(w, T(1.0 / 240.0), T(1));
-    q = M::fma_(w * T(1.0 / 182.0), q, T(1));
-    q = M::fma_(w * T(1.0 / 132.0), q, T(1));
-    q = M::fma_(w * T(1.0 / 90.0), q, T(1));
-    q = M::fma_(w * T(1.0 / 56.0), q, T(1));
-    q = M::fma_(w * T(1.0 / 30.0), q, T(1));
-    q = M::fma_(w * T(1.0 / 12.0), q, T(1));
-    cm = w * T(0.5) * q;
-    sh = sm + u;
+  if constexpr (sizeof(T) == 8) {
+    cat_hyp_f64(u, sm, cm, sh);
   } else {
-    const T E = M::exp_(u);
-    const T Ei = M::rcp_(E);
-    sh = T(0.5) * (E - Ei);
-    sm = sh - u;
-    cm = T(0.5) * (E + Ei) - T(1);
+    if (u < T(1)) {   // series below 1 (no cancellation), exp above
+      const T w = u * u;
+      T p = M::fma_(w, T(1.0 / 110.0), T(1));
+      p = M::fma_(w * T(1.0 / 72.0), p, T(1));
+      p = M::fma_(w * T(1.0 / 42.0), p, T(1));
+      p = M::fma_(w * T(1.0 / 20.0), p, T(1));
+      sm = u * w * T(1.0 / 6.0) * p;
+      T q = M::fma_(w, T(1.0 / 90.0), T(1));
+      q = M::fma_(w * T(1.0 / 56.0), q, T(1));
+      q = M::fma_(w * T(1.0 / 30.0), q, T(1));
+      q = M::fma_(w * T(1.0 / 12.0), q, T(1));
+      cm = w * T(0.5) * q;
+      sh = sm + u;
+    } else {
+      const T E = M::exp_(u);
+      const T Ei = M::rcp_(E);
+      sh = T(0.5) * (E - Ei);
+      sm = sh - u;
+      cm = T(0.5) * (E + Ei) - T(1);
+    }
   }
 }
 
@@ -119,26 +208,40 @@ __device__ __forceinline__ T cat_u_guess(T e) {
   return lr + M::log_(lr + M::log_(M::max_(lr, T(1))));
 }
 
-// e = r - 1 > 0 required.  u0 > 0: warm start (previous step's root), else cold start.
+// one safeguarded Halley step of g(u) = sm - e u  (g' = cm - e, g'' = sh)
 template <typename T, typename M>
-__device__ __forceinline__ CatRoot<T> cat_solve_u(T e, T u0) {
-  T u = (u0 > T(0)) ? u0 : cat_u_guess<T, M>(e);
+__device__ __forceinline__ T cat_halley_step(T u, T g, T gp, T sh) {
+  T du;
+  const T den = T(2) * gp * gp - g * sh;
+  if (gp > T(0) && den > T(0)) {
+    du = M::div_(T(2) * g * gp, den);          // Halley
+  } else if (gp > T(0)) {
+    du = M::div_(g, gp);                       // Newton
+  } else {
+    du = -(T(0.5) * u + T(0.1));               // left of the minimum of g: move right
+  }
+  if (du >= u) du = T(0.5) * u;                // keep u > 0
+  return du;
+}
+
+// e = r - 1 > 0 required.  With a warm start the first Halley step costs no transcendental: at the
+// old root sm(u0) = e0 u0, so g(u0) for the new e is (e0 - e) u0 and g', g'' come from the carried
+// cosh-1 and sinh.  A rollout step moves the span by ~1e-3 relative, so that step lands within
+// ~1e-9 of the root and ONE full iteration finishes (the loop still runs until |du| is below tol).
+template <typename T, typename M>
+__device__ __forceinline__ CatRoot<T> cat_solve_u(T e, const CatWarm<T>& w) {
+  T u;
+  if (w.u > T(0)) {
+    u = w.u - cat_halley_step<T, M>(w.u, (w.e - e) * w.u, w.cm - e, w.sh);
+  } else {
+    u = cat_u_guess<T, M>(e);
+  }
   T sm, cm, sh, du;
   int it = 0;
   bool more;
   do {
     cat_hyp<T, M>(u, sm, cm, sh);
-    const T g = sm - e * u;
-    const T gp = cm - e;
-    const T den = T(2) * gp * gp - g * sh;
-    if (gp > T(0) && den > T(0)) {
-      du = M::div_(T(2) * g * gp, den);          // Halley
-    } else if (gp > T(0)) {
-      du = M::div_(g, gp);                       // Newton
-    } else {
-      du = -(T(0.5) * u + T(0.1));               // left of the minimum of g: move right
-    }
-    if (du >= u) du = T(0.5) * u;                // keep u > 0
+    du = cat_halley_step<T, M>(u, sm - e * u, cm - e, sh);
     u -= du;
     more = M::abs_(du) > M::step_tol() * M::min_(u, T(1));
   } while (more && ++it < 60);
@@ -149,7 +252,8 @@ __device__ __forceinline__ CatRoot<T> cat_solve_u(T e, T u0) {
   CatRoot<T> r;
   r.u = u;
   r.sh = sh - ch * du + d2 * (sh - ch * d3);
-  r.ch = ch - sh * du + d2 * (ch - sh * d3);
+  r.cm = cm - sh * du + d2 * (ch - sh * d3);
+  r.ch = r.cm + T(1);
   return r;
 }
 
@@ -161,14 +265,16 @@ __device__ __forceinline__ CatRoot<T> cat_solve_u(T e, T u0) {
 //   z_low = (zA+zB)/2 - (L/2) coth(u) + l/(2u)   if |dH| <= L tanh(u)  (vertex inside the span,
 //   equivalent to 0 <= l/2 - atanh(dH/L)/C <= l), else min(zA, zB).
 template <typename T> struct CatSpan {
-  T C;        // NaN when outside the domain
+  T C;        // NaN when outside the domain (NEED_C false: 0 inside the domain, NaN outside)
   T u;        // root (valid even if C is out of [c_lo,c_hi]); 0 when no root exists
   T sh, ch;
   bool inside;
+  CatWarm<T> warm;   // hand to the next solve of the same (slowly moving) span
 };
 
-template <typename T, typename M>
-__device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, T u_warm) {
+// NEED_C = false skips the division C = 2u/l: the domain test is done on 2u against c*l.
+template <typename T, typename M, bool NEED_C = true>
+__device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, const CatWarm<T>& warm) {
   CatSpan<T> s;
   const T s2 = (L - dH) * (L + dH);
   const T sq = M::sqrt_(M::max_(s2, T(0)));
@@ -179,16 +285,38 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, T
     s.sh = T(0);
     s.ch = T(1);
     s.inside = false;
+    s.warm.u = T(0);
+    s.warm.sh = T(0);
+    s.warm.cm = T(0);
+    s.warm.e = T(0);
     return s;
   }
-  const CatRoot<T> r = cat_solve_u<T, M>(e, u_warm);
-  const T C = M::div_(T(2) * r.u, l);
+  const CatRoot<T> r = cat_solve_u<T, M>(e, warm);
   s.u = r.u;
   s.sh = r.sh;
   s.ch = r.ch;
-  s.C = (C > c_lo && C < c_hi) ? C : M::nan_();
+  s.warm.u = r.u;
+  s.warm.sh = r.sh;
+  s.warm.cm = r.cm;
+  s.warm.e = e;
+  if constexpr (NEED_C) {
+    const T C = M::div_(T(2) * r.u, l);
+    s.C = (C > c_lo && C < c_hi) ? C : M::nan_();
+  } else {
+    const T tu = T(2) * r.u;
+    s.C = (tu > c_lo * l && tu < c_hi * l) ? T(0) : M::nan_();
+  }
   s.inside = M::abs_(dH) * r.ch <= L * r.sh;
   return s;
+}
+
+template <typename T> __device__ __forceinline__ CatWarm<T> cat_cold() {
+  CatWarm<T> w;
+  w.u = T(0);
+  w.sh = T(0);
+  w.cm = T(0);
+  w.e = T(0);
+  return w;
 }
 
 // lowest z of the span (world frame), SURVEY.md 8a "per-step catenary terms"

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -30,6 +31,7 @@ struct CatCtx {
   void* slot[N_SLOTS];
   size_t cap[N_SLOTS];
   int sm_count;
+  int mpc_block;   // 0 = heuristic; else forced block size (CAT_MPC_BLOCK_SIZE env, tuning only)
 };
 
 int fail(CatCtx* c, int code, const char* what, cudaError_t e = cudaSuccess) {
@@ -297,6 +299,9 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.w_sag = T(p->w_sag);
   q.w_ang = T(p->w_ang);
   q.rhoL = T(p->rho * p->L);
+  q.rhoL2 = q.rhoL > T(0) ? q.rhoL * q.rhoL : T(-1);   // a non-positive threshold is always 'active'
+  q.carry_t = (CAT_EQ_TABLE[q.eq_theta].live_mask & 0xC000u) == 0;
+  q.carry_g = (CAT_EQ_TABLE[q.eq_gamma].live_mask & 0xC000u) == 0;
   q.z_thr = T(p->z_floor + p->margin);
   q.c_lo = T(p->c_lo);
   q.c_hi = T(p->c_hi);
@@ -315,7 +320,11 @@ int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems
   if (rc) return rc;
   const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
   NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
-  const dim3 grid(nblk(q.K, CAT_MPC_BLOCK), (unsigned)q.n_problems, 1);
+  // under ~1 wave of 128-thread blocks the tail decides: 64-thread blocks spread candidates evenly over
+  // the 148 SMs (config 3: 1024 blocks = 6.9 per SM instead of 512 = 3.5 per SM)
+  int block = c->mpc_block;
+  if (block == 0) block = ((long long)q.K * q.n_problems <= (long long)c->sm_count * 1024) ? 64 : 128;
+  const dim3 grid(nblk(q.K, block), (unsigned)q.n_problems, 1);
   CatBest* bb;
   unsigned int* tk;
   {
@@ -329,10 +338,10 @@ int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems
   }
   const bool shipped = (q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED);
   if (shipped)
-    k_mpc_rollout<T, false><<<grid, CAT_MPC_BLOCK, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
+    k_mpc_rollout<T, false><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
                                                                    best_cost, best_idx);
   else
-    k_mpc_rollout<T, true><<<grid, CAT_MPC_BLOCK, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
+    k_mpc_rollout<T, true><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
                                                                   best_cost, best_idx);
   LAUNCHED();
   return CAT_OK;
@@ -397,6 +406,11 @@ int cat_init(int device, void** ctx) {
   if (!c) return CAT_ENOMEM;
   c->device = device;
   c->launches = 0;
+  c->mpc_block = 0;
+  if (const char* e = std::getenv("CAT_MPC_BLOCK_SIZE")) {
+    const int v = std::atoi(e);
+    if (v == 32 || v == 64 || v == 128) c->mpc_block = v;
+  }
   std::memset(c->slot, 0, sizeof(c->slot));
   std::memset(c->cap, 0, sizeof(c->cap));
   bool ok = cudaSetDevice(device) == cudaSuccess;
