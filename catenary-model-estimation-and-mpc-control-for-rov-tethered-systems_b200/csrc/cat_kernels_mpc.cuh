@@ -88,6 +88,42 @@ __device__ __forceinline__ CatBest cat_block_argmin(double cost, long long idx) 
   return b;
 }
 
+// grid-wide argmin of one problem: block fold -> one slot per block -> the last block (atomic ticket)
+// folds the slots, writes the winner and resets the ticket (re-entrant, graph-replayable).
+__device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int prob, CatBest* __restrict__ block_best,
+                                                unsigned int* __restrict__ tickets, double* __restrict__ best_cost,
+                                                long long* __restrict__ best_idx) {
+  const CatBest b = cat_block_argmin(jc, ji);
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) {
+    block_best[(long long)prob * gridDim.x + blockIdx.x] = b;
+    __threadfence();
+    const unsigned int t = atomicAdd(&tickets[prob], 1u);
+    s_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double bc = __longlong_as_double(0x7ff0000000000000LL);
+  long long bi = 0x7fffffffffffffffLL;
+  const volatile CatBest* slots = block_best + (long long)prob * gridDim.x;
+  for (unsigned int s = threadIdx.x; s < gridDim.x; s += blockDim.x) {
+    const double oc = slots[s].cost;
+    const long long oi = slots[s].idx;
+    if (cat_better(oc, oi, bc, bi)) {
+      bc = oc;
+      bi = oi;
+    }
+  }
+  __syncthreads();   // s_cost/s_idx of cat_block_argmin are reused
+  const CatBest r = cat_block_argmin(bc, bi);
+  if (threadIdx.x == 0) {
+    best_cost[prob] = r.cost;
+    best_idx[prob] = r.idx;
+    tickets[prob] = 0u;   // ready for the next launch / graph replay
+  }
+}
+
 template <typename T, bool GENERIC>
 __global__ void __launch_bounds__(CAT_MPC_BLOCK)
 k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, const T* __restrict__ controls,
@@ -211,35 +247,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   // ---- argmin over the candidates of this problem ----
   const double jc = live ? (double)J : __longlong_as_double(0x7ff0000000000000LL);
   const long long ji = live ? (q.k_offset + k) : 0x7fffffffffffffffLL;
-  const CatBest b = cat_block_argmin(jc, ji);
-  __shared__ bool s_last;
-  if (threadIdx.x == 0) {
-    block_best[(long long)prob * gridDim.x + blockIdx.x] = b;
-    __threadfence();
-    const unsigned int t = atomicAdd(&tickets[prob], 1u);
-    s_last = (t == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  double bc = __longlong_as_double(0x7ff0000000000000LL);
-  long long bi = 0x7fffffffffffffffLL;
-  const volatile CatBest* slots = block_best + (long long)prob * gridDim.x;
-  for (unsigned int s = threadIdx.x; s < gridDim.x; s += blockDim.x) {
-    const double oc = slots[s].cost;
-    const long long oi = slots[s].idx;
-    if (cat_better(oc, oi, bc, bi)) {
-      bc = oc;
-      bi = oi;
-    }
-  }
-  __syncthreads();   // s_cost/s_idx of cat_block_argmin are reused
-  const CatBest r = cat_block_argmin(bc, bi);
-  if (threadIdx.x == 0) {
-    best_cost[prob] = r.cost;
-    best_idx[prob] = r.idx;
-    tickets[prob] = 0u;   // ready for the next launch / graph replay
-  }
+  cat_grid_argmin(jc, ji, prob, block_best, tickets, best_cost, best_idx);
 }
 
 // materialise the on-device RNG controls: out[p][h][a][k] (SoA over candidates)

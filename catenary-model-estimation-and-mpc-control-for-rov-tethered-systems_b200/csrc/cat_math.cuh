@@ -109,6 +109,16 @@ template <> struct CatMath<double> {
   static __device__ __forceinline__ double abs_(double x) { return fabs(x); }
   static __device__ __forceinline__ double rcp_(double x) { return 1.0 / x; }
   static __device__ __forceinline__ double div_(double a, double b) { return a / b; }
+  // 1/x for normal positive x to ~1 ulp without the IEEE fix-up path: MUFU.RCP64H seed (20 bits) + two
+  // Newton refinements.  Used where the quotient is a correction or feeds a 1e-9 comparison.
+  static __device__ __forceinline__ double rcp_fast_(double x) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-x, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    return fma(y, e, y);
+  }
   static __device__ __forceinline__ double min_(double a, double b) { return fmin(a, b); }
   static __device__ __forceinline__ double max_(double a, double b) { return fmax(a, b); }
   static __device__ __forceinline__ double fma_(double a, double b, double c) { return fma(a, b, c); }
@@ -140,6 +150,7 @@ template <> struct CatMath<float> {
   static __device__ __forceinline__ float abs_(float x) { return fabsf(x); }
   static __device__ __forceinline__ float rcp_(float x) { return __frcp_rn(x); }
   static __device__ __forceinline__ float div_(float a, float b) { return __fdividef(a, b); }
+  static __device__ __forceinline__ float rcp_fast_(float x) { return __frcp_rn(x); }
   static __device__ __forceinline__ float min_(float a, float b) { return fminf(a, b); }
   static __device__ __forceinline__ float max_(float a, float b) { return fmaxf(a, b); }
   static __device__ __forceinline__ float fma_(float a, float b, float c) { return fmaf(a, b, c); }
@@ -165,10 +176,10 @@ template <typename T> struct CatRoot {
   T u, sh, ch, cm;   // u = C l / 2, sinh(u), cosh(u), cosh(u) - 1
 };
 
-// warm start carried from the previous solve of a slowly moving span: the old root with its
-// sinh / cosh-1 and the e it solved.  u == 0 means "none" (cold start).
+// warm start carried from the previous solve of a slowly moving span: the old root with
+// sinh(u)-u, cosh(u)-1, sinh(u) there.  u == 0 means "none" (cold start).
 template <typename T> struct CatWarm {
-  T u, sh, cm, e;
+  T u, sm, cm, sh;
 };
 
 // sinh(u)-u, cosh(u)-1, sinh(u) for u > 0.
@@ -208,52 +219,58 @@ __device__ __forceinline__ T cat_u_guess(T e) {
   return lr + M::log_(lr + M::log_(M::max_(lr, T(1))));
 }
 
-// one safeguarded Halley step of g(u) = sm - e u  (g' = cm - e, g'' = sh)
+// One safeguarded Halley step for the root of  G(u) = D (sinh u - u) - N u,  N = L^2 - dH^2 - l^2,
+// D = l (sqrt(L^2 - dH^2) + l):  the same root as g(u) = (sinh u - u) - e u with e = N / D, without
+// forming the quotient.  G' = D (cosh u - 1) - N, G'' = D sinh u.  The quotient of the step uses the
+// fast reciprocal: an error of 1e-15 relative in a step that is itself a correction is invisible.
 template <typename T, typename M>
-__device__ __forceinline__ T cat_halley_step(T u, T g, T gp, T sh) {
+__device__ __forceinline__ T cat_halley_step(T u, T N, T D, T sm, T cm, T sh) {
+  const T G = D * sm - N * u;
+  const T Gp = D * cm - N;
+  const T den = T(2) * Gp * Gp - G * (D * sh);
   T du;
-  const T den = T(2) * gp * gp - g * sh;
-  if (gp > T(0) && den > T(0)) {
-    du = M::div_(T(2) * g * gp, den);          // Halley
-  } else if (gp > T(0)) {
-    du = M::div_(g, gp);                       // Newton
+  if (Gp > T(0) && den > T(0)) {
+    du = T(2) * G * Gp * M::rcp_fast_(den);    // Halley
+  } else if (Gp > T(0)) {
+    du = G * M::rcp_fast_(Gp);                 // Newton
   } else {
-    du = -(T(0.5) * u + T(0.1));               // left of the minimum of g: move right
+    du = -(T(0.5) * u + T(0.1));               // left of the minimum of G: move right
   }
-  if (du >= u) du = T(0.5) * u;                // keep u > 0
+  if (!(du < u)) du = T(0.5) * u;              // keep u > 0
   return du;
 }
 
-// e = r - 1 > 0 required.  With a warm start the first Halley step costs no transcendental: at the
-// old root sm(u0) = e0 u0, so g(u0) for the new e is (e0 - e) u0 and g', g'' come from the carried
-// cosh-1 and sinh.  A rollout step moves the span by ~1e-3 relative, so that step lands within
-// ~1e-9 of the root and ONE full iteration finishes (the loop still runs until |du| is below tol).
+// N > 0, D > 0 required.  With a warm start the first Halley step costs no transcendental (the carried
+// sinh/cosh are exact at the old root).  A rollout step moves the span by ~1e-3 relative, so that
+// step lands within ~1e-9 of the root and ONE full iteration finishes; the loop still runs until
+// |du| is below tol.  Returns the root with sinh-u, cosh-1, sinh Taylor-corrected to it.
 template <typename T, typename M>
-__device__ __forceinline__ CatRoot<T> cat_solve_u(T e, const CatWarm<T>& w) {
+__device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w) {
   T u;
   if (w.u > T(0)) {
-    u = w.u - cat_halley_step<T, M>(w.u, (w.e - e) * w.u, w.cm - e, w.sh);
+    u = w.u - cat_halley_step<T, M>(w.u, N, D, w.sm, w.cm, w.sh);
   } else {
-    u = cat_u_guess<T, M>(e);
+    u = cat_u_guess<T, M>(M::div_(N, D));
   }
   T sm, cm, sh, du;
   int it = 0;
   bool more;
   do {
     cat_hyp<T, M>(u, sm, cm, sh);
-    du = cat_halley_step<T, M>(u, sm - e * u, cm - e, sh);
+    du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
     u -= du;
     more = M::abs_(du) > M::step_tol() * M::min_(u, T(1));
   } while (more && ++it < 60);
-  // sinh/cosh at the updated u from the values at u+du (|du| <= 1e-5: 4th-order remainder)
+  // values at the updated u from those at u+du (|du| <= 1e-5: 4th-order remainder).
+  // d/du: sm' = cm, cm' = sh, sh' = ch
   const T ch = cm + T(1);
-  const T d2 = du * du * T(0.5);
-  const T d3 = du * T(1.0 / 3.0);
-  CatRoot<T> r;
+  const T h2 = du * du * T(0.5);
+  const T h3 = du * T(1.0 / 3.0);
+  CatWarm<T> r;
   r.u = u;
-  r.sh = sh - ch * du + d2 * (sh - ch * d3);
-  r.cm = cm - sh * du + d2 * (ch - sh * d3);
-  r.ch = r.cm + T(1);
+  r.sm = sm - cm * du + h2 * (sh - ch * h3);
+  r.cm = cm - sh * du + h2 * (ch - sh * h3);
+  r.sh = sh - ch * du + h2 * (sh - ch * h3);
   return r;
 }
 
@@ -272,33 +289,37 @@ template <typename T> struct CatSpan {
   CatWarm<T> warm;   // hand to the next solve of the same (slowly moving) span
 };
 
+template <typename T> __device__ __forceinline__ CatWarm<T> cat_cold() {
+  CatWarm<T> w;
+  w.u = T(0);
+  w.sm = T(0);
+  w.cm = T(0);
+  w.sh = T(0);
+  return w;
+}
+
 // NEED_C = false skips the division C = 2u/l: the domain test is done on 2u against c*l.
 template <typename T, typename M, bool NEED_C = true>
 __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, const CatWarm<T>& warm) {
   CatSpan<T> s;
   const T s2 = (L - dH) * (L + dH);
   const T sq = M::sqrt_(M::max_(s2, T(0)));
-  const T e = M::div_(s2 - l * l, l * (sq + l));
-  if (!(s2 > T(0)) || !(e > T(0)) || !(l > T(0))) {
+  const T N = s2 - l * l;
+  const T D = l * (sq + l);
+  if (!(s2 > T(0)) || !(N > T(0)) || !(l > T(0))) {
     s.C = M::nan_();
     s.u = T(0);
     s.sh = T(0);
     s.ch = T(1);
     s.inside = false;
-    s.warm.u = T(0);
-    s.warm.sh = T(0);
-    s.warm.cm = T(0);
-    s.warm.e = T(0);
+    s.warm = cat_cold<T>();
     return s;
   }
-  const CatRoot<T> r = cat_solve_u<T, M>(e, warm);
+  const CatWarm<T> r = cat_solve_u<T, M>(N, D, warm);
   s.u = r.u;
   s.sh = r.sh;
-  s.ch = r.ch;
-  s.warm.u = r.u;
-  s.warm.sh = r.sh;
-  s.warm.cm = r.cm;
-  s.warm.e = e;
+  s.ch = r.cm + T(1);
+  s.warm = r;
   if constexpr (NEED_C) {
     const T C = M::div_(T(2) * r.u, l);
     s.C = (C > c_lo && C < c_hi) ? C : M::nan_();
@@ -306,17 +327,8 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, c
     const T tu = T(2) * r.u;
     s.C = (tu > c_lo * l && tu < c_hi * l) ? T(0) : M::nan_();
   }
-  s.inside = M::abs_(dH) * r.ch <= L * r.sh;
+  s.inside = M::abs_(dH) * s.ch <= L * r.sh;
   return s;
-}
-
-template <typename T> __device__ __forceinline__ CatWarm<T> cat_cold() {
-  CatWarm<T> w;
-  w.u = T(0);
-  w.sh = T(0);
-  w.cm = T(0);
-  w.e = T(0);
-  return w;
 }
 
 // lowest z of the span (world frame), SURVEY.md 8a "per-step catenary terms"
@@ -325,7 +337,7 @@ __device__ __forceinline__ T cat_z_low(const CatSpan<T>& s, T l, T L, T zA, T zB
   const T zmin = M::min_(zA, zB);
   if (!(s.C == s.C) || !s.inside) return zmin;
   // (zA+zB)/2 + (l sh - L ch u) / (2 sh u)
-  return T(0.5) * (zA + zB) + M::div_(l * s.sh - L * s.ch * s.u, T(2) * s.sh * s.u);
+  return T(0.5) * (zA + zB) + (l * s.sh - L * s.ch * s.u) * M::rcp_fast_(T(2) * s.sh * s.u);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -320,10 +320,11 @@ int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems
   if (rc) return rc;
   const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
   NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
-  // under ~1 wave of 128-thread blocks the tail decides: 64-thread blocks spread candidates evenly over
-  // the 148 SMs (config 3: 1024 blocks = 6.9 per SM instead of 512 = 3.5 per SM)
+  // Launch shape: one thread per candidate.  (A role-split variant -- dynamics and catenary chains of a
+  // candidate in two threads -- was measured in round 1 and was 13% SLOWER at config 3: the kernel is bound by
+  // issue slots, not by the dependency chain, and the split duplicates loads and kinematics.  DESIGN.md 9.)
   int block = c->mpc_block;
-  if (block == 0) block = ((long long)q.K * q.n_problems <= (long long)c->sm_count * 1024) ? 64 : 128;
+  if (block == 0) block = 128;
   const dim3 grid(nblk(q.K, block), (unsigned)q.n_problems, 1);
   CatBest* bb;
   unsigned int* tk;
@@ -338,11 +339,11 @@ int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems
   }
   const bool shipped = (q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED);
   if (shipped)
-    k_mpc_rollout<T, false><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
-                                                                   best_cost, best_idx);
+    k_mpc_rollout<T, false><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk, best_cost,
+                                                           best_idx);
   else
-    k_mpc_rollout<T, true><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
-                                                                  best_cost, best_idx);
+    k_mpc_rollout<T, true><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk, best_cost,
+                                                          best_idx);
   LAUNCHED();
   return CAT_OK;
 }
