@@ -157,6 +157,89 @@ def emit(node):
     raise ParseError(k)
 
 
+_VEC_FUNCS = {"sin"}     # functions with an interleaved N-wide implementation in CatMath (sin_v)
+
+
+def _has_call(node):
+    k = node[0]
+    if k == "call":
+        return True
+    if k in ("neg", "pow"):
+        return _has_call(node[1])
+    if k == "bin":
+        return _has_call(node[2]) or _has_call(node[3])
+    return False
+
+
+def _leaf_vec_calls(node, acc):
+    """Calls of a vectorised function whose argument contains no further call, in evaluation order."""
+    k = node[0]
+    if k == "call":
+        if node[1] in _VEC_FUNCS and not _has_call(node[2]):
+            acc.append(node)
+        else:
+            _leaf_vec_calls(node[2], acc)
+    elif k in ("neg", "pow"):
+        _leaf_vec_calls(node[1], acc)
+    elif k == "bin":
+        _leaf_vec_calls(node[2], acc)
+        _leaf_vec_calls(node[3], acc)
+    return acc
+
+
+def emit_vec(node, stmts, counter, batched=None):
+    """Expression for row ``n`` of an N-row batch.  Transcendental calls are hoisted into statements that
+    evaluate all N rows at once (``M::template sin_v<..>``); the innermost calls of the whole expression go
+    into ONE batch of M*N arguments, so every polynomial coefficient is fetched once and the M*N Horner
+    chains interleave."""
+    if batched is None:
+        batched = {}
+        leaves = _leaf_vec_calls(node, [])
+        by_fn = {}
+        for lf in leaves:
+            by_fn.setdefault(lf[1], []).append(lf)
+        for fn, group in by_fn.items():
+            name = f"b{counter[0]}"
+            counter[0] += 1
+            m = len(group)
+            stmts.append(f"  T {name}[{m} * N];")
+            stmts.append("#pragma unroll")
+            stmts.append("  for (int n = 0; n < N; ++n) {")
+            for slot, lf in enumerate(group):
+                stmts.append(f"    {name}[{slot} * N + n] = {emit_vec(lf[2], stmts, counter, batched)};")
+                batched[id(lf)] = f"{name}[{slot} * N + n]"
+            stmts.append("  }")
+            stmts.append(f"  M::template {fn}_v<{m} * N>({name});")
+    k = node[0]
+    if k == "num":
+        return f"T({float(node[1])!r})"
+    if k == "var":
+        return f"x[n][{node[1]}]"
+    if k == "neg":
+        return f"(-{emit_vec(node[1], stmts, counter, batched)})"
+    if k == "bin":
+        return (f"({emit_vec(node[2], stmts, counter, batched)} {node[1]} "
+                f"{emit_vec(node[3], stmts, counter, batched)})")
+    if k == "pow":
+        return f"M::template ipow<{node[2]}>({emit_vec(node[1], stmts, counter, batched)})"
+    if k == "call":
+        if id(node) in batched:
+            return batched[id(node)]
+        arg = emit_vec(node[2], stmts, counter, batched)
+        name = f"t{counter[0]}"
+        counter[0] += 1
+        stmts.append(f"  T {name}[N];")
+        stmts.append("#pragma unroll")
+        stmts.append(f"  for (int n = 0; n < N; ++n) {name}[n] = {arg};")
+        if node[1] in _VEC_FUNCS:
+            stmts.append(f"  M::template {node[1]}_v<N>({name});")
+        else:
+            stmts.append("#pragma unroll")
+            stmts.append(f"  for (int n = 0; n < N; ++n) {name}[n] = M::{node[1]}_({name}[n]);")
+        return f"{name}[n]"
+    raise ParseError(k)
+
+
 def evaluate(node, x, mod):
     """Host-side evaluation of the AST (used only by codegen self-tests; ``mod`` = math or numpy)."""
     k = node[0]
@@ -226,6 +309,17 @@ def generate(model_json=MODEL_JSON, out_file=OUT_FILE):
                 "}",
                 "",
             ]
+            stmts, counter = [], [0]
+            expr = emit_vec(node, stmts, counter)
+            lines += [
+                "template <typename T, typename M, int N>",
+                f"__device__ __forceinline__ void {fn}_v(const T (&x)[N][CAT_N_FEATURES], T (&out)[N]) {{",
+                *stmts,
+                "#pragma unroll",
+                f"  for (int n = 0; n < N; ++n) out[n] = {expr};",
+                "}",
+                "",
+            ]
             table.append((eq_id, name, row["complexity"], _mask(live), fn))
             if row["complexity"] == entry["shipped_complexity"]:
                 shipped[name] = (eq_id, fn, _mask(live))
@@ -244,6 +338,14 @@ def generate(model_json=MODEL_JSON, out_file=OUT_FILE):
               "__device__ __forceinline__ T cat_dgamma_dt(const T (&x)[CAT_N_FEATURES]) { return "
               + shipped["dgamma_dt"][1] + "<T, M>(x); }",
               "",
+              "// N feature rows at once (the RK4 stages of one step): transcendental chains interleave",
+              "template <typename T, typename M, int N>",
+              "__device__ __forceinline__ void cat_dtheta_dt_v(const T (&x)[N][CAT_N_FEATURES], T (&out)[N]) { "
+              + shipped["dtheta_dt"][1] + "_v<T, M, N>(x, out); }",
+              "template <typename T, typename M, int N>",
+              "__device__ __forceinline__ void cat_dgamma_dt_v(const T (&x)[N][CAT_N_FEATURES], T (&out)[N]) { "
+              + shipped["dgamma_dt"][1] + "_v<T, M, N>(x, out); }",
+              "",
               "// any hall-of-fame row by id (open-loop RK4 / predict kernels)",
               "template <typename T, typename M>",
               "__device__ __forceinline__ T cat_eval_equation(int eq_id, const T (&x)[CAT_N_FEATURES]) {",
@@ -251,6 +353,12 @@ def generate(model_json=MODEL_JSON, out_file=OUT_FILE):
     for i, name, cx, mask, fn in table:
         lines.append(f"    case {i}: return {fn}<T, M>(x);")
     lines += ["    default: return T(0);", "  }", "}", "",
+              "template <typename T, typename M, int N>",
+              "__device__ __forceinline__ void cat_eval_equation_v(int eq_id, const T (&x)[N][CAT_N_FEATURES], T (&out)[N]) {",
+              "  switch (eq_id) {"]
+    for i, name, cx, mask, fn in table:
+        lines.append(f"    case {i}: {fn}_v<T, M, N>(x, out); break;")
+    lines += ["    default:", "#pragma unroll", "      for (int n = 0; n < N; ++n) out[n] = T(0);", "  }", "}", "",
               "struct CatEqInfo { int id; int is_gamma; int complexity; unsigned live_mask; };",
               "static const CatEqInfo CAT_EQ_TABLE[CAT_N_EQUATIONS] = {"]
     for i, name, cx, mask, fn in table:

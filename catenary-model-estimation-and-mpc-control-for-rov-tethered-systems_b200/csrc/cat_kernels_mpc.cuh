@@ -43,6 +43,19 @@ __device__ __forceinline__ void cat_eval_pair(const CatMpcDev<T>& q, const T (&x
   }
 }
 
+// both equations on N feature rows at once (the stage-2/3 and stage-4 rows of one RK4 step)
+template <typename T, bool GENERIC, int N>
+__device__ __forceinline__ void cat_eval_pair_v(const CatMpcDev<T>& q, const T (&x)[N][18], T (&ft)[N], T (&fg)[N]) {
+  typedef CatMath<T> M;
+  if constexpr (GENERIC) {
+    cat_eval_equation_v<T, M, N>(q.eq_theta, x, ft);
+    cat_eval_equation_v<T, M, N>(q.eq_gamma, x, fg);
+  } else {
+    cat_dtheta_dt_v<T, M, N>(x, ft);
+    cat_dgamma_dt_v<T, M, N>(x, fg);
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ void cat_scale18(T (&x)[18]) {
 #pragma unroll
@@ -167,15 +180,42 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     carry_g = (CAT_DGAMMA_LIVE_MASK & 0xC000u) == 0;
   }
 
+  // controls and the reference point of a step are fetched one step ahead, so the load latency hides
+  // behind the arithmetic of the current step (round-1 profile: 25% of the stall samples sat on the first
+  // use of the control loads)
+  T Vnext[3] = {T(0), T(0), T(0)};
+  T Rnext[3];
+  if (!rng) {
+    Vnext[0] = uc[0];
+    Vnext[1] = uc[q.sa];
+    Vnext[2] = uc[2 * q.sa];
+  }
+  Rnext[0] = T(pr[0]);
+  Rnext[1] = T(pr[1]);
+  Rnext[2] = T(pr[2]);
+
   for (int h = 0; h < q.H; ++h) {
     T Vn[3];
     if (rng) {
       cat_sample_control<T, M>(q.seed, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
                                (uint32_t)h, q.sigma, q.clip, Vn);
     } else {
-      Vn[0] = uc[h * q.sh];
-      Vn[1] = uc[h * q.sh + q.sa];
-      Vn[2] = uc[h * q.sh + 2 * q.sa];
+      Vn[0] = Vnext[0];
+      Vn[1] = Vnext[1];
+      Vn[2] = Vnext[2];
+    }
+    const T Rh[3] = {Rnext[0], Rnext[1], Rnext[2]};
+    if (h + 1 < q.H) {
+      if (!rng) {
+        uc += q.sh;
+        Vnext[0] = uc[0];
+        Vnext[1] = uc[q.sa];
+        Vnext[2] = uc[2 * q.sa];
+      }
+      pr += 3;
+      Rnext[0] = T(pr[0]);
+      Rnext[1] = T(pr[1]);
+      Rnext[2] = T(pr[2]);
     }
     T Pn[3], An[3];
 #pragma unroll
@@ -184,14 +224,15 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       An[a] = M::div_(Vn[a] - V[a], q.dt);
     }
     // ---- RK4 step of both angle ODEs (simulate_rk4_theta_gamma.py:61-66; k3 == k2) ----
-    T x1[18], xm[18];
-    cat_features18<T, M>(P0, Pn, Vn, An, th + q.dt * k1t, ga + q.dt * k1g, th, ga, x1);
-    cat_scale18<T>(x1);
+    // rows: [0] = midpoint features (stages 2 and 3), [1] = end-point features (stage 4)
+    T xs[2][18];
+    cat_features18<T, M>(P0, Pn, Vn, An, th + q.dt * k1t, ga + q.dt * k1g, th, ga, xs[1]);
+    cat_scale18<T>(xs[1]);
 #pragma unroll
-    for (int j = 0; j < 18; ++j) xm[j] = (x0[j] + x1[j]) * T(0.5);
-    T k2t, k2g, k4t, k4g;
-    cat_eval_pair<T, GENERIC>(q, xm, k2t, k2g);
-    cat_eval_pair<T, GENERIC>(q, x1, k4t, k4g);
+    for (int j = 0; j < 18; ++j) xs[0][j] = (x0[j] + xs[1][j]) * T(0.5);
+    T kt[2], kg[2];
+    cat_eval_pair_v<T, GENERIC, 2>(q, xs, kt, kg);
+    const T k2t = kt[0], k4t = kt[1], k2g = kg[0], k4g = kg[1];
     const T thn = th + q.dt6 * (k1t + T(2) * k2t + T(2) * k2t + k4t);
     const T gan = ga + q.dt6 * (k1g + T(2) * k2g + T(2) * k2g + k4g);
     // ---- catenary terms of the new pose (main_fun.py:423) ----
@@ -203,12 +244,13 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     warm = sp.warm;
     const T z_low = cat_z_low<T, M>(sp, l, q.L, P0[2], P0[2] + rz);
     // ---- cost, association as in the oracle ----
-    const T ex = Pn[0] - T(pr[3 * h]), ey = Pn[1] - T(pr[3 * h + 1]), ez = Pn[2] - T(pr[3 * h + 2]);
+    const T ex = Pn[0] - Rh[0], ey = Pn[1] - Rh[1], ez = Pn[2] - Rh[2];
     const T dvx = Vn[0] - V[0], dvy = Vn[1] - V[1], dvz = Vn[2] - V[2];
-    // max(0, d - rho L): the square root is only taken when the term is active (or d is NaN)
+    // max(0, d - rho L): the square root is only taken when the term is active (or d is NaN) in some lane
+    // of the warp -- a warp-uniform branch, so the inactive case issues nothing
     T over = T(0);
-    if (!(d2 <= q.rhoL2)) over = M::max_(T(0), M::sqrt_(d2) - q.rhoL);
-    const T deep = M::max_(T(0), q.z_thr - z_low);
+    if (__any_sync(0xffffffffu, !(d2 <= q.rhoL2))) over = M::pos_(M::sqrt_(d2) - q.rhoL);
+    const T deep = M::pos_(q.z_thr - z_low);
     T c = q.w_trk * (ex * ex + ey * ey + ez * ez);
     c = c + q.w_du * (dvx * dvx + dvy * dvy + dvz * dvz);
     c = c + q.w_len * (over * over);
@@ -228,7 +270,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     }
     // ---- stage-1 row and slopes of the next step ----
 #pragma unroll
-    for (int j = 0; j < 18; ++j) x0[j] = x1[j];
+    for (int j = 0; j < 18; ++j) x0[j] = xs[1][j];
     x0[14] = (th - CatScaler<T>::mean(14)) * CatScaler<T>::inv_scale(14);
     x0[15] = (ga - CatScaler<T>::mean(15)) * CatScaler<T>::inv_scale(15);
     if (carry_t && carry_g) {

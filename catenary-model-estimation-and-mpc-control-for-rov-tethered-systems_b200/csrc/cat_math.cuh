@@ -44,30 +44,73 @@ __constant__ double CAT_LN2_C[4] = {
     0.69314718055994528623,      // ln2 hi
     2.3190468138462995584e-17};  // ln2 lo
 
-// sin(x), |error| <~ 2 ulp for |x| < 1e5 (the scaled features live in |x| < 1e3); beyond that, and
-// for inf/nan, the CUDA routine.
-__device__ __forceinline__ double cat_sin_f64(double x) {
-  if (!(fabs(x) < 1.0e5)) return sin(x);
-  const double t = fma(x, CAT_PI_C[0], CAT_PI_C[1]);
-  const int q = __double2loint(t);
-  const double qf = t - CAT_PI_C[1];
-  double r = fma(-qf, CAT_PI_C[2], x);
-  r = fma(-qf, CAT_PI_C[3], r);
-  r = fma(-qf, CAT_PI_C[4], r);
-  const double z = r * r;
-  double p = CAT_SIN_C[9];
+// sin of N independent arguments at once, |error| <~ 2 ulp for |x| < 1e5 (the scaled features live in
+// |x| < 1e3); beyond that, and for inf/nan, ONE cold branch per batch to the CUDA routine.  The N Horner
+// chains are interleaved, so each coefficient is fetched once per batch and the DFMA latency of one chain
+// hides behind the others.
+template <int N>
+__device__ __forceinline__ void cat_sin_vec_f64(double (&a)[N]) {
+  double r[N], z[N], p[N];
+  int q[N];
+  bool bad = false;
 #pragma unroll
-  for (int i = 8; i >= 0; --i) p = fma(p, z, CAT_SIN_C[i]);
-  const double v = fma(r * z, p, r);
-  // sin(x) = (-1)^q sin(r)
-  return __hiloint2double(__double2hiint(v) ^ (q << 31), __double2loint(v));
+  for (int n = 0; n < N; ++n) {
+    const double t = fma(a[n], CAT_PI_C[0], CAT_PI_C[1]);
+    q[n] = __double2loint(t);
+    const double qf = t - CAT_PI_C[1];
+    double rr = fma(-qf, CAT_PI_C[2], a[n]);
+    rr = fma(-qf, CAT_PI_C[3], rr);
+    r[n] = fma(-qf, CAT_PI_C[4], rr);
+    z[n] = r[n] * r[n];
+    p[n] = CAT_SIN_C[9];
+    bad = bad || !(fabs(a[n]) < 1.0e5);
+  }
+#pragma unroll
+  for (int i = 8; i >= 0; --i) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) p[n] = fma(p[n], z[n], CAT_SIN_C[i]);
+  }
+#pragma unroll
+  for (int n = 0; n < N; ++n) {
+    const double v = fma(r[n] * z[n], p[n], r[n]);
+    // sin(x) = (-1)^q sin(r)
+    r[n] = __hiloint2double(__double2hiint(v) ^ (q[n] << 31), __double2loint(v));
+  }
+  if (bad) {
+#pragma unroll
+    for (int n = 0; n < N; ++n)
+      if (!(fabs(a[n]) < 1.0e5)) r[n] = sin(a[n]);
+  }
+#pragma unroll
+  for (int n = 0; n < N; ++n) a[n] = r[n];
+}
+
+__device__ __forceinline__ double cat_sin_f64(double x) {
+  double a[1] = {x};
+  cat_sin_vec_f64<1>(a);
+  return a[0];
+}
+
+// sqrt(x) for x >= 0 without the IEEE special-case path: MUFU.RSQ64H seed + two coupled Newton steps
+// (~1 ulp).  x == 0 (and denormal x, flushed by the seed) returns 0; NaN / negative propagate NaN.
+__device__ __forceinline__ double cat_sqrt_f64(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double g = x * y;            // ~ sqrt(x)
+  double h = 0.5 * y;          // ~ 1 / (2 sqrt(x))
+  double e = fma(-g, h, 0.5);
+  g = fma(g, e, g);
+  h = fma(h, e, h);
+  e = fma(-g, g, x);           // residual x - g^2
+  g = fma(e, h, g);
+  return (x > 2.3e-308 && x < 1.0e300) ? g : ((x == 0.0) ? 0.0 : sqrt(x));
 }
 
 // For u >= 0: sh = sinh u, cm = cosh u - 1, sm = sinh u - u, all without cancellation at small u and
 // without a division: u = k ln2 + r, |r| <= ln2/2;  sinh/cosh(k ln2) are exact combinations of
 // 2^k, 2^-k;  addition theorems.  For k = 0 this IS the series (A = 0, B = 1).
 __device__ __forceinline__ void cat_hyp_f64(double u, double& sm, double& cm, double& sh) {
-  u = fmin(u, 700.0);
+  u = (u < 700.0) ? u : 700.0;
   const double t = fma(u, CAT_LN2_C[0], CAT_LN2_C[1]);
   const int k = __double2loint(t);
   const double kf = t - CAT_LN2_C[1];
@@ -101,11 +144,13 @@ template <> struct CatMath<double> {
   typedef double real;
   static __device__ __forceinline__ double sin_(double x) { return cat_sin_f64(x); }
   static __device__ __forceinline__ double cos_(double x) { return cos(x); }
+  template <int N> static __device__ __forceinline__ void sin_v(double (&a)[N]) { cat_sin_vec_f64<N>(a); }
+  static __device__ __forceinline__ double pos_(double x) { return x > 0.0 ? x : 0.0; }   // max(0, x), NaN -> 0
   static __device__ __forceinline__ void sincos_(double x, double* s, double* c) { sincos(x, s, c); }
   static __device__ __forceinline__ double tanh_(double x) { return tanh(x); }
   static __device__ __forceinline__ double exp_(double x) { return exp(x); }
   static __device__ __forceinline__ double log_(double x) { return log(x); }
-  static __device__ __forceinline__ double sqrt_(double x) { return sqrt(x); }
+  static __device__ __forceinline__ double sqrt_(double x) { return cat_sqrt_f64(x); }
   static __device__ __forceinline__ double abs_(double x) { return fabs(x); }
   static __device__ __forceinline__ double rcp_(double x) { return 1.0 / x; }
   static __device__ __forceinline__ double div_(double a, double b) { return a / b; }
@@ -138,6 +183,11 @@ template <> struct CatMath<float> {
   typedef float real;
   static __device__ __forceinline__ float sin_(float x) { return __sinf(x); }
   static __device__ __forceinline__ float cos_(float x) { return __cosf(x); }
+  template <int N> static __device__ __forceinline__ void sin_v(float (&a)[N]) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) a[n] = __sinf(a[n]);
+  }
+  static __device__ __forceinline__ float pos_(float x) { return x > 0.0f ? x : 0.0f; }
   static __device__ __forceinline__ void sincos_(float x, float* s, float* c) { __sincosf(x, s, c); }
   static __device__ __forceinline__ float tanh_(float x) {
     float r;
@@ -259,7 +309,7 @@ __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w)
     cat_hyp<T, M>(u, sm, cm, sh);
     du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
     u -= du;
-    more = M::abs_(du) > M::step_tol() * M::min_(u, T(1));
+    more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1));
   } while (more && ++it < 60);
   // values at the updated u from those at u+du (|du| <= 1e-5: 4th-order remainder).
   // d/du: sm' = cm, cm' = sh, sh' = ch
@@ -303,7 +353,7 @@ template <typename T, typename M, bool NEED_C = true>
 __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, const CatWarm<T>& warm) {
   CatSpan<T> s;
   const T s2 = (L - dH) * (L + dH);
-  const T sq = M::sqrt_(M::max_(s2, T(0)));
+  const T sq = M::sqrt_(M::pos_(s2));
   const T N = s2 - l * l;
   const T D = l * (sq + l);
   if (!(s2 > T(0)) || !(N > T(0)) || !(l > T(0))) {
