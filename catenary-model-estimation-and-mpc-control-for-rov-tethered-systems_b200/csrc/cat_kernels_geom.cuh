@@ -22,81 +22,84 @@ __global__ void __launch_bounds__(256) k_solve_param(long long n, const T* __res
 // Curve shapes: Catenary.__call__ (pympc; builder-defined sampling, see oracle.catenary_points)
 // fused with transform_catenary (main_fun.py:38-111).
 //
-// Block = CAT_SHAPE_TILE configurations.  Phase 1: thread t solves configuration t of the tile
-// (both spans A->B and A->B') and parks the per-span constants in shared memory.  Phase 2: the
-// block walks the tile's n_pts*TILE points with the point index fastest, so a warp writes 32
-// consecutive (x,y,z) triples = 768 contiguous bytes of the AoS (n, n_pts, 3) output.
+// Block = CAT_SHAPE_TILE configurations.
+// Phase 1: thread t solves configuration t of the tile (span A->B and, for the rotated outputs, the
+//   span A->B' of main_fun.py:92-93) and parks in shared memory, per span, the constants of the sag
+//   profile and, per requested output, an affine map: every curve lies in the vertical plane through
+//   its chord, so a sample is  A + s a + zoff(s) b  with  a = R (rel_x, rel_y, 0),  b = R e_z  and R the
+//   composition of the Rodrigues rotations of main_fun.py:96-99,106-109 (identity for the first two
+//   outputs).  The two per-point rotations of the reference collapse into 6 FMAs per point.
+// Phase 2: one warp per configuration, lanes over points.  zoff(s) = (cosh(2u s - v_low) - cosh v_low)/C
+//   is evaluated with the polynomial sinh/cosh once per lane and advanced by 32 samples with the
+//   addition theorem (4 FMAs), so a 100-point curve costs 32 transcendental evaluations, not 100.
+//   A warp writes 32 consecutive (x,y,z) triples = 768 contiguous bytes of the AoS (n, n_pts, 3) output.
 // ------------------------------------------------------------------------------------------
 #define CAT_SHAPE_TILE 128
+#define CAT_SHAPE_RESEED 8     // re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
 
 template <typename T> struct CatShapeSpan {
-  T rel[3];     // B - A
-  T l;          // horizontal span
   T two_u;      // C * l
   T v_low;      // C * x_low = u - atanh(dH/L)
   T inv_C;      // 1/C
-  T ch_low;     // cosh(v_low)
-  T Bend[3];    // exact end point (chord fallback pins it)
+  T cm_low;     // cosh(v_low) - 1
+  T cmD, shD;   // cosh(D) - 1, sinh(D) for the 32-sample hop D = 2u * 32/(n_pts-1)
   int valid;
+};
+
+template <typename T> struct CatShapeMap {
+  T a[3], b[3];   // sample = A + s a + zoff b
 };
 
 template <typename T> struct CatShapeCfg {
   T A[3];
   CatShapeSpan<T> sp[2];
-  T k_theta[3], k_gamma[3];
-  T ct, st, cg, sg;
+  CatShapeMap<T> map[4];   // original, theta_rotated, theta_aligned, final
 };
 
 template <typename T, typename M>
-__device__ __forceinline__ void cat_shape_span_setup(const T A[3], const T Bq[3], T L, T c_lo, T c_hi,
-                                                     CatShapeSpan<T>& sp, T* C_out) {
-  sp.rel[0] = Bq[0] - A[0];
-  sp.rel[1] = Bq[1] - A[1];
-  sp.rel[2] = Bq[2] - A[2];
-  sp.Bend[0] = Bq[0];
-  sp.Bend[1] = Bq[1];
-  sp.Bend[2] = Bq[2];
-  const T l = M::sqrt_(sp.rel[0] * sp.rel[0] + sp.rel[1] * sp.rel[1]);
-  const T dH = sp.rel[2];
+__device__ __forceinline__ void cat_shape_span_setup(const T rel[3], T L, T c_lo, T c_hi, T hop, CatShapeSpan<T>& sp,
+                                                     T* C_out) {
+  const T l = M::sqrt_(rel[0] * rel[0] + rel[1] * rel[1]);
+  const T dH = rel[2];
   const CatSpan<T> s = cat_span<T, M>(l, dH, L, c_lo, c_hi, cat_cold<T>());
-  sp.l = l;
   sp.valid = (s.C == s.C) ? 1 : 0;
   if (C_out) *C_out = s.C;
   if (sp.valid) {
     sp.two_u = T(2) * s.u;
     sp.v_low = s.u - T(0.5) * M::log_(M::div_(L + dH, L - dH));
     sp.inv_C = M::rcp_(s.C);
-    const T E = M::exp_(sp.v_low);
-    sp.ch_low = T(0.5) * (E + M::rcp_(E));
+    T sm, sh;
+    cat_hyp<T, M>(M::abs_(sp.v_low), sm, sp.cm_low, sh);
+    cat_hyp<T, M>(sp.two_u * hop, sm, sp.cmD, sp.shD);
   } else {
     sp.two_u = T(0);
     sp.v_low = T(0);
     sp.inv_C = T(0);
-    sp.ch_low = T(1);
+    sp.cm_low = T(0);
+    sp.cmD = T(0);
+    sp.shD = T(0);
   }
 }
 
-template <typename T, typename M>
-__device__ __forceinline__ void cat_shape_point(const T A[3], const CatShapeSpan<T>& sp, T s, bool last, T p[3]) {
-  if (s == T(0)) {          // the curve starts exactly at A (cosh is even: the oracle's z_0 - zA is exactly 0)
-    p[0] = A[0];
-    p[1] = A[1];
-    p[2] = A[2];
-  } else if (sp.valid) {
-    p[0] = A[0] + sp.rel[0] * s;
-    p[1] = A[1] + sp.rel[1] * s;
-    const T t = sp.two_u * s - sp.v_low;
-    const T E = M::exp_(t);
-    const T ch = T(0.5) * (E + M::rcp_(E));
-    p[2] = A[2] + (ch - sp.ch_low) * sp.inv_C;
-  } else if (last) {
-    p[0] = sp.Bend[0];
-    p[1] = sp.Bend[1];
-    p[2] = sp.Bend[2];
-  } else {
-    p[0] = A[0] + sp.rel[0] * s;
-    p[1] = A[1] + sp.rel[1] * s;
-    p[2] = A[2] + sp.rel[2] * s;
+// R = c I + s [k]x + (1-c) k k^T applied to v (k unit), main_fun.py:31-35
+template <typename T>
+__device__ __forceinline__ void cat_rot_apply(const T k[3], T c, T s, const T v[3], T out[3]) {
+  const T cx = k[1] * v[2] - k[2] * v[1];
+  const T cy = k[2] * v[0] - k[0] * v[2];
+  const T cz = k[0] * v[1] - k[1] * v[0];
+  const T dot = k[0] * v[0] + k[1] * v[1] + k[2] * v[2];
+  const T omc = T(1) - c;
+  out[0] = v[0] * c + cx * s + k[0] * dot * omc;
+  out[1] = v[1] * c + cy * s + k[1] * dot * omc;
+  out[2] = v[2] * c + cz * s + k[2] * dot * omc;
+}
+
+template <typename T>
+__device__ __forceinline__ void cat_shape_map_set(CatShapeMap<T>& m, const T a[3], const T b[3]) {
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    m.a[j] = a[j];
+    m.b[j] = b[j];
   }
 }
 
@@ -113,6 +116,8 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE) k_shape(long long n, const T* 
   const int tid = threadIdx.x;
   const long long i = base + tid;
   const bool need_rot = (which & (CAT_OUT_THETA_ROTATED | CAT_OUT_THETA_ALIGNED | CAT_OUT_FINAL)) != 0;
+  const T inv_nm1 = (n_pts > 1) ? M::div_(T(1), T(n_pts - 1)) : T(0);
+  const T hop = T(32) * inv_nm1;
   if (i < n) {
     CatShapeCfg<T>& c = cfg[tid];
     const T a[3] = {A[3 * i], A[3 * i + 1], A[3 * i + 2]};
@@ -121,98 +126,118 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE) k_shape(long long n, const T* 
     c.A[0] = a[0];
     c.A[1] = a[1];
     c.A[2] = a[2];
+    const T conn[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]};
+    const T ez[3] = {T(0), T(0), T(1)};
+    const T zero3[3] = {T(0), T(0), T(0)};
     T Cv;
-    cat_shape_span_setup<T, M>(a, b, Li, c_lo, c_hi, c.sp[0], &Cv);
+    cat_shape_span_setup<T, M>(conn, Li, c_lo, c_hi, hop, c.sp[0], &Cv);
     if (C_out) C_out[i] = Cv;
     int vbits = c.sp[0].valid;
+    if (c.sp[0].valid) {
+      const T axy[3] = {conn[0], conn[1], T(0)};
+      cat_shape_map_set<T>(c.map[0], axy, ez);
+    } else {                                   // straight chord [A, B] (main_fun.py:67-69)
+      cat_shape_map_set<T>(c.map[0], conn, zero3);
+    }
     if (need_rot) {
       const T th = theta ? theta[i] : T(0);
       const T ga = gamma ? gamma[i] : T(0);
-      M::sincos_(th, &c.st, &c.ct);
-      M::sincos_(ga, &c.sg, &c.cg);
-      const T conn[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]};
+      T st, ct, sg, cg;
+      M::sincos_(th, &st, &ct);
+      M::sincos_(ga, &sg, &cg);
       T kt[3];
       cat_theta_axis<T, M>(conn, kt);
       // main_fun.py:92  rotated_B = A + rodrigues(conn, k_theta, theta)
       T rb[3];
-      cat_rodrigues<T, M>(conn, kt, c.ct, c.st, rb);
+      cat_rodrigues<T, M>(conn, kt, ct, st, rb);
       const T bq[3] = {a[0] + rb[0], a[1] + rb[1], a[2] + rb[2]};
-      cat_shape_span_setup<T, M>(a, bq, Li, c_lo, c_hi, c.sp[1], (T*)nullptr);
+      const T rel1[3] = {bq[0] - a[0], bq[1] - a[1], bq[2] - a[2]};
+      cat_shape_span_setup<T, M>(rel1, Li, c_lo, c_hi, hop, c.sp[1], (T*)nullptr);
       vbits |= c.sp[1].valid << 1;
       // axes as rodrigues_rotation normalises them (main_fun.py:30)
       const T nt = M::sqrt_(kt[0] * kt[0] + kt[1] * kt[1] + kt[2] * kt[2]);
-      c.k_theta[0] = M::div_(kt[0], nt);
-      c.k_theta[1] = M::div_(kt[1], nt);
-      c.k_theta[2] = M::div_(kt[2], nt);
+      const T kth[3] = {M::div_(kt[0], nt), M::div_(kt[1], nt), M::div_(kt[2], nt)};
       // main_fun.py:102-103 gamma axis = conn/|conn| (then normalised again inside rodrigues)
       const T nc = M::sqrt_(conn[0] * conn[0] + conn[1] * conn[1] + conn[2] * conn[2]);
-      const T kg[3] = {M::div_(conn[0], nc), M::div_(conn[1], nc), M::div_(conn[2], nc)};
-      const T ng = M::sqrt_(kg[0] * kg[0] + kg[1] * kg[1] + kg[2] * kg[2]);
-      c.k_gamma[0] = M::div_(kg[0], ng);
-      c.k_gamma[1] = M::div_(kg[1], ng);
-      c.k_gamma[2] = M::div_(kg[2], ng);
+      const T kg0[3] = {M::div_(conn[0], nc), M::div_(conn[1], nc), M::div_(conn[2], nc)};
+      const T ng = M::sqrt_(kg0[0] * kg0[0] + kg0[1] * kg0[1] + kg0[2] * kg0[2]);
+      const T kga[3] = {M::div_(kg0[0], ng), M::div_(kg0[1], ng), M::div_(kg0[2], ng)};
+      // in-plane basis of the rotated span: (a1, b1); chord fallback: (rel1, 0)
+      T a1[3], b1[3];
+      if (c.sp[1].valid) {
+        a1[0] = rel1[0];
+        a1[1] = rel1[1];
+        a1[2] = T(0);
+        b1[0] = T(0);
+        b1[1] = T(0);
+        b1[2] = T(1);
+      } else {
+        a1[0] = rel1[0];
+        a1[1] = rel1[1];
+        a1[2] = rel1[2];
+        b1[0] = b1[1] = b1[2] = T(0);
+      }
+      cat_shape_map_set<T>(c.map[1], a1, b1);
+      // main_fun.py:96-99: A + R(k_theta, -theta)(pt - A)
+      T a2[3], b2[3];
+      cat_rot_apply<T>(kth, ct, -st, a1, a2);
+      cat_rot_apply<T>(kth, ct, -st, b1, b2);
+      cat_shape_map_set<T>(c.map[2], a2, b2);
+      // main_fun.py:106-109: A + R(k_gamma, gamma)(pt - A)
+      T a3[3], b3[3];
+      cat_rot_apply<T>(kga, cg, sg, a2, a3);
+      cat_rot_apply<T>(kga, cg, sg, b2, b3);
+      cat_shape_map_set<T>(c.map[3], a3, b3);
     }
     if (valid) valid[i] = (unsigned char)vbits;
   }
   __syncthreads();
 
-  const long long n_here = (n - base < CAT_SHAPE_TILE) ? (n - base) : CAT_SHAPE_TILE;
-  const long long total = n_here * n_pts;
-  const T inv_nm1 = (n_pts > 1) ? M::rcp_(T(n_pts - 1)) : T(0);
+  const int n_here = (int)((n - base < CAT_SHAPE_TILE) ? (n - base) : CAT_SHAPE_TILE);
+  const int lane = tid & 31, warp = tid >> 5, n_warps = CAT_SHAPE_TILE / 32;
   const long long blk = n * (long long)n_pts * 3;   // elements per output block
-  for (long long j = tid; j < total; j += CAT_SHAPE_TILE) {
-    const int ci = (int)(j / n_pts);
-    const int pt = (int)(j - (long long)ci * n_pts);
+  for (int ci = warp; ci < n_here; ci += n_warps) {
     const CatShapeCfg<T>& c = cfg[ci];
-    // s = pt/(n-1) as the oracle computes it (division), end point exactly 1
-    const T s = (pt == n_pts - 1) ? T(1) : M::div_(T(pt), T(n_pts - 1));
-    (void)inv_nm1;
-    const bool last = pt == n_pts - 1;
-    T* o = out + ((base + ci) * (long long)n_pts + pt) * 3;
-    if (which & CAT_OUT_ORIGINAL) {
-      T p[3];
-      cat_shape_point<T, M>(c.A, c.sp[0], s, last, p);
-      o[0] = p[0];
-      o[1] = p[1];
-      o[2] = p[2];
-      o += blk;
-    }
-    if (need_rot) {
-      T p[3];
-      cat_shape_point<T, M>(c.A, c.sp[1], s, last, p);
-      if (which & CAT_OUT_THETA_ROTATED) {
-        o[0] = p[0];
-        o[1] = p[1];
-        o[2] = p[2];
-        o += blk;
-      }
-      if (which & (CAT_OUT_THETA_ALIGNED | CAT_OUT_FINAL)) {
-        // main_fun.py:96-99: A + R(k_theta, -theta)(pt - A)
-        const T v[3] = {p[0] - c.A[0], p[1] - c.A[1], p[2] - c.A[2]};
-        const T* k = c.k_theta;
-        const T cx = k[1] * v[2] - k[2] * v[1], cy = k[2] * v[0] - k[0] * v[2], cz = k[0] * v[1] - k[1] * v[0];
-        const T dot = k[0] * v[0] + k[1] * v[1] + k[2] * v[2];
-        const T omc = T(1) - c.ct;
-        T q[3];
-        q[0] = c.A[0] + (v[0] * c.ct + cx * (-c.st) + k[0] * dot * omc);
-        q[1] = c.A[1] + (v[1] * c.ct + cy * (-c.st) + k[1] * dot * omc);
-        q[2] = c.A[2] + (v[2] * c.ct + cz * (-c.st) + k[2] * dot * omc);
-        if (which & CAT_OUT_THETA_ALIGNED) {
-          o[0] = q[0];
-          o[1] = q[1];
-          o[2] = q[2];
-          o += blk;
+    T* const o_cfg = out + (base + ci) * (long long)n_pts * 3;
+#pragma unroll
+    for (int spi = 0; spi < 2; ++spi) {
+      const int outs = spi == 0 ? (which & CAT_OUT_ORIGINAL) : (which & ~CAT_OUT_ORIGINAL);
+      if (!outs) continue;
+      const CatShapeSpan<T>& sp = c.sp[spi];
+      T cm = T(0), sh = T(0);
+      int hops = 0;
+      for (int pt = lane; pt < n_pts; pt += 32, ++hops) {
+        const bool last = pt == n_pts - 1;
+        const T s = last ? T(1) : T(pt) * inv_nm1;
+        T zoff = T(0);
+        if (sp.valid) {
+          if (hops % CAT_SHAPE_RESEED == 0) {
+            const T t = sp.two_u * s - sp.v_low;
+            T sm;
+            cat_hyp<T, M>(M::abs_(t), sm, cm, sh);
+            sh = t < T(0) ? -sh : sh;
+          } else {
+            // cosh(t + D) - 1 = cm + cm cmD + cmD + sh shD ;  sinh(t + D) = sh + sh cmD + (cm + 1) shD
+            const T cn = M::fma_(cm, sp.cmD, cm) + M::fma_(sh, sp.shD, sp.cmD);
+            const T sn = M::fma_(sh, sp.cmD, sh) + M::fma_(cm, sp.shD, sp.shD);
+            cm = cn;
+            sh = sn;
+          }
+          zoff = (cm - sp.cm_low) * sp.inv_C;
         }
-        if (which & CAT_OUT_FINAL) {
-          // main_fun.py:106-109: A + R(k_gamma, gamma)(pt - A)
-          const T w[3] = {q[0] - c.A[0], q[1] - c.A[1], q[2] - c.A[2]};
-          const T* g = c.k_gamma;
-          const T gx = g[1] * w[2] - g[2] * w[1], gy = g[2] * w[0] - g[0] * w[2], gz = g[0] * w[1] - g[1] * w[0];
-          const T gd = g[0] * w[0] + g[1] * w[1] + g[2] * w[2];
-          const T omg = T(1) - c.cg;
-          o[0] = c.A[0] + (w[0] * c.cg + gx * c.sg + g[0] * gd * omg);
-          o[1] = c.A[1] + (w[1] * c.cg + gy * c.sg + g[1] * gd * omg);
-          o[2] = c.A[2] + (w[2] * c.cg + gz * c.sg + g[2] * gd * omg);
+        T* o = o_cfg + (long long)pt * 3;
+        int slot = 0;
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          if (!(which & (1 << m))) continue;
+          if ((m == 0) == (spi == 0)) {
+            const CatShapeMap<T>& mp = c.map[m];
+            T* om = o + slot * blk;
+            om[0] = c.A[0] + M::fma_(zoff, mp.b[0], s * mp.a[0]);
+            om[1] = c.A[1] + M::fma_(zoff, mp.b[1], s * mp.a[1]);
+            om[2] = c.A[2] + M::fma_(zoff, mp.b[2], s * mp.a[2]);
+          }
+          ++slot;
         }
       }
     }

@@ -138,7 +138,7 @@ __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int pro
 }
 
 template <typename T, bool GENERIC>
-__global__ void __launch_bounds__(CAT_MPC_BLOCK)
+__global__ void __launch_bounds__(CAT_MPC_BLOCK, 4)   // <= 128 registers: config 3 needs 3.5 blocks per SM resident
 k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, const T* __restrict__ controls,
               const double* __restrict__ p_ref, T* __restrict__ costs, CatBest* __restrict__ block_best,
               unsigned int* __restrict__ tickets, double* __restrict__ best_cost,

@@ -92,7 +92,8 @@ __device__ __forceinline__ double cat_sin_f64(double x) {
 }
 
 // sqrt(x) for x >= 0 without the IEEE special-case path: MUFU.RSQ64H seed + two coupled Newton steps
-// (~1 ulp).  x == 0 (and denormal x, flushed by the seed) returns 0; NaN / negative propagate NaN.
+// (~1 ulp).  Every special input (0, denormal, inf, negative, NaN) makes the fast result NaN and takes the
+// one cold branch to the IEEE routine.
 __device__ __forceinline__ double cat_sqrt_f64(double x) {
   double y;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
@@ -103,7 +104,8 @@ __device__ __forceinline__ double cat_sqrt_f64(double x) {
   h = fma(h, e, h);
   e = fma(-g, g, x);           // residual x - g^2
   g = fma(e, h, g);
-  return (x > 2.3e-308 && x < 1.0e300) ? g : ((x == 0.0) ? 0.0 : sqrt(x));
+  if (g != g) g = sqrt(x);     // x = 0, denormal, inf, negative or NaN: the seed is inf/0/NaN -> IEEE routine
+  return g;
 }
 
 // For u >= 0: sh = sinh u, cm = cosh u - 1, sm = sinh u - u, all without cancellation at small u and
@@ -174,7 +176,7 @@ template <> struct CatMath<double> {
     return r;
   }
   // |du| <= step_tol * min(u,1) ends the Halley iteration: the step AFTER that one is cubic in it
-  static __device__ __forceinline__ double step_tol() { return 1e-5; }
+  static __device__ __forceinline__ double step_tol() { return 1e-6; }
   static __device__ __forceinline__ double nan_() { return __longlong_as_double(0x7ff8000000000000LL); }
   static __device__ __forceinline__ double inf_() { return __longlong_as_double(0x7ff0000000000000LL); }
 };
@@ -311,16 +313,15 @@ __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w)
     u -= du;
     more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1));
   } while (more && ++it < 60);
-  // values at the updated u from those at u+du (|du| <= 1e-5: 4th-order remainder).
+  // values at the updated u from those at u+du, second order (|du| <= 1e-6 min(u,1): remainder du^3/6 < 2e-19).
   // d/du: sm' = cm, cm' = sh, sh' = ch
   const T ch = cm + T(1);
   const T h2 = du * du * T(0.5);
-  const T h3 = du * T(1.0 / 3.0);
   CatWarm<T> r;
   r.u = u;
-  r.sm = sm - cm * du + h2 * (sh - ch * h3);
-  r.cm = cm - sh * du + h2 * (ch - sh * h3);
-  r.sh = sh - ch * du + h2 * (sh - ch * h3);
+  r.sm = M::fma_(h2, sh, M::fma_(-cm, du, sm));
+  r.cm = M::fma_(h2, ch, M::fma_(-sh, du, cm));
+  r.sh = M::fma_(h2, sh, M::fma_(-ch, du, sh));
   return r;
 }
 
@@ -384,7 +385,7 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, c
 // lowest z of the span (world frame), SURVEY.md 8a "per-step catenary terms"
 template <typename T, typename M>
 __device__ __forceinline__ T cat_z_low(const CatSpan<T>& s, T l, T L, T zA, T zB) {
-  const T zmin = M::min_(zA, zB);
+  const T zmin = zB < zA ? zB : zA;
   if (!(s.C == s.C) || !s.inside) return zmin;
   // (zA+zB)/2 + (l sh - L ch u) / (2 sh u)
   return T(0.5) * (zA + zB) + (l * s.sh - L * s.ch * s.u) * M::rcp_fast_(T(2) * s.sh * s.u);
