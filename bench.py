@@ -158,14 +158,21 @@ def run_ours(args):
     dev_sets = [torch.from_numpy(b).to(f"cuda:{local}") for b in host_sets]
     step = devmod.MpcDeviceStep(p, pref, K, controls=host_sets[0], k_offset=rank * K, device=local, ctx=ctx)
 
-    def one(i):
+    pipe = dist_mod.PipelinedExchange(step) if world > 1 else None
+
+    def one(i, wait=False):
+        """One MPC step.  N > 1: rollout on the main stream, 16-byte all-gather + device fold on a side stream
+        (double-buffered, no host sync); ``wait`` blocks for the job-wide winner (the latency loop)."""
         step.set_controls(dev_sets[i % n_sets])
-        step.launch()
-        if world > 1:
-            return dist_mod.exchange_winner(step.winner)
-        return None
+        if pipe is None:
+            step.launch()
+            return None
+        slot = pipe.submit()
+        return pipe.result(slot) if wait else None
 
     def barrier():
+        if pipe is not None:
+            pipe.drain()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -186,9 +193,18 @@ def run_ours(args):
     e0.record()
     for i in range(args.steps):
         one(i)
+    if pipe is not None:
+        torch.cuda.current_stream().wait_stream(pipe.side)      # the last exchanges are part of the timed region
     e1.record()
     barrier()
     launches = ctx.launch_count - l0
+    if pipe is not None:
+        launches += args.steps                                  # k_reduce_winners, one per step, on the side stream
+        # the pipelined exchange must agree with the plain host-side exchange
+        step.launch()
+        want = dist_mod.exchange_winner(step.winner)
+        got = pipe.result(pipe.submit())
+        assert got == want, (got, want)
     ms_total = e0.elapsed_time(e1)
     if world > 1:
         t = torch.tensor([ms_total], device=f"cuda:{local}", dtype=torch.float64)
@@ -200,7 +216,7 @@ def run_ours(args):
     for i in range(n_lat):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        r = one(i)
+        r = one(i, wait=True)
         if r is None:
             step.result()
         b.record()
@@ -304,7 +320,7 @@ def run_ours(args):
            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
            "config": {"workload": "config3", "candidates_per_gpu": K, "horizon": H, "dt": p["dt"],
-                      "controls": "explicit fp64 SoA [H][3][K]", "exchange": "nccl all_gather 16 B/rank" if world > 1 else "none",
+                      "controls": "explicit fp64 SoA [H][3][K]", "exchange": "nccl all_gather 16 B/rank + device fold on a side stream, double-buffered" if world > 1 else "none",
                       "l2": "3 rotating control sets (236 MB) > 126 MB L2"},
            "p50_ms": lat[len(lat) // 2], "p99_ms": lat[int(len(lat) * 0.99)], "latency_samples": len(lat),
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}

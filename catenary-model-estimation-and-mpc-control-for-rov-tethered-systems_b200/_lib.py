@@ -78,6 +78,7 @@ SIGNATURES = {
     "cat_mpc_step_dev_f32": (_int, [_vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cat_sample_controls_dev_f64": (_int, [_vp, _PP, _vp]),
     "cat_reduce_winners_f64": (_int, [_int, _vp, _vp, _vp, _vp]),
+    "cat_reduce_winners_dev_f64": (_int, [_vp, _int, _vp, _vp]),
     "cat_measure_peak": (_int, [_vp, _int, C.POINTER(C.c_double)]),
 }
 

@@ -292,6 +292,25 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   cat_grid_argmin(jc, ji, prob, block_best, tickets, best_cost, best_idx);
 }
 
+// fold of the per-rank winners gathered from G ranks, on the device: in = G x [cost bits, global idx]
+// (the layout MpcDeviceStep.winner has and all_gather produces), out = [cost bits, idx].  Rank order,
+// np.argmin ordering -> identical on every rank.
+__global__ void k_reduce_winners(int n, const long long* __restrict__ in, long long* __restrict__ out) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  double bc = __longlong_as_double(in[0]);
+  long long bi = in[1];
+  for (int g = 1; g < n; ++g) {
+    const double c = __longlong_as_double(in[2 * g]);
+    const long long i = in[2 * g + 1];
+    if (cat_better(c, i, bc, bi)) {
+      bc = c;
+      bi = i;
+    }
+  }
+  out[0] = __double_as_longlong(bc);
+  out[1] = bi;
+}
+
 // materialise the on-device RNG controls: out[p][h][a][k] (SoA over candidates)
 template <typename T>
 __global__ void __launch_bounds__(256) k_sample_controls(const CatMpcDev<T> q, T* __restrict__ out) {

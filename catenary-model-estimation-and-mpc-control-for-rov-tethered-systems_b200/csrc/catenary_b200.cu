@@ -753,6 +753,16 @@ int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx, double
   return CAT_OK;
 }
 
+int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_t* out) {
+  CTX();
+  NEED(n >= 1 && gathered && out);
+  int rc = bind(c);
+  if (rc) return rc;
+  k_reduce_winners<<<1, 32, 0, c->stream>>>(n, (const long long*)gathered, (long long*)out);
+  LAUNCHED();
+  return CAT_OK;
+}
+
 // ---- roofline denominators --------------------------------------------------------------------------
 int cat_measure_peak(void* ctx, int kind, double* ops_per_s) {
   CTX();

@@ -53,13 +53,15 @@ class MpcDeviceStep:
         """Swap in another device tensor of candidate controls (same layout and dtype)."""
         self.controls = controls_dev
 
-    def launch(self):
-        """Enqueue the step on torch's current stream; returns immediately."""
+    def launch(self, winner=None):
+        """Enqueue the step on torch's current stream; returns immediately.  ``winner``: alternative int64
+        [2n] device buffer for [cost bits | idx] (double-buffering across pipelined steps)."""
         torch = self.torch
+        w = self.winner if winner is None else winner
         self.ctx.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
         self.ctx.check(self._fn(self.ctx.handle, C.byref(self.params), self.problems.data_ptr(),
                                 None if self.controls is None else self.controls.data_ptr(), self.p_ref.data_ptr(),
-                                self.best_cost.data_ptr(), self.best_idx.data_ptr(),
+                                w.data_ptr(), w.data_ptr() + 8 * self.n,
                                 None if self.costs is None else self.costs.data_ptr()))
 
     def result(self):

@@ -75,3 +75,55 @@ class ShardedMpcStep:
 def fleet_shard(n_problems, rank, world):
     """Config 5: problems [lo, hi) of this rank; no cross-GPU communication."""
     return shard_range(n_problems, rank, world)
+
+
+class PipelinedExchange:
+    """Sync-free multi-GPU step: the MPC kernel runs on torch's current stream; the 16-byte all-gather and the
+    device-side fold (cat_reduce_winners_dev_f64) run on a side stream, double-buffered, so step i+1's rollout
+    overlaps step i's exchange and the host never blocks until ``result``.  Every rank ends with the same
+    (cost bits, idx) pair in ``final[slot]``."""
+
+    def __init__(self, step, group=None, depth=2):
+        import torch
+        import torch.distributed as dist
+        from .context import Context
+        self.torch, self.dist, self.step, self.group = torch, dist, step, group
+        self.world = dist.get_world_size(group)
+        dev = step.dev
+        self.depth = depth
+        self.side = torch.cuda.Stream(device=dev)
+        self.fold_ctx = Context(dev.index)                  # its own handle: its stream is the side stream
+        self.fold_ctx.set_stream(self.side.cuda_stream)
+        self.local = [torch.zeros(2, dtype=torch.int64, device=dev) for _ in range(depth)]
+        self.gathered = [torch.zeros(2 * self.world, dtype=torch.int64, device=dev) for _ in range(depth)]
+        self.final = [torch.zeros(2, dtype=torch.int64, device=dev) for _ in range(depth)]
+        self.done = [torch.cuda.Event() for _ in range(depth)]
+        self.ready = [torch.cuda.Event() for _ in range(depth)]
+        self.count = 0
+
+    def submit(self):
+        """Enqueue one step (rollout + exchange + fold); returns the slot holding its result."""
+        torch = self.torch
+        s = self.count % self.depth
+        main = torch.cuda.current_stream(self.step.dev)
+        if self.count >= self.depth:
+            main.wait_event(self.done[s])                   # the exchange that last used this slot has drained
+        self.step.launch(winner=self.local[s])
+        self.ready[s].record(main)
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(self.ready[s])
+            self.dist.all_gather_into_tensor(self.gathered[s], self.local[s], group=self.group)
+            self.fold_ctx.check(self.fold_ctx.lib.cat_reduce_winners_dev_f64(
+                self.fold_ctx.handle, self.world, self.gathered[s].data_ptr(), self.final[s].data_ptr()))
+            self.done[s].record(self.side)
+        self.count += 1
+        return s
+
+    def result(self, slot):
+        """(best_idx, best_cost) of the step submitted into ``slot`` (blocks the host on that slot only)."""
+        self.done[slot].synchronize()
+        w = self.final[slot].cpu().numpy()
+        return int(w[1]), float(w[:1].view(np.float64)[0])
+
+    def drain(self):
+        self.side.synchronize()

@@ -204,6 +204,11 @@ CAT_API int cat_sample_controls_dev_f64(void* ctx, const CatMpcParams* p, double
 CAT_API int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx,
                            double* best_cost, int64_t* best_idx);
 
+/* the same fold on the device (enqueued on the ctx stream, no host sync): gathered = n x [cost bits, global idx]
+ * as int64 pairs (what cat_mpc_step_dev_* leaves when best_cost and best_idx point into one 16-byte buffer and
+ * the ranks all-gather it), out = one such pair. */
+CAT_API int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_t* out);
+
 /* ---- peak microbenchmarks for the roofline denominators (bench.py) -------------------
  * kind 0 = DFMA, 1 = FFMA, 2 = MUFU.EX2; returns operations per second (FMA = 1 op). */
 CAT_API int cat_measure_peak(void* ctx, int kind, double* ops_per_s);
