@@ -11,5 +11,6 @@ from .geometry import (Catenary, catenary_shapes, lowest_point, rodrigues_rotati
                        transform_catenary)
 from .mpc import (circle_reference, default_mpc_params, make_params, make_problems, mpc_fleet_step,
                   mpc_sample_step, reduce_winners)
+from .controller import RecedingHorizonController, mpc_receding_horizon
 
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -14,6 +14,8 @@ LIB_PATH = os.path.join(_HERE, "libcatenary_b200.so")
 CAT_OK, CAT_EINVAL, CAT_ECUDA, CAT_ENOMEM, CAT_ENODEV = 0, -1, -2, -3, -4
 OUT_ORIGINAL, OUT_THETA_ROTATED, OUT_THETA_ALIGNED, OUT_FINAL = 1, 2, 4, 8
 MPC_RNG_CONTROLS, MPC_CONTROLS_AOS = 1, 2
+CTRL_ARGMIN, CTRL_MPPI = 0, 1
+CTRL_LOG_W = 16
 
 
 class CatMpcParams(C.Structure):
@@ -32,12 +34,18 @@ class CatMpcProblem(C.Structure):
                 ("gamma_prev", C.c_double)]
 
 
+class CatCtrlConfig(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("max_steps", C.c_int32), ("use_graph", C.c_int32), ("reserved", C.c_int32),
+                ("lam", C.c_double), ("u_max", C.c_double * 3)]
+
+
 PROBLEM_DTYPE = np.dtype([("P0", "f8", 3), ("P1", "f8", 3), ("V1", "f8", 3), ("A1", "f8", 3), ("theta", "f8"),
                           ("gamma", "f8"), ("theta_prev", "f8"), ("gamma_prev", "f8")])
 assert PROBLEM_DTYPE.itemsize == C.sizeof(CatMpcProblem) == 128
 
 _vp, _i64, _i32, _int = C.c_void_p, C.c_int64, C.c_int32, C.c_int
 _PP = C.POINTER(CatMpcParams)
+_PC = C.POINTER(CatCtrlConfig)
 
 # name -> (restype, argtypes); every symbol include/catenary_b200.h declares
 SIGNATURES = {
@@ -79,6 +87,12 @@ SIGNATURES = {
     "cat_sample_controls_dev_f64": (_int, [_vp, _PP, _vp]),
     "cat_reduce_winners_f64": (_int, [_int, _vp, _vp, _vp, _vp]),
     "cat_reduce_winners_dev_f64": (_int, [_vp, _int, _vp, _vp]),
+    "cat_ctrl_create_f64": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
+    "cat_ctrl_create_f32": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
+    "cat_ctrl_run": (_int, [_vp, _i32]),
+    "cat_ctrl_set_state": (_int, [_vp, _vp]),
+    "cat_ctrl_read": (_int, [_vp, C.POINTER(_i32), _vp, _vp, _vp, _i32, _i32]),
+    "cat_ctrl_destroy": (_int, [_vp]),
     "cat_measure_peak": (_int, [_vp, _int, C.POINTER(C.c_double)]),
 }
 

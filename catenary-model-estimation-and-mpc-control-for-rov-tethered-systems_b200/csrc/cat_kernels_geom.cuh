@@ -50,11 +50,28 @@ template <typename T> struct CatShapeMap {
   T a[3], b[3];   // sample = A + s a + zoff b
 };
 
-template <typename T> struct CatShapeCfg {
-  T A[3];
-  CatShapeSpan<T> sp[2];
-  CatShapeMap<T> map[4];   // original, theta_rotated, theta_aligned, final
-};
+// Shared-memory record of one configuration, sized by what `which` asks for (occupancy: the full record is
+// 328 B in fp64, the final-curve-only record 136 B):  A[3] | spans needed x 7 | maps requested x 6, as T values
+// (valid is stored as 0/1 in T).  The stride is made odd so the 128 phase-1 writers hit distinct banks.
+#define CAT_SHAPE_SPAN_W 7
+#define CAT_SHAPE_MAP_W 6
+__host__ __device__ __forceinline__ int cat_shape_record_len(int which) {
+  const int nspan = ((which & CAT_OUT_ORIGINAL) ? 1 : 0) + ((which & ~CAT_OUT_ORIGINAL & 15) ? 1 : 0);
+  int nmap = 0;
+  for (int m = 0; m < 4; ++m) nmap += (which >> m) & 1;
+  return (3 + CAT_SHAPE_SPAN_W * nspan + CAT_SHAPE_MAP_W * nmap) | 1;
+}
+
+template <typename T>
+__device__ __forceinline__ void cat_shape_store_span(T* r, const CatShapeSpan<T>& sp) {
+  r[0] = sp.two_u;
+  r[1] = sp.v_low;
+  r[2] = sp.inv_C;
+  r[3] = sp.cm_low;
+  r[4] = sp.cmD;
+  r[5] = sp.shD;
+  r[6] = T(sp.valid);
+}
 
 template <typename T, typename M>
 __device__ __forceinline__ void cat_shape_span_setup(const T rel[3], T L, T c_lo, T c_hi, T hop, CatShapeSpan<T>& sp,
@@ -111,7 +128,12 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE) k_shape(long long n, const T* 
                                                           T c_lo, T c_hi, T* __restrict__ out,
                                                           T* __restrict__ C_out, unsigned char* __restrict__ valid) {
   typedef CatMath<T> M;
-  __shared__ CatShapeCfg<T> cfg[CAT_SHAPE_TILE];
+  extern __shared__ __align__(16) unsigned char cat_shape_smem[];
+  T* const rec = reinterpret_cast<T*>(cat_shape_smem);
+  const int rec_len = cat_shape_record_len(which);
+  const bool need0 = (which & CAT_OUT_ORIGINAL) != 0;
+  const int span1_at = 3 + (need0 ? CAT_SHAPE_SPAN_W : 0);
+  const int maps_at = span1_at + ((which & ~CAT_OUT_ORIGINAL & 15) ? CAT_SHAPE_SPAN_W : 0);
   const long long base = (long long)blockIdx.x * CAT_SHAPE_TILE;
   const int tid = threadIdx.x;
   const long long i = base + tid;
@@ -119,13 +141,17 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE) k_shape(long long n, const T* 
   const T inv_nm1 = (n_pts > 1) ? M::div_(T(1), T(n_pts - 1)) : T(0);
   const T hop = T(32) * inv_nm1;
   if (i < n) {
-    CatShapeCfg<T>& c = cfg[tid];
+    struct {
+      CatShapeSpan<T> sp[2];
+      CatShapeMap<T> map[4];
+    } c;
+    T* const r = rec + tid * rec_len;
     const T a[3] = {A[3 * i], A[3 * i + 1], A[3 * i + 2]};
     const T b[3] = {B[3 * i], B[3 * i + 1], B[3 * i + 2]};
     const T Li = L[i * L_stride];
-    c.A[0] = a[0];
-    c.A[1] = a[1];
-    c.A[2] = a[2];
+    r[0] = a[0];
+    r[1] = a[1];
+    r[2] = a[2];
     const T conn[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]};
     const T ez[3] = {T(0), T(0), T(1)};
     const T zero3[3] = {T(0), T(0), T(0)};
@@ -190,6 +216,20 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE) k_shape(long long n, const T* 
       cat_shape_map_set<T>(c.map[3], a3, b3);
     }
     if (valid) valid[i] = (unsigned char)vbits;
+    if (need0) cat_shape_store_span<T>(r + 3, c.sp[0]);
+    if (need_rot) cat_shape_store_span<T>(r + span1_at, c.sp[1]);
+    int slot = 0;
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      if (!(which & (1 << m))) continue;
+      T* rm = r + maps_at + CAT_SHAPE_MAP_W * slot;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        rm[j] = c.map[m].a[j];
+        rm[3 + j] = c.map[m].b[j];
+      }
+      ++slot;
+    }
   }
   __syncthreads();
 
@@ -197,13 +237,22 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE) k_shape(long long n, const T* 
   const int lane = tid & 31, warp = tid >> 5, n_warps = CAT_SHAPE_TILE / 32;
   const long long blk = n * (long long)n_pts * 3;   // elements per output block
   for (int ci = warp; ci < n_here; ci += n_warps) {
-    const CatShapeCfg<T>& c = cfg[ci];
+    const T* const r = rec + ci * rec_len;
+    const T A0 = r[0], A1 = r[1], A2 = r[2];
     T* const o_cfg = out + (base + ci) * (long long)n_pts * 3;
 #pragma unroll
     for (int spi = 0; spi < 2; ++spi) {
       const int outs = spi == 0 ? (which & CAT_OUT_ORIGINAL) : (which & ~CAT_OUT_ORIGINAL);
       if (!outs) continue;
-      const CatShapeSpan<T>& sp = c.sp[spi];
+      const T* const rs = r + (spi == 0 ? 3 : span1_at);
+      CatShapeSpan<T> sp;
+      sp.two_u = rs[0];
+      sp.v_low = rs[1];
+      sp.inv_C = rs[2];
+      sp.cm_low = rs[3];
+      sp.cmD = rs[4];
+      sp.shD = rs[5];
+      sp.valid = rs[6] != T(0);
       T cm = T(0), sh = T(0);
       int hops = 0;
       for (int pt = lane; pt < n_pts; pt += 32, ++hops) {
@@ -231,11 +280,11 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE) k_shape(long long n, const T* 
         for (int m = 0; m < 4; ++m) {
           if (!(which & (1 << m))) continue;
           if ((m == 0) == (spi == 0)) {
-            const CatShapeMap<T>& mp = c.map[m];
+            const T* mp = r + maps_at + CAT_SHAPE_MAP_W * slot;   // a[3] | b[3]
             T* om = o + slot * blk;
-            om[0] = c.A[0] + M::fma_(zoff, mp.b[0], s * mp.a[0]);
-            om[1] = c.A[1] + M::fma_(zoff, mp.b[1], s * mp.a[1]);
-            om[2] = c.A[2] + M::fma_(zoff, mp.b[2], s * mp.a[2]);
+            om[0] = A0 + M::fma_(zoff, mp[3], s * mp[0]);
+            om[1] = A1 + M::fma_(zoff, mp[4], s * mp[1]);
+            om[2] = A2 + M::fma_(zoff, mp[5], s * mp[2]);
           }
           ++slot;
         }

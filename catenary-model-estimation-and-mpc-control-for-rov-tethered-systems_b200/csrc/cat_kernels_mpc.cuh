@@ -29,7 +29,28 @@ template <typename T> struct CatMpcDev {
   T dt, dt_mm, dt6, L, w_trk, w_du, w_len, w_sag, w_ang, rhoL, rhoL2, z_thr, c_lo, c_hi, pen, clip;
   T sigma[3];
   unsigned long long seed;
+  // receding-horizon controller mode (cat_kernels_ctrl.cuh); all null / H in a plain step
+  const double* u_nom;    // [n_problems][H][3]: candidates = clamp(u_nom + noise, +-u_max); candidate 0 noise-free
+  const int* step;        // device-resident control-step counter t: RNG key = seed + t, reference window starts at t
+  int ref_len;            // rows of p_ref per problem (H in a plain step)
+  T u_max[3];
 };
+
+// candidate control of the receding-horizon controller: clamp(u_nom[h] + sigma*clip(N(0,1)), +-u_max);
+// global candidate 0 carries no noise (oracle ctrl_candidates)
+template <typename T, typename M>
+__device__ __forceinline__ void cat_nominal_control(const CatMpcDev<T>& q, unsigned long long seed_eff, int prob,
+                                                    long long kglob, int h, T out[3]) {
+  cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)kglob, (uint32_t)h, q.sigma,
+                           q.clip, out);
+  const double* un = q.u_nom + ((long long)prob * q.H + h) * 3;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const T z = kglob == 0 ? T(0) : out[a];
+    const T v = T(un[a]) + z;
+    out[a] = M::min_(M::max_(v, -q.u_max[a]), q.u_max[a]);
+  }
+}
 
 template <typename T, bool GENERIC>
 __device__ __forceinline__ void cat_eval_pair(const CatMpcDev<T>& q, const T (&x)[18], T& ft, T& fg) {
@@ -160,7 +181,12 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
 
   const bool rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
   const T* uc = rng ? nullptr : controls + (long long)prob * q.sp + kk * q.sk;
-  const double* pr = p_ref + (long long)prob * q.H * 3;
+  // controller mode: the step counter lives in HBM so that one captured graph serves every control step
+  int t0 = 0;
+  if (q.step) t0 = min(*q.step, q.ref_len - 1);
+  const unsigned long long seed_eff = q.seed + (unsigned long long)(q.step ? *q.step : 0);
+  const int ref_rem = q.ref_len - t0;   // rows left in the reference trajectory; the last one is held
+  const double* pr = p_ref + ((long long)prob * q.ref_len + t0) * 3;
 
   // Scaled features and stage-1 slopes of the CURRENT state.  They are carried across steps: the
   // stage-4 feature row of step h equals the stage-1 row of step h+1 except for the theta/gamma
@@ -197,8 +223,11 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   for (int h = 0; h < q.H; ++h) {
     T Vn[3];
     if (rng) {
-      cat_sample_control<T, M>(q.seed, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
-                               (uint32_t)h, q.sigma, q.clip, Vn);
+      if (q.u_nom)
+        cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + kk, h, Vn);
+      else
+        cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
+                                 (uint32_t)h, q.sigma, q.clip, Vn);
     } else {
       Vn[0] = Vnext[0];
       Vn[1] = Vnext[1];
@@ -212,7 +241,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
         Vnext[1] = uc[q.sa];
         Vnext[2] = uc[2 * q.sa];
       }
-      pr += 3;
+      if (h + 1 < ref_rem) pr += 3;
       Rnext[0] = T(pr[0]);
       Rnext[1] = T(pr[1]);
       Rnext[2] = T(pr[2]);

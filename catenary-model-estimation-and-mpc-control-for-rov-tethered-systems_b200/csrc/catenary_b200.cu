@@ -15,6 +15,7 @@
 #include "cat_kernels_dyn.cuh"
 #include "cat_kernels_geom.cuh"
 #include "cat_kernels_mpc.cuh"
+#include "cat_kernels_ctrl.cuh"
 
 namespace {
 
@@ -143,7 +144,8 @@ template <typename T>
 int shape_dev_on(CatCtx* c, cudaStream_t st, int64_t n, const T* A, const T* B, const T* L, int64_t L_stride,
                  const T* theta, const T* gamma, int32_t n_pts, int32_t which, T* out, T* C_out, uint8_t* valid) {
   if (n == 0) return CAT_OK;
-  k_shape<T><<<nblk(n, CAT_SHAPE_TILE), CAT_SHAPE_TILE, 0, st>>>(n, A, B, L, L_stride, theta, gamma, n_pts, which,
+  const size_t smem = (size_t)CAT_SHAPE_TILE * cat_shape_record_len(which) * sizeof(T);
+  k_shape<T><<<nblk(n, CAT_SHAPE_TILE), CAT_SHAPE_TILE, smem, st>>>(n, A, B, L, L_stride, theta, gamma, n_pts, which,
                                                                  T(kCLo), T(kCHi), out, C_out, valid);
   LAUNCHED();
   return CAT_OK;
@@ -264,6 +266,17 @@ int rk4_open_host(CatCtx* c, int64_t n_traj, int64_t T_len, const T* X, const T*
 }
 
 // ---------------------------------------------------------------------------------------------
+// Threads per block of k_mpc_rollout: 128 = one warp per SM sub-partition per block.  Measured on B200 at
+// config 3 (65,536 x 50, explicit controls): 128 -> 0.116 ms, 64 -> 0.120 ms, 32 -> 0.136 ms; smaller blocks
+// balance the SMs better (512 blocks on 148 SMs is 3.46 per SM) but unbalance the four schedulers inside an SM,
+// which costs more.  CAT_MPC_BLOCK_SIZE overrides (tuning only).
+inline int mpc_block_size(CatCtx* c, long long K, int n_problems) {
+  if (c->mpc_block) return c->mpc_block;
+  (void)K;
+  (void)n_problems;
+  return 128;
+}
+
 template <typename T>
 int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   NEED(p != nullptr);
@@ -309,28 +322,26 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.clip = T(p->clip);
   for (int a = 0; a < 3; ++a) q.sigma[a] = T(p->sigma[a]);
   q.seed = p->seed;
+  q.u_nom = nullptr;
+  q.step = nullptr;
+  q.ref_len = p->H;
+  for (int a = 0; a < 3; ++a) q.u_max[a] = T(0);
   return CAT_OK;
 }
 
+// launch of k_mpc_rollout for a filled q; bb/tk = per-block winner slots and tickets (ctx scratch when null)
 template <typename T>
-int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
-                 const double* p_ref, double* best_cost, long long* best_idx, T* costs) {
-  CatMpcDev<T> q;
-  int rc = mpc_fill<T>(c, p, q);
-  if (rc) return rc;
-  const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
-  NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
+int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, const T* controls,
+               const double* p_ref, double* best_cost, long long* best_idx, T* costs, CatBest* bb,
+               unsigned int* tk) {
   // Launch shape: one thread per candidate.  (A role-split variant -- dynamics and catenary chains of a
   // candidate in two threads -- was measured in round 1 and was 13% SLOWER at config 3: the kernel is bound by
   // issue slots, not by the dependency chain, and the split duplicates loads and kinematics.  DESIGN.md 9.)
-  int block = c->mpc_block;
-  if (block == 0) block = 128;
+  const int block = mpc_block_size(c, q.K, q.n_problems);
   const dim3 grid(nblk(q.K, block), (unsigned)q.n_problems, 1);
-  CatBest* bb;
-  unsigned int* tk;
-  {
+  if (!bb) {
     void* pp = nullptr;
-    rc = scratch(c, SLOT_BEST, (size_t)grid.x * grid.y * sizeof(CatBest), &pp);
+    int rc = scratch(c, SLOT_BEST, (size_t)grid.x * grid.y * sizeof(CatBest), &pp);
     if (rc) return rc;
     bb = (CatBest*)pp;
     rc = scratch(c, SLOT_TICKET, (size_t)65536 * sizeof(unsigned int), &pp, true);
@@ -346,6 +357,17 @@ int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems
                                                           best_idx);
   LAUNCHED();
   return CAT_OK;
+}
+
+template <typename T>
+int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
+                 const double* p_ref, double* best_cost, long long* best_idx, T* costs) {
+  CatMpcDev<T> q;
+  int rc = mpc_fill<T>(c, p, q);
+  if (rc) return rc;
+  const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
+  NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
+  return mpc_launch<T>(c, q, problems, controls, p_ref, best_cost, best_idx, costs, nullptr, nullptr);
 }
 
 template <typename T>
@@ -380,6 +402,200 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   if (costs)
     CU(cudaMemcpyAsync(costs, d_costs, np * (size_t)p->K * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// receding-horizon controller: device-resident state, one CUDA graph per control step
+struct CatCtrl {
+  CatCtx* c;
+  bool f32;
+  CatMpcParams p;
+  CatCtrlConfig cfg;
+  int64_t ref_len;
+  int steps;                 // control steps enqueued so far
+  CatMpcProblem* d_prob;
+  double *d_unom, *d_ustar, *d_ref, *d_log, *d_bc;
+  long long* d_bi;
+  void* d_costs;             // T [n_problems][K] (MPPI only)
+  int* d_step;
+  unsigned int *d_ticket, *d_tk;
+  CatBest* d_bb;
+  cudaGraphExec_t exec;
+  cudaStream_t exec_stream;  // stream the graph was captured on
+};
+
+void ctrl_free(CatCtrl* k) {
+  if (!k) return;
+  cudaSetDevice(k->c->device);
+  if (k->exec) cudaGraphExecDestroy(k->exec);
+  void* bufs[] = {k->d_prob, k->d_unom, k->d_ustar, k->d_ref, k->d_log, k->d_bc, k->d_costs, k->d_step,
+                  k->d_ticket, k->d_tk, k->d_bb};
+  for (void* b : bufs)
+    if (b) cudaFree(b);
+  delete k;
+}
+
+template <typename T>
+int ctrl_fill(CatCtrl* k, CatMpcDev<T>& q) {
+  CatCtx* c = k->c;
+  int rc = mpc_fill<T>(c, &k->p, q);
+  if (rc) return rc;
+  q.flags = CAT_MPC_RNG_CONTROLS;
+  q.u_nom = k->d_unom;
+  q.step = k->d_step;
+  q.ref_len = (int)k->ref_len;
+  for (int a = 0; a < 3; ++a) q.u_max[a] = T(k->cfg.u_max[a]);
+  return CAT_OK;
+}
+
+// the kernels of ONE control step, enqueued on the ctx stream
+template <typename T>
+int ctrl_enqueue_step(CatCtrl* k) {
+  CatCtx* c = k->c;
+  CatMpcDev<T> q;
+  CatMpcDev<double> qd;
+  int rc = ctrl_fill<T>(k, q);
+  if (rc) return rc;
+  rc = ctrl_fill<double>(k, qd);
+  if (rc) return rc;
+  CatCtrlDev x;
+  x.mode = k->cfg.mode;
+  x.max_steps = k->cfg.max_steps;
+  x.lambda = k->cfg.lambda;
+  const bool mppi = k->cfg.mode == CAT_CTRL_MPPI;
+  rc = mpc_launch<T>(c, q, k->d_prob, nullptr, k->d_ref, k->d_bc, k->d_bi, (T*)k->d_costs, k->d_bb, k->d_tk);
+  if (rc) return rc;
+  if (mppi) {
+    k_ctrl_mppi<T><<<dim3((unsigned)q.H, (unsigned)q.n_problems), 256, 0, c->stream>>>(
+        q, x, (const T*)k->d_costs, k->d_bc, k->d_bi, k->d_ustar);
+    LAUNCHED();
+  }
+  k_ctrl_advance<T><<<(unsigned)q.n_problems, 64, (size_t)q.H * 3 * sizeof(double), c->stream>>>(
+      q, qd, x, k->d_prob, k->d_unom, k->d_ustar, k->d_ref, k->d_bc, k->d_bi, k->d_log, k->d_step, k->d_ticket);
+  LAUNCHED();
+  return CAT_OK;
+}
+
+int ctrl_create(CatCtx* c, bool f32, const CatMpcParams* p, const CatCtrlConfig* cfg, const CatMpcProblem* problems,
+                const double* u_nom0, const double* p_ref_traj, int64_t ref_len, void** out) {
+  NEED(out != nullptr);
+  *out = nullptr;
+  NEED(p && cfg && problems && p_ref_traj);
+  NEED(p->K >= 1 && p->H >= 1 && p->H <= 4096 && p->n_problems >= 1 && p->n_problems <= 65535);
+  NEED(p->k_offset == 0);
+  NEED(ref_len >= 1 && ref_len < (1LL << 30));
+  NEED(cfg->mode == CAT_CTRL_ARGMIN || cfg->mode == CAT_CTRL_MPPI);
+  NEED(cfg->max_steps >= 1);
+  NEED(cfg->mode != CAT_CTRL_MPPI || cfg->lambda > 0);
+  int rc = bind(c);
+  if (rc) return rc;
+  {
+    CatMpcDev<double> chk;
+    rc = mpc_fill<double>(c, p, chk);
+    if (rc) return rc;
+  }
+  CatCtrl* k = new (std::nothrow) CatCtrl();
+  if (!k) return fail(c, CAT_ENOMEM, "controller allocation");
+  std::memset((void*)k, 0, sizeof(*k));
+  k->c = c;
+  k->f32 = f32;
+  k->p = *p;
+  k->p.flags = CAT_MPC_RNG_CONTROLS;
+  k->cfg = *cfg;
+  k->ref_len = ref_len;
+  const size_t np = (size_t)p->n_problems, H = (size_t)p->H;
+  const size_t n_blocks = ((size_t)p->K + 31) / 32;   // upper bound for any block size >= 32
+  const size_t esz = f32 ? sizeof(float) : sizeof(double);
+  bool ok = true;
+  auto dm = [&](void** ptr, size_t bytes) {
+    if (ok && cudaMalloc(ptr, bytes ? bytes : 16) != cudaSuccess) {
+      ok = false;
+      *ptr = nullptr;
+    }
+  };
+  dm((void**)&k->d_prob, np * sizeof(CatMpcProblem));
+  dm((void**)&k->d_unom, np * H * 3 * sizeof(double));
+  dm((void**)&k->d_ustar, np * H * 3 * sizeof(double));
+  dm((void**)&k->d_ref, np * (size_t)ref_len * 3 * sizeof(double));
+  dm((void**)&k->d_log, np * (size_t)cfg->max_steps * CAT_CTRL_LOG_W * sizeof(double));
+  dm((void**)&k->d_bc, np * 16);
+  if (cfg->mode == CAT_CTRL_MPPI) dm(&k->d_costs, np * (size_t)p->K * esz);
+  dm((void**)&k->d_step, 16);
+  dm((void**)&k->d_ticket, 16);
+  dm((void**)&k->d_tk, np * sizeof(unsigned int));
+  dm((void**)&k->d_bb, np * n_blocks * sizeof(CatBest));
+  if (!ok) {
+    cudaGetLastError();
+    ctrl_free(k);
+    return fail(c, CAT_ENOMEM, "cudaMalloc (controller)");
+  }
+  k->d_bi = (long long*)(k->d_bc + np);
+  cudaError_t e = cudaMemcpyAsync(k->d_prob, problems, np * sizeof(CatMpcProblem), cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess)
+    e = u_nom0 ? cudaMemcpyAsync(k->d_unom, u_nom0, np * H * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream)
+               : cudaMemsetAsync(k->d_unom, 0, np * H * 3 * sizeof(double), c->stream);
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(k->d_ref, p_ref_traj, np * (size_t)ref_len * 3 * sizeof(double), cudaMemcpyHostToDevice,
+                        c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(k->d_ustar, 0, np * H * 3 * sizeof(double), c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(k->d_step, 0, 16, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(k->d_ticket, 0, 16, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(k->d_tk, 0, np * sizeof(unsigned int), c->stream);
+  if (e == cudaSuccess)
+    e = cudaMemsetAsync(k->d_log, 0, np * (size_t)cfg->max_steps * CAT_CTRL_LOG_W * sizeof(double), c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);   // the host buffers may go away after this call
+  if (e != cudaSuccess) {
+    ctrl_free(k);
+    return fail(c, CAT_ECUDA, "controller upload", e);
+  }
+  *out = k;
+  return CAT_OK;
+}
+
+int ctrl_run(CatCtrl* k, int32_t n_steps) {
+  CatCtx* c = k->c;
+  NEED(n_steps >= 0 && (int64_t)k->steps + n_steps <= (int64_t)k->cfg.max_steps);
+  int rc = bind(c);
+  if (rc) return rc;
+  if (n_steps == 0) return CAT_OK;
+  if (k->cfg.use_graph) {
+    if (k->exec && k->exec_stream != c->stream) {   // captured on another stream: rebuild
+      cudaGraphExecDestroy(k->exec);
+      k->exec = nullptr;
+    }
+    if (!k->exec) {
+      cudaGraph_t g = nullptr;
+      CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+      const int64_t before = c->launches;
+      rc = k->f32 ? ctrl_enqueue_step<float>(k) : ctrl_enqueue_step<double>(k);
+      c->launches = before;   // capturing is not launching
+      cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+      if (rc) {
+        if (g) cudaGraphDestroy(g);
+        return rc;
+      }
+      if (e != cudaSuccess) return fail(c, CAT_ECUDA, "cudaStreamEndCapture", e);
+      e = cudaGraphInstantiate(&k->exec, g, 0);
+      cudaGraphDestroy(g);
+      if (e != cudaSuccess) {
+        k->exec = nullptr;
+        return fail(c, CAT_ECUDA, "cudaGraphInstantiate", e);
+      }
+      k->exec_stream = c->stream;
+    }
+    const int per_step = k->cfg.mode == CAT_CTRL_MPPI ? 3 : 2;
+    for (int i = 0; i < n_steps; ++i) {
+      CU(cudaGraphLaunch(k->exec, c->stream));
+      c->launches += per_step;
+    }
+  } else {
+    for (int i = 0; i < n_steps; ++i) {
+      rc = k->f32 ? ctrl_enqueue_step<float>(k) : ctrl_enqueue_step<double>(k);
+      if (rc) return rc;
+    }
+  }
+  k->steps += n_steps;
   return CAT_OK;
 }
 
@@ -764,6 +980,66 @@ int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_
 }
 
 // ---- roofline denominators --------------------------------------------------------------------------
+int cat_ctrl_create_f64(void* ctx, const CatMpcParams* p, const CatCtrlConfig* cfg, const CatMpcProblem* problems,
+                        const double* u_nom0, const double* p_ref_traj, int64_t ref_len, void** ctrl) {
+  CTX();
+  return ctrl_create(c, false, p, cfg, problems, u_nom0, p_ref_traj, ref_len, ctrl);
+}
+int cat_ctrl_create_f32(void* ctx, const CatMpcParams* p, const CatCtrlConfig* cfg, const CatMpcProblem* problems,
+                        const double* u_nom0, const double* p_ref_traj, int64_t ref_len, void** ctrl) {
+  CTX();
+  return ctrl_create(c, true, p, cfg, problems, u_nom0, p_ref_traj, ref_len, ctrl);
+}
+int cat_ctrl_run(void* ctrl, int32_t n_steps) {
+  CatCtrl* k = (CatCtrl*)ctrl;
+  if (!k) return CAT_EINVAL;
+  return ctrl_run(k, n_steps);
+}
+int cat_ctrl_set_state(void* ctrl, const CatMpcProblem* problems) {
+  CatCtrl* k = (CatCtrl*)ctrl;
+  if (!k) return CAT_EINVAL;
+  CatCtx* c = k->c;
+  NEED(problems != nullptr);
+  int rc = bind(c);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(k->d_prob, problems, (size_t)k->p.n_problems * sizeof(CatMpcProblem), cudaMemcpyHostToDevice,
+                     c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+int cat_ctrl_read(void* ctrl, int32_t* step_out, CatMpcProblem* problems_out, double* u_nom_out, double* log_out,
+                  int32_t log_from, int32_t log_n) {
+  CatCtrl* k = (CatCtrl*)ctrl;
+  if (!k) return CAT_EINVAL;
+  CatCtx* c = k->c;
+  NEED(!log_out || (log_from >= 0 && log_n >= 0 && (int64_t)log_from + log_n <= (int64_t)k->cfg.max_steps));
+  int rc = bind(c);
+  if (rc) return rc;
+  const size_t np = (size_t)k->p.n_problems, H = (size_t)k->p.H;
+  int step = 0;
+  if (step_out) CU(cudaMemcpyAsync(&step, k->d_step, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  if (problems_out)
+    CU(cudaMemcpyAsync(problems_out, k->d_prob, np * sizeof(CatMpcProblem), cudaMemcpyDeviceToHost, c->stream));
+  if (u_nom_out)
+    CU(cudaMemcpyAsync(u_nom_out, k->d_unom, np * H * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (log_out && log_n > 0)
+    CU(cudaMemcpy2DAsync(log_out, (size_t)log_n * CAT_CTRL_LOG_W * sizeof(double),
+                         k->d_log + (size_t)log_from * CAT_CTRL_LOG_W,
+                         (size_t)k->cfg.max_steps * CAT_CTRL_LOG_W * sizeof(double),
+                         (size_t)log_n * CAT_CTRL_LOG_W * sizeof(double), np, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (step_out) *step_out = step;
+  return CAT_OK;
+}
+int cat_ctrl_destroy(void* ctrl) {
+  CatCtrl* k = (CatCtrl*)ctrl;
+  if (!k) return CAT_EINVAL;
+  cudaSetDevice(k->c->device);
+  cudaStreamSynchronize(k->c->stream);
+  ctrl_free(k);
+  return CAT_OK;
+}
+
 int cat_measure_peak(void* ctx, int kind, double* ops_per_s) {
   CTX();
   NEED(ops_per_s != nullptr && kind >= 0 && kind <= 2);

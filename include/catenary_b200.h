@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define CAT_ABI_VERSION 1
+#define CAT_ABI_VERSION 2
 
 #if defined(CAT_BUILD_SHARED) && defined(__GNUC__)
 #define CAT_API __attribute__((visibility("default")))
@@ -56,6 +56,13 @@ enum {
   CAT_MPC_RNG_CONTROLS = 1,  /* controls == NULL: sample on device (Philox4x32-10) */
   CAT_MPC_CONTROLS_AOS = 2   /* controls are [n_problems][K][H][3] (the oracle's (K,H,3)) instead of SoA */
 };
+
+/* receding-horizon controller: how the next nominal sequence is formed */
+enum {
+  CAT_CTRL_ARGMIN = 0,       /* the best candidate of this step */
+  CAT_CTRL_MPPI = 1          /* exp(-(J - Jmin)/lambda)-weighted mean of all candidates */
+};
+#define CAT_CTRL_LOG_W 16    /* doubles per logged control step, see cat_ctrl_read */
 
 /* Shared parameters of one sampling-MPC step (builder-defined composition).
  * Plain-old-data, passed by pointer from the host, by value to the kernel. */
@@ -208,6 +215,47 @@ CAT_API int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx
  * as int64 pairs (what cat_mpc_step_dev_* leaves when best_cost and best_idx point into one 16-byte buffer and
  * the ranks all-gather it), out = one such pair. */
 CAT_API int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_t* out);
+
+/* ---- receding-horizon controller around the sampling-MPC step ----
+ * The role the (absent) pympc controller played at the reference's call sites: every control step samples K
+ * candidate sequences around a nominal one, rolls them out (the kernel above), picks / blends the next nominal
+ * sequence, applies its first control and shifts the rest by one step (warm start).  Everything -- plant state,
+ * nominal sequence, step counter, log -- stays in HBM; a control step is 2 kernels (3 with MPPI), replayed as one
+ * CUDA graph, with no host<->device traffic.  Definition: oracle mpc_receding_horizon.
+ *   candidate k, step h:  u = clamp(u_nom[h] + sigma * clip(N(0,1)), +-u_max), Philox keyed by
+ *   (seed + t, problem, k, h); candidate 0 carries no noise (the shifted previous solution itself).
+ *   reference window of control step t: p_ref_traj[min(t + h, ref_len - 1)], h = 0..H-1.
+ * p->flags is ignored (controls are always sampled on the device); p->k_offset must be 0. */
+typedef struct CatCtrlConfig {
+  int32_t mode;        /* CAT_CTRL_* */
+  int32_t max_steps;   /* log capacity = most control steps this controller can run */
+  int32_t use_graph;   /* != 0: capture one control step into a CUDA graph and replay it */
+  int32_t reserved;
+  double lambda;       /* MPPI temperature, cost units (> 0 when mode == CAT_CTRL_MPPI) */
+  double u_max[3];     /* per-axis bound on the commanded velocity, mm/s */
+} CatCtrlConfig;
+
+/* problems: n_problems initial states (host).  u_nom0: [n_problems][H][3] host or NULL (= 0).
+ * p_ref_traj: [n_problems][ref_len][3] host (m). */
+CAT_API int cat_ctrl_create_f64(void* ctx, const CatMpcParams* p, const CatCtrlConfig* cfg,
+                                const CatMpcProblem* problems, const double* u_nom0, const double* p_ref_traj,
+                                int64_t ref_len, void** ctrl);
+CAT_API int cat_ctrl_create_f32(void* ctx, const CatMpcParams* p, const CatCtrlConfig* cfg,
+                                const CatMpcProblem* problems, const double* u_nom0, const double* p_ref_traj,
+                                int64_t ref_len, void** ctrl);   /* fp32 rollouts, fp64 plant */
+/* enqueue n_steps closed-loop control steps on the ctx stream (plant = the model itself); no host sync */
+CAT_API int cat_ctrl_run(void* ctrl, int32_t n_steps);
+/* overwrite the plant state with a measurement before the next step (n_problems structs, host) */
+CAT_API int cat_ctrl_set_state(void* ctrl, const CatMpcProblem* problems);
+/* synchronise and read back; any pointer may be NULL.  step_out: control steps done.  problems_out: current
+ * plant states.  u_nom_out: [n_problems][H][3] current nominal sequence.  log_out: [n_problems][log_n]
+ * [CAT_CTRL_LOG_W] rows of control steps log_from .. log_from+log_n-1:
+ *   0-2 P1 after the step (m), 3-5 applied control (mm/s), 6 theta, 7 gamma, 8 C, 9 z_low, 10 best cost of
+ *   the step's candidates, 11 best candidate index, 12 cost of the applied step, 13 step index, 14 span |P1-P0|,
+ *   15 reserved. */
+CAT_API int cat_ctrl_read(void* ctrl, int32_t* step_out, CatMpcProblem* problems_out, double* u_nom_out,
+                          double* log_out, int32_t log_from, int32_t log_n);
+CAT_API int cat_ctrl_destroy(void* ctrl);
 
 /* ---- peak microbenchmarks for the roofline denominators (bench.py) -------------------
  * kind 0 = DFMA, 1 = FFMA, 2 = MUFU.EX2; returns operations per second (FMA = 1 op). */

@@ -623,3 +623,63 @@ def sample_controls(seed, k_index, H, sigma, clip=3.0, problem=0):
                   rb * np.cos(2 * np.pi * u[3])], axis=-1)
     z = np.clip(z, -clip, clip)
     return z * np.asarray(sigma, np.float64)
+
+
+# --------------------------------------------------------------------------
+# BUILDER-DEFINED: receding-horizon controller around the sampling step
+# --------------------------------------------------------------------------
+CTRL_LOG_W = 16
+
+
+def ctrl_candidates(u_nom, seed, t, K, sigma, u_max, clip=3.0, problem=0):
+    """(K,H,3) candidates of control step t: clamp(u_nom[h] + sigma*clip(N(0,1)), +-u_max), Philox keyed by
+    (seed + t, problem, k, h); candidate 0 carries no noise."""
+    H = u_nom.shape[0]
+    Z = sample_controls((int(seed) + int(t)) & 0xFFFFFFFFFFFFFFFF, np.arange(K), H, sigma, clip, problem)
+    Z[0] = 0.0
+    um = np.asarray(u_max, np.float64)
+    return np.minimum(np.maximum(u_nom[None] + Z, -um), um)
+
+
+def mpc_receding_horizon(params, p_ref_traj, n_steps, K, H, sigma, u_max, seed=0, mode="argmin", lam=1.0,
+                         clip=3.0, u_nom0=None, problem=0):
+    """Closed loop of n_steps control steps (plant = the model).  Returns dict(log (n_steps,16), u_nom (H,3),
+    state (params dict after the last step)).  Per control step t:
+      U      = ctrl_candidates(u_nom, seed, t, ...)
+      window = p_ref_traj[min(t + h, ref_len - 1)], h = 0..H-1
+      J      = mpc_rollout_costs(state, U, window);  i* = argmin_first(J)
+      u*     = U[i*]                                   (mode 'argmin')
+             = sum_k w_k U_k / sum_k w_k, w_k = exp(-(J_k - J_i*)/lam), nan J -> w = 0   (mode 'mppi';
+               falls back to U[i*] when J_i* is nan)
+      plant: one rollout step with u*[0] -> new (P1, V1, A1, theta, gamma, prevs)
+      u_nom  = (u*[1], ..., u*[H-1], u*[H-1])
+    """
+    p = dict(params)
+    traj = np.asarray(p_ref_traj, np.float64)
+    ref_len = traj.shape[0]
+    u_nom = np.zeros((H, 3)) if u_nom0 is None else np.array(u_nom0, np.float64)
+    log = np.zeros((n_steps, CTRL_LOG_W))
+    for t in range(n_steps):
+        U = ctrl_candidates(u_nom, seed, t, K, sigma, u_max, clip, problem)
+        win = traj[np.minimum(t + np.arange(H), ref_len - 1)]
+        J = mpc_rollout_costs(p, U, win)
+        i, Jb = argmin_first(J)
+        if mode == "mppi" and not np.isnan(Jb):
+            w = np.exp(-(J - Jb) / lam)
+            w = np.where(np.isnan(J), 0.0, w)
+            u_star = (w[:, None, None] * U).sum(axis=0) / w.sum()
+        else:
+            u_star = U[i].copy()
+        c, tr = mpc_rollout_costs(p, u_star[None, :1], win[:1], return_traj=True)
+        V_old = np.asarray(p["V1"], np.float64)
+        P_new = tr["P"][0, 0]
+        p["A1"] = tuple((u_star[0] - V_old) / float(p["dt"]))
+        p["V1"] = tuple(u_star[0])
+        p["P1"] = tuple(P_new)
+        p["theta_prev"], p["gamma_prev"] = p["theta"], p["gamma"]
+        p["theta"], p["gamma"] = float(tr["theta"][0, 0]), float(tr["gamma"][0, 0])
+        rel = P_new - np.asarray(p["P0"], np.float64)
+        log[t] = [*P_new, *u_star[0], p["theta"], p["gamma"], tr["C"][0, 0], tr["z_low"][0, 0], Jb, i,
+                  c[0], t, np.sqrt(rel[0] ** 2 + rel[1] ** 2 + rel[2] ** 2), 0.0]
+        u_nom = np.concatenate([u_star[1:], u_star[-1:]], axis=0)
+    return dict(log=log, u_nom=u_nom, state=p)

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol(cb):
         assert hasattr(lib, n), f"{n} declared in include/catenary_b200.h but not exported"
     bound = importlib.import_module(PKG + "._lib").SIGNATURES
     assert sorted(bound) == names, "ctypes SIGNATURES and the header disagree"
-    assert lib.cat_abi_version() == 1
+    assert lib.cat_abi_version() == 2
 
 
 def test_struct_layouts_match_header(cb):
