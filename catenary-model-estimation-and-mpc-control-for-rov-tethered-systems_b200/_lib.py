@@ -9,7 +9,7 @@ import threading
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcatenary_b200.so")
+LIB_PATH = os.environ.get("CAT_B200_LIB") or os.path.join(_HERE, "libcatenary_b200.so")   # env: a build elsewhere
 
 CAT_OK, CAT_EINVAL, CAT_ECUDA, CAT_ENOMEM, CAT_ENODEV = 0, -1, -2, -3, -4
 OUT_ORIGINAL, OUT_THETA_ROTATED, OUT_THETA_ALIGNED, OUT_FINAL = 1, 2, 4, 8
@@ -87,6 +87,9 @@ SIGNATURES = {
     "cat_sample_controls_dev_f64": (_int, [_vp, _PP, _vp]),
     "cat_reduce_winners_f64": (_int, [_int, _vp, _vp, _vp, _vp]),
     "cat_reduce_winners_dev_f64": (_int, [_vp, _int, _vp, _vp]),
+    "cat_expr_eval_f64": (_int, [_vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "cat_expr_eval_f32": (_int, [_vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "cat_expr_integrate_f64": (_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp]),
     "cat_ctrl_create_f64": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
     "cat_ctrl_create_f32": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
     "cat_ctrl_run": (_int, [_vp, _i32]),

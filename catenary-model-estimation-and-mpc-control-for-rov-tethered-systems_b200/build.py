@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB = os.path.join(_HERE, "libcatenary_b200.so")
 SOURCES = ["catenary_b200.cu"]
-HEADERS = ["cat_math.cuh", "cat_kernels_geom.cuh", "cat_kernels_dyn.cuh", "cat_kernels_mpc.cuh",
+HEADERS = ["cat_math.cuh", "cat_kernels_geom.cuh", "cat_kernels_dyn.cuh", "cat_kernels_mpc.cuh", "cat_kernels_ctrl.cuh", "cat_kernels_expr.cuh",
            os.path.join("gen", "dyn_eqs.cuh"), os.path.join("..", "..", "include", "catenary_b200.h")]
 
 

@@ -35,6 +35,9 @@ __global__ void __launch_bounds__(256) k_solve_param(long long n, const T* __res
 //   A warp writes 32 consecutive (x,y,z) triples = 768 contiguous bytes of the AoS (n, n_pts, 3) output.
 // ------------------------------------------------------------------------------------------
 #define CAT_SHAPE_TILE 128
+#ifndef CAT_SHAPE_MINB
+#define CAT_SHAPE_MINB 5    // resident blocks per SM the register budget is cut for
+#endif
 #define CAT_SHAPE_RESEED 8     // re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
 
 template <typename T> struct CatShapeSpan {
@@ -121,7 +124,7 @@ __device__ __forceinline__ void cat_shape_map_set(CatShapeMap<T>& m, const T a[3
 }
 
 template <typename T>
-__global__ void __launch_bounds__(CAT_SHAPE_TILE) k_shape(long long n, const T* __restrict__ A,
+__global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long long n, const T* __restrict__ A,
                                                           const T* __restrict__ B, const T* __restrict__ L,
                                                           long long L_stride, const T* __restrict__ theta,
                                                           const T* __restrict__ gamma, int n_pts, int which,

@@ -149,6 +149,9 @@ template <> struct CatMath<double> {
   template <int N> static __device__ __forceinline__ void sin_v(double (&a)[N]) { cat_sin_vec_f64<N>(a); }
   static __device__ __forceinline__ double pos_(double x) { return x > 0.0 ? x : 0.0; }   // max(0, x), NaN -> 0
   static __device__ __forceinline__ void sincos_(double x, double* s, double* c) { sincos(x, s, c); }
+  // sin/cos(2 pi u), u in [0,1): exact argument reduction, no Payne-Hanek path (the Box-Muller angles)
+  static __device__ __forceinline__ void sincos2pi_(double u, double* s, double* c) { sincospi(2.0 * u, s, c); }
+  static __device__ __forceinline__ double cos2pi_(double u) { return cospi(2.0 * u); }
   static __device__ __forceinline__ double tanh_(double x) { return tanh(x); }
   static __device__ __forceinline__ double exp_(double x) { return exp(x); }
   static __device__ __forceinline__ double log_(double x) { return log(x); }
@@ -191,6 +194,8 @@ template <> struct CatMath<float> {
   }
   static __device__ __forceinline__ float pos_(float x) { return x > 0.0f ? x : 0.0f; }
   static __device__ __forceinline__ void sincos_(float x, float* s, float* c) { __sincosf(x, s, c); }
+  static __device__ __forceinline__ void sincos2pi_(float u, float* s, float* c) { __sincosf(6.283185307179586f * u, s, c); }
+  static __device__ __forceinline__ float cos2pi_(float u) { return __cosf(6.283185307179586f * u); }
   static __device__ __forceinline__ float tanh_(float x) {
     float r;
     asm("tanh.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -503,9 +508,9 @@ __device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t probl
   const T u0 = (T(r[0]) + T(0.5)) * s, u1 = (T(r[1]) + T(0.5)) * s;
   const T u2 = (T(r[2]) + T(0.5)) * s, u3 = (T(r[3]) + T(0.5)) * s;
   const T ra = M::sqrt_(T(-2) * M::log_(u0)), rb = M::sqrt_(T(-2) * M::log_(u2));
-  T sa, ca, cb, sb;
-  M::sincos_(T(6.283185307179586) * u1, &sa, &ca);
-  M::sincos_(T(6.283185307179586) * u3, &sb, &cb);
+  T sa, ca;
+  M::sincos2pi_(u1, &sa, &ca);
+  const T cb = M::cos2pi_(u3);
   const T z0 = M::min_(M::max_(ra * ca, -clip), clip);
   const T z1 = M::min_(M::max_(ra * sa, -clip), clip);
   const T z2 = M::min_(M::max_(rb * cb, -clip), clip);

@@ -10,12 +10,14 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/catenary_b200.h"
 #include "cat_kernels_dyn.cuh"
 #include "cat_kernels_geom.cuh"
 #include "cat_kernels_mpc.cuh"
 #include "cat_kernels_ctrl.cuh"
+#include "cat_kernels_expr.cuh"
 
 namespace {
 
@@ -401,6 +403,140 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   CU(cudaMemcpyAsync(best_idx, d_bi, np * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
   if (costs)
     CU(cudaMemcpyAsync(costs, d_costs, np * (size_t)p->K * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// run-time equation programs (cat_kernels_expr.cuh)
+int expr_validate(CatCtx* c, int32_t n_features, int32_t n_ops, const int32_t* ops, int32_t n_consts,
+                  const double* consts) {
+  NEED(n_features >= 1 && n_ops >= 1 && n_ops <= CAT_EXPR_MAX_OPS && ops && n_consts >= 0 && n_consts <= CAT_EXPR_MAX_OPS);
+  NEED(n_consts == 0 || consts);
+  int depth = 0;
+  for (int i = 0; i < n_ops; ++i) {
+    const int op = ops[2 * i], arg = ops[2 * i + 1];
+    NEED(op >= 0 && op < CAT_OP_COUNT);
+    if (op == CAT_OP_CONST) {
+      NEED(arg >= 0 && arg < n_consts);
+      ++depth;
+    } else if (op == CAT_OP_VAR) {
+      NEED(arg >= 0 && arg < n_features);
+      ++depth;
+    } else if (op == CAT_OP_ADD || op == CAT_OP_SUB || op == CAT_OP_MUL || op == CAT_OP_DIV || op == CAT_OP_POW) {
+      NEED(depth >= 2);
+      --depth;
+    } else {
+      NEED(depth >= 1);
+      if (op == CAT_OP_POWI) NEED(arg >= -64 && arg <= 64);
+    }
+    NEED(depth <= CAT_EXPR_STACK);
+  }
+  NEED(depth == 1);
+  return CAT_OK;
+}
+
+// program + optional scaler into SLOT_F: [ops int2 n_ops | consts double n_consts | mean T F | inv_scale T F]
+template <typename T>
+int expr_upload(CatCtx* c, int32_t F, int32_t n_ops, const int32_t* ops, int32_t n_consts, const double* consts,
+                const double* mean, const double* scale, int2** d_ops, double** d_consts, T** d_mean, T** d_inv) {
+  const size_t b_ops = (size_t)n_ops * sizeof(int2);
+  const size_t b_c = (size_t)(n_consts ? n_consts : 1) * sizeof(double);
+  const size_t b_s = (size_t)F * sizeof(T);
+  unsigned char* base;
+  SCRATCH(SLOT_F, b_ops + b_c + 2 * b_s + 64, base);
+  *d_ops = (int2*)base;
+  *d_consts = (double*)(base + b_ops);
+  *d_mean = nullptr;
+  *d_inv = nullptr;
+  CU(cudaMemcpyAsync(*d_ops, ops, b_ops, cudaMemcpyHostToDevice, c->stream));
+  if (n_consts) CU(cudaMemcpyAsync(*d_consts, consts, (size_t)n_consts * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if (mean && scale) {
+    std::vector<T> h(2 * (size_t)F);
+    for (int j = 0; j < F; ++j) {
+      h[j] = T(mean[j]);
+      h[F + j] = T(1.0 / scale[j]);
+    }
+    *d_mean = (T*)(base + b_ops + b_c);
+    *d_inv = *d_mean + F;
+    CU(cudaMemcpyAsync(*d_mean, h.data(), 2 * b_s, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));   // h goes out of scope
+  }
+  return CAT_OK;
+}
+
+template <typename T>
+int expr_eval_host(CatCtx* c, int64_t n, int32_t F, const T* X, int32_t n_ops, const int32_t* ops, int32_t n_consts,
+                   const double* consts, const double* mean, const double* scale, T* out) {
+  NEED(n >= 0 && (n == 0 || (X && out)) && ((mean == nullptr) == (scale == nullptr)));
+  int rc = expr_validate(c, F, n_ops, ops, n_consts, consts);
+  if (rc) return rc;
+  if (n == 0) return CAT_OK;
+  rc = bind(c);
+  if (rc) return rc;
+  T *dX, *dO, *dm, *di;
+  int2* d_ops;
+  double* d_c;
+  SCRATCH(SLOT_A, (size_t)n * F * sizeof(T), dX);
+  SCRATCH(SLOT_B, (size_t)n * sizeof(T), dO);
+  rc = expr_upload<T>(c, F, n_ops, ops, n_consts, consts, mean, scale, &d_ops, &d_c, &dm, &di);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(dX, X, (size_t)n * F * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  const size_t smem = (size_t)n_ops * sizeof(int2) + (size_t)(n_consts + 1) * sizeof(T);
+  k_expr_eval<T><<<nblk(n, 256), 256, smem, c->stream>>>(n, F, dX, d_ops, n_ops, d_c, n_consts, dm, di, dO);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dO, (size_t)n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+template <typename T>
+int expr_integrate_host(CatCtx* c, int64_t n_traj, int64_t T_len, int32_t F, const T* X, const T* time, const T* y0,
+                        int32_t n_ops, const int32_t* ops, int32_t n_consts, const double* consts, int32_t method,
+                        T* y_out, T* ydot_out) {
+  NEED(n_traj >= 0 && T_len >= 0 && method >= 0 && method <= 2);
+  int rc = expr_validate(c, F, n_ops, ops, n_consts, consts);
+  if (rc) return rc;
+  if (n_traj == 0 || T_len == 0) return CAT_OK;
+  NEED(X && time && y0 && y_out);
+  rc = bind(c);
+  if (rc) return rc;
+  T *dX, *dt, *dy0, *dinc, *dy, *dyd, *dm, *di;
+  int2* d_ops;
+  double* d_c;
+  const size_t rows = (size_t)n_traj * T_len;
+  SCRATCH(SLOT_A, rows * F * sizeof(T), dX);
+  SCRATCH(SLOT_B, (size_t)T_len * sizeof(T), dt);
+  SCRATCH(SLOT_C, (size_t)n_traj * sizeof(T), dy0);
+  SCRATCH(SLOT_D, rows * sizeof(T), dinc);
+  SCRATCH(SLOT_E, rows * sizeof(T), dy);
+  SCRATCH(SLOT_G, rows * sizeof(T), dyd);
+  rc = expr_upload<T>(c, F, n_ops, ops, n_consts, consts, nullptr, nullptr, &d_ops, &d_c, &dm, &di);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(dX, X, rows * F * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dt, time, (size_t)T_len * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dy0, y0, (size_t)n_traj * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  const size_t smem = (size_t)n_ops * sizeof(int2) + (size_t)(n_consts + 1) * sizeof(T);
+  const long long work = (long long)n_traj * (T_len - 1);
+  if (T_len > 1) {
+    k_expr_increments<T><<<nblk(work, 256), 256, smem, c->stream>>>(n_traj, T_len, F, dX, dt, d_ops, n_ops, d_c,
+                                                                     n_consts, method, dinc);
+    LAUNCHED();
+  }
+  if (method == 2) {
+    // test_cluster.py:110-129: ydot starts at 0, y at y0
+    CU(cudaMemsetAsync(dy, 0, (size_t)n_traj * sizeof(T), c->stream));   // zero y0 of the first pass
+    k_rk4_accumulate<T><<<nblk(n_traj, 128), 128, 0, c->stream>>>(n_traj, T_len, dy, dinc, dyd);
+    LAUNCHED();
+    if (T_len > 1) {
+      k_expr_second_pass<T><<<nblk(work, 256), 256, 0, c->stream>>>(n_traj, T_len, dt, dyd, dinc);
+      LAUNCHED();
+    }
+    if (ydot_out) CU(cudaMemcpyAsync(ydot_out, dyd, rows * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+  }
+  k_rk4_accumulate<T><<<nblk(n_traj, 128), 128, 0, c->stream>>>(n_traj, T_len, dy0, dinc, dy);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(y_out, dy, rows * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return CAT_OK;
 }
@@ -980,6 +1116,25 @@ int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_
 }
 
 // ---- roofline denominators --------------------------------------------------------------------------
+int cat_expr_eval_f64(void* ctx, int64_t n, int32_t n_features, const double* X, int32_t n_ops, const int32_t* ops,
+                      int32_t n_consts, const double* consts, const double* mean, const double* scale, double* out) {
+  CTX();
+  return expr_eval_host<double>(c, n, n_features, X, n_ops, ops, n_consts, consts, mean, scale, out);
+}
+int cat_expr_eval_f32(void* ctx, int64_t n, int32_t n_features, const float* X, int32_t n_ops, const int32_t* ops,
+                      int32_t n_consts, const double* consts, const double* mean, const double* scale, float* out) {
+  CTX();
+  return expr_eval_host<float>(c, n, n_features, X, n_ops, ops, n_consts, consts, mean, scale, out);
+}
+int cat_expr_integrate_f64(void* ctx, int64_t n_traj, int64_t T, int32_t n_features, const double* X,
+                           const double* time, const double* y0, int32_t n_ops, const int32_t* ops,
+                           int32_t n_consts, const double* consts, int32_t method, double* y_out,
+                           double* ydot_out) {
+  CTX();
+  return expr_integrate_host<double>(c, n_traj, T, n_features, X, time, y0, n_ops, ops, n_consts, consts, method,
+                                     y_out, ydot_out);
+}
+
 int cat_ctrl_create_f64(void* ctx, const CatMpcParams* p, const CatCtrlConfig* cfg, const CatMpcProblem* problems,
                         const double* u_nom0, const double* p_ref_traj, int64_t ref_len, void** ctrl) {
   CTX();

@@ -216,6 +216,33 @@ CAT_API int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx
  * the ranks all-gather it), out = one such pair. */
 CAT_API int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_t* out);
 
+/* ---- run-time equation programs ----------------------------------
+ * Any PySR hall-of-fame row -- the ~3,900 equations under the reference's cluster_run/outputs and outputs
+ * directories, or a model the user retrains (simple.py:60-75) -- evaluated without rebuilding the library:
+ * the host compiles the CSV's sympy_format / Equation string to a postfix program (expr.py) and every GPU
+ * thread runs it on its feature row.  ops: n_ops pairs (opcode, arg), opcodes:
+ *   0 CONST(arg = index into consts)  1 VAR(arg = feature index)  2 ADD 3 SUB 4 MUL 5 DIV 6 NEG 7 SIN 8 COS
+ *   9 TANH 10 EXP 11 LOG 12 SQRT 13 ABS 14 SQUARE 15 CUBE 16 SIGN 17 POW (a**b, both on the stack)
+ *   18 POWI (a**arg, |arg| <= 64).  A malformed program (stack under/overflow, depth > 32, bad index) is
+ *   CAT_EINVAL.
+ * cat_expr_eval: replaces PySRRegressor.predict (test_temp.py:53-54): X (n, n_features) row-major -> out (n);
+ *   mean/scale (n_features each, both or neither): StandardScaler.transform applied first (test_temp.py:49).
+ * cat_expr_integrate: replaces rk4_integration (simulate_rk4_theta_gamma.py:52-68, method 0),
+ *   integrate_theta_gamma (main_fun.py:735-764, method 1) and the second-order scheme of
+ *   test_cluster.py:110-129 / dd_test_cluster.py:80-99 (method 2: the equation predicts the second derivative;
+ *   ydot starts at 0 and is Euler-integrated, then y from y0; ydot_out (n_traj,T) may be NULL).
+ *   X (n_traj, T, n_features), time (T), y0 (n_traj) -> y_out (n_traj, T). */
+CAT_API int cat_expr_eval_f64(void* ctx, int64_t n, int32_t n_features, const double* X, int32_t n_ops,
+                              const int32_t* ops, int32_t n_consts, const double* consts, const double* mean,
+                              const double* scale, double* out);
+CAT_API int cat_expr_eval_f32(void* ctx, int64_t n, int32_t n_features, const float* X, int32_t n_ops,
+                              const int32_t* ops, int32_t n_consts, const double* consts, const double* mean,
+                              const double* scale, float* out);
+CAT_API int cat_expr_integrate_f64(void* ctx, int64_t n_traj, int64_t T, int32_t n_features, const double* X,
+                                   const double* time, const double* y0, int32_t n_ops, const int32_t* ops,
+                                   int32_t n_consts, const double* consts, int32_t method, double* y_out,
+                                   double* ydot_out);
+
 /* ---- receding-horizon controller around the sampling-MPC step ----
  * The role the (absent) pympc controller played at the reference's call sites: every control step samples K
  * candidate sequences around a nominal one, rolls them out (the kernel above), picks / blends the next nominal

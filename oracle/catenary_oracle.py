@@ -683,3 +683,46 @@ def mpc_receding_horizon(params, p_ref_traj, n_steps, K, H, sigma, u_max, seed=0
                   c[0], t, np.sqrt(rel[0] ** 2 + rel[1] ** 2 + rel[2] ** 2), 0.0]
         u_nom = np.concatenate([u_star[1:], u_star[-1:]], axis=0)
     return dict(log=log, u_nom=u_nom, state=p)
+
+
+# --------------------------------------------------------------------------
+# run-time equations: checker for expr.py / cat_kernels_expr.cuh
+# --------------------------------------------------------------------------
+class LambdifiedModel:
+    """predict() of an arbitrary equation string the way PySRRegressor does it: sympy.sympify + lambdify to
+    NumPy (simple.py:92,105 wrote the sympy_format strings)."""
+
+    def __init__(self, expr, n_features, feature_names=None, scaler_mean=None, scaler_scale=None):
+        import sympy
+        names = list(feature_names) if feature_names else [f"x{j}" for j in range(n_features)]
+        syms = [sympy.Symbol(n) for n in names]
+        loc = dict(zip(names, syms))
+        loc.update(square=lambda v: v ** 2, cube=lambda v: v ** 3, neg=lambda v: -v)
+        self.fn = sympy.lambdify(syms, sympy.sympify(str(expr).replace("^", "**"), locals=loc), modules="numpy")
+        self.n = n_features
+        self.mean = None if scaler_mean is None else np.asarray(scaler_mean, np.float64)
+        self.scale = None if scaler_scale is None else np.asarray(scaler_scale, np.float64)
+
+    def predict(self, X):
+        X = np.asarray(X, np.float64)
+        if self.mean is not None:
+            X = (X - self.mean) / self.scale
+        with np.errstate(all="ignore"):
+            y = self.fn(*[X[:, j] for j in range(self.n)])
+        return np.broadcast_to(np.asarray(y, np.float64), (X.shape[0],)).copy()
+
+
+def integrate_second_order(pred, time, y0):
+    """test_cluster.py:110-129 restated: the model predicts the SECOND derivative; rate from 0, angle from y0,
+    both explicit Euler on the previous sample."""
+    n = len(time)
+    rate = np.zeros(n)
+    y = np.zeros(n)
+    y[0] = y0
+    for i in range(1, n):
+        dt = time[i] - time[i - 1]
+        rate[i] = rate[i - 1] + pred[i - 1] * dt
+    for i in range(1, n):
+        dt = time[i] - time[i - 1]
+        y[i] = y[i - 1] + rate[i - 1] * dt
+    return y, rate

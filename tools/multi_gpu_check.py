@@ -1,0 +1,103 @@
+#!/usr/bin/env python
+"""Multi-GPU check (run under torchrun on N GPUs): config 4 -- 4,194,304 candidates x H=100 of ONE problem,
+sharded contiguously, device-sampled controls, one 16-byte winner exchange over NCCL.  Every rank must end with
+the same (idx, cost); rank 0 re-runs the whole job shard by shard on its own GPU and the two must agree exactly.
+Also config 5 (fleet): 4,096 problems x 4,096 candidates x H=50 sharded by problem, no communication; rank 0
+spot-checks two of its problems against the oracle.  Prints one JSON line on rank 0."""
+import importlib
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+import catenary_b200 as cb  # noqa: E402
+
+
+def main():
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dmod = importlib.import_module(cb.__name__ + ".distributed")
+    devmod = importlib.import_module(cb.__name__ + ".device")
+    sigma = cb.dynamics.load_model()["scaler_scale"][3:6]
+    p = cb.default_mpc_params()
+    K_total, H = 4194304, 100
+    pref = cb.circle_reference(H, p["dt"])
+    job = dmod.ShardedMpcStep(p, pref, K_total, sigma, seed=99, device=local)
+    for _ in range(3):
+        got = job.run()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_it = 10
+    e0.record()
+    for _ in range(n_it):
+        got = job.run()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / n_it], device=f"cuda:{local}", dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    allg = [None] * world
+    dist.all_gather_object(allg, got)
+    assert all(g == allg[0] for g in allg), allg
+    out = {"world": world, "config4": {"K_total": K_total, "H": H, "best_idx": got[0], "best_cost": got[1],
+                                       "ms_per_step": float(ms.item()),
+                                       "rollout_steps_per_s": K_total * H / (float(ms.item()) * 1e-3)}}
+    if rank == 0:
+        winners = []
+        for r in range(world):
+            lo, hi = dmod.shard_range(K_total, r, world)
+            st = devmod.MpcDeviceStep(p, pref, hi - lo, sigma=sigma, seed=99, k_offset=lo, device=local)
+            st.launch()
+            i, c = st.result()
+            winners.append((float(c[0]), int(i[0])))
+        want = cb.reduce_winners([w[0] for w in winners], [w[1] for w in winners])
+        assert want == got, (want, got)
+        out["config4"]["single_gpu_replay_agrees"] = True
+    # ---- config 5: fleet, sharded by problem, no communication ----
+    n_prob, Kf, Hf = 4096, 4096, 50
+    lo, hi = dmod.fleet_shard(n_prob, rank, world)
+    rng = np.random.default_rng(10_000)
+    d = rng.normal(size=(n_prob, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:, 2] = -np.abs(d[:, 2])
+    poses = d * rng.uniform(0.8, 2.5, n_prob)[:, None]
+    prm = dict(p, P1=poses[lo:hi])
+    problems = cb.make_problems(prm, hi - lo)
+    prefs = np.stack([cb.circle_reference(Hf, p["dt"], center=poses[i]) for i in range(lo, hi)])
+    st = devmod.MpcDeviceStep(p, prefs, Kf, sigma=sigma, seed=7, problems=problems, problem_offset=lo, device=local)
+    for _ in range(2):
+        st.launch()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0.record()
+    for _ in range(5):
+        st.launch()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / 5], device=f"cuda:{local}", dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    bi, bc = st.result()
+    out["config5"] = {"problems": n_prob, "K": Kf, "H": Hf, "ms_per_sweep": float(ms.item()),
+                      "rollout_steps_per_s": n_prob * Kf * Hf / (float(ms.item()) * 1e-3)}
+    if rank == 0:
+        from oracle import catenary_oracle as orc
+        for j in (0, hi - lo - 1):
+            U = orc.sample_controls(7, np.arange(Kf), Hf, sigma, problem=lo + j)
+            po = orc.default_mpc_params(P1=tuple(poses[lo + j]))
+            J = orc.mpc_rollout_costs(po, U, prefs[j])
+            assert int(bi[j]) == int(np.argmin(J)), (j, int(bi[j]), int(np.argmin(J)))
+            assert abs(bc[j] - J.min()) <= 1e-9 * abs(J.min())
+        out["config5"]["oracle_spot_check"] = True
+        print(json.dumps(out))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
