@@ -12,5 +12,9 @@ from .geometry import (Catenary, catenary_shapes, lowest_point, rodrigues_rotati
 from .mpc import (circle_reference, default_mpc_params, make_params, make_problems, mpc_fleet_step,
                   mpc_sample_step, reduce_winners)
 from .controller import RecedingHorizonController, mpc_receding_horizon
+from .expr import (ExpressionError, ExpressionModel, compile_expression, integrate_second_order, load_equation_table,
+                   load_run)
+from .features import (build_clean_features, build_gamma_features, build_theta_features, extract_features16,
+                       feature_bank, load_and_resample_all, load_trajectory_csv, resample_linear, uniform_resample)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -1116,6 +1116,57 @@ int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_
 }
 
 // ---- roofline denominators --------------------------------------------------------------------------
+int cat_resample_linear_f64(void* ctx, int64_t n_in, const double* time_in, int32_t n_cols, const double* cols,
+                            int64_t n_out, const double* time_out, double* out) {
+  CTX();
+  NEED(n_in >= 2 && n_cols >= 1 && n_out >= 0 && time_in && cols);
+  if (n_out == 0) return CAT_OK;
+  NEED(time_out && out);
+  int rc = bind(c);
+  if (rc) return rc;
+  double *dti, *dc, *dto, *dout;
+  SCRATCH(SLOT_A, (size_t)n_in * sizeof(double), dti);
+  SCRATCH(SLOT_B, (size_t)n_in * n_cols * sizeof(double), dc);
+  SCRATCH(SLOT_C, (size_t)n_out * sizeof(double), dto);
+  SCRATCH(SLOT_D, (size_t)n_out * n_cols * sizeof(double), dout);
+  CU(cudaMemcpyAsync(dti, time_in, (size_t)n_in * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dc, cols, (size_t)n_in * n_cols * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dto, time_out, (size_t)n_out * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_resample_linear<double><<<nblk(n_out, 256), 256, 0, c->stream>>>(n_in, dti, n_cols, dc, n_out, dto, dout);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dout, (size_t)n_out * n_cols * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+int cat_feature_bank_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
+                         const double* time, const double* theta, const double* gamma, double L, double w,
+                         double* bank) {
+  CTX();
+  NEED(T >= 0 && L > 0);
+  if (T == 0) return CAT_OK;
+  NEED(P0 && P1 && V1 && time && theta && gamma && bank);
+  int rc = bind(c);
+  if (rc) return rc;
+  double *d3, *d1, *dB;
+  const size_t b3 = (size_t)T * 3 * sizeof(double), b1 = (size_t)T * sizeof(double);
+  SCRATCH(SLOT_A, 3 * b3, d3);
+  SCRATCH(SLOT_B, 3 * b1, d1);
+  SCRATCH(SLOT_C, (size_t)T * CAT_BANK_W * sizeof(double), dB);
+  CU(cudaMemcpyAsync(d3, P0, b3, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d3 + 3 * T, P1, b3, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d3 + 6 * T, V1, b3, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d1, time, b1, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d1 + T, theta, b1, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d1 + 2 * T, gamma, b1, cudaMemcpyHostToDevice, c->stream));
+  k_feature_bank<double><<<nblk(T, 128), 128, 0, c->stream>>>(T, d3, d3 + 3 * T, d3 + 6 * T, d1, d1 + T, d1 + 2 * T, L,
+                                                               w, kCLo, kCHi, dB);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(bank, dB, (size_t)T * CAT_BANK_W * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
 int cat_expr_eval_f64(void* ctx, int64_t n, int32_t n_features, const double* X, int32_t n_ops, const int32_t* ops,
                       int32_t n_consts, const double* consts, const double* mean, const double* scale, double* out) {
   CTX();

@@ -99,9 +99,13 @@ class EquationModel:
 
 
 def _integrate(model, x_input, time, y0, method, dtype, ctx):
+    if hasattr(model, "program") and hasattr(model, "integrate"):      # expr.ExpressionModel: run-time program
+        if np.dtype(dtype) != np.float64:
+            raise ValueError("run-time equation programs integrate in float64")
+        return model.integrate(x_input, time, y0, method="rk4" if method == 0 else "euler")
     ctx = ctx or default_context()
     if not isinstance(model, EquationModel):
-        raise TypeError("model must be an EquationModel (a generated PySR equation compiled into the library)")
+        raise TypeError("model must be an EquationModel (generated at build time) or an expr.ExpressionModel")
     dtype = np.dtype(dtype)
     X = np.ascontiguousarray(x_input, dtype)
     single = X.ndim == 2

@@ -1,0 +1,141 @@
+"""The reference's other feature layouts and its data ingest (rank 4) on the GPU.
+
+``feature_bank`` computes every per-row term once (cat_feature_bank_f64: kinematics, np.gradient acceleration,
+cable-relative surge/sway, the per-row catenary solve + tension the reference runs through
+``np.vectorize(brentq)`` at ~89 us/row); the builders below keep the reference's names, arguments and column
+orders and are column selections of that bank.  ``uniform_resample`` / ``load_and_resample_all`` keep
+main_fun.py:128-160's surface with the interpolation on the device.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import _lib
+from .context import default_context
+
+BANK_W = 32
+BANK = {"P1": slice(0, 3), "V1": slice(3, 6), "A1": slice(6, 9), "unit_rel": slice(9, 12), "dist_clip": 12,
+        "angle_proj": 13, "v_surge": 14, "v_sway": 15, "l": 16, "delta_H": 17, "C": 18, "T": 19,
+        "angle_proj_tanh": 20, "a1_dot_unitrel": 21, "a1_perp_norm": 22, "v1_norm": 23, "a1_norm": 24,
+        "acc_vel_ratio": 25, "theta": 26, "gamma": 27, "theta_prev": 28, "gamma_prev": 29, "dist": 30}
+
+P0_COLS = ["rod_end X", "rod_end Y", "rod_end Z"]
+P1_COLS = ["robot_cable_attach_point X", "robot_cable_attach_point Y", "robot_cable_attach_point Z"]
+V1_COLS = ["rob_cor_speed X", "rob_cor_speed Y", "rob_cor_speed Z"]
+TRAJECTORY_COLS = [f"br{r}_{n}" for r in (0, 1) for n in ("x", "y", "z", "phi", "theta", "psi", "u", "v", "w", "p",
+                                                           "q", "r")]         # Rov_traj_gen.py:133-134
+
+
+def experiment_columns(df):
+    """The experimental CSV schema (simple.py:16-35) -> contiguous arrays in the units the reference uses:
+    P0, P1 (T,3) in m (mm / 1000), V1 (T,3) in mm/s, time, theta, gamma (T,)."""
+    g = lambda k: np.asarray(df[k], np.float64)
+    stack = lambda ks: np.ascontiguousarray(np.stack([g(k) for k in ks], axis=1))
+    return (stack(P0_COLS) / 1000, stack(P1_COLS) / 1000, stack(V1_COLS), np.ascontiguousarray(g("Time")),
+            np.ascontiguousarray(g("Theta")), np.ascontiguousarray(g("Gamma")))
+
+
+def feature_bank(df, L=3.0, cable_wet_weight=1.521, ctx=None):
+    """(T, 32) term bank of an experiment DataFrame (or any mapping with the CSV's column names)."""
+    ctx = ctx or default_context()
+    P0, P1, V1, t, th, ga = experiment_columns(df)
+    bank = np.empty((t.shape[0], BANK_W))
+    ctx.check(ctx.lib.cat_feature_bank_f64(ctx.handle, t.shape[0], _lib.ptr(np.ascontiguousarray(P0)),
+                                           _lib.ptr(np.ascontiguousarray(P1)), _lib.ptr(V1), _lib.ptr(t),
+                                           _lib.ptr(th), _lib.ptr(ga), float(L), float(cable_wet_weight),
+                                           _lib.ptr(bank)))
+    return bank
+
+
+def _cols(bank, names):
+    parts = []
+    for n in names:
+        c = bank[:, BANK[n]]
+        parts.append(c if c.ndim == 2 else c[:, None])
+    return np.hstack(parts)
+
+
+def build_theta_features(df, L, cable_wet_weight, ctx=None):
+    """main_fun.py:267-340: [theta, v_surge, v_sway, l, delta_H, T, tanh(angle_proj), A1_y, |A1_perp|]."""
+    b = feature_bank(df, L, cable_wet_weight, ctx)
+    return np.hstack([_cols(b, ["theta", "v_surge", "v_sway", "l", "delta_H", "T", "angle_proj_tanh"]),
+                      b[:, 7:8], _cols(b, ["a1_perp_norm"])])
+
+
+def build_gamma_features(df, L, cable_wet_weight, ctx=None):
+    """main_fun.py:342-415: [gamma, v_sway, v_surge, l, delta_H, T, tanh(angle_proj), A1_y, |A1_perp|]."""
+    b = feature_bank(df, L, cable_wet_weight, ctx)
+    return np.hstack([_cols(b, ["gamma", "v_sway", "v_surge", "l", "delta_H", "T", "angle_proj_tanh"]),
+                      b[:, 7:8], _cols(b, ["a1_perp_norm"])])
+
+
+def build_clean_features(df, ctx=None):
+    """main_fun.py:197-265 (13 columns)."""
+    b = feature_bank(df, ctx=ctx)
+    v1n, a1n = b[:, 23:24], b[:, 24:25]
+    return np.hstack([_cols(b, ["v_surge", "a1_dot_unitrel", "v_sway", "a1_perp_norm", "v1_norm", "a1_norm",
+                                "acc_vel_ratio"]), v1n ** 2, a1n ** 2,
+                      _cols(b, ["dist_clip", "angle_proj_tanh"]), b[:, 4:5], b[:, 7:8]])
+
+
+def extract_features16(df, ctx=None):
+    """main_fun.extract_features (main_fun.py:166-193): [P1, V1, A1, unit_rel, tension, angle_proj, theta, gamma]
+    (the 18-column variant with the previous angles is dynamics.extract_features, simple.py:15-41)."""
+    b = feature_bank(df, ctx=ctx)
+    return _cols(b, ["P1", "V1", "A1", "unit_rel", "dist_clip", "angle_proj", "theta", "gamma"])
+
+
+def resample_linear(time_in, values, time_out, ctx=None):
+    """scipy interp1d(kind='linear', fill_value='extrapolate') of the columns of ``values`` (n_in, n_cols)."""
+    ctx = ctx or default_context()
+    ti = np.ascontiguousarray(time_in, np.float64)
+    v = np.ascontiguousarray(values, np.float64)
+    if v.ndim == 1:
+        v = v[:, None]
+    if ti.ndim != 1 or v.shape[0] != ti.shape[0] or ti.shape[0] < 2:
+        raise ValueError("time_in (n_in >= 2,) and values (n_in, n_cols) expected")
+    to = np.ascontiguousarray(time_out, np.float64)
+    out = np.empty((to.shape[0], v.shape[1]))
+    ctx.check(ctx.lib.cat_resample_linear_f64(ctx.handle, ti.shape[0], _lib.ptr(ti), v.shape[1], _lib.ptr(v),
+                                              to.shape[0], _lib.ptr(to), _lib.ptr(out)))
+    return out
+
+
+UNIFORM_DT = 0.05      # main_fun.py:127
+
+
+def uniform_resample(df, dt=UNIFORM_DT, ctx=None):
+    """main_fun.py:128-145: every column linearly interpolated onto np.arange(t0, t_end, dt); returns a
+    DataFrame with 'Time' first, as the reference does."""
+    import pandas as pd
+    if "Time" not in df.columns:
+        raise ValueError("Missing 'Time' column in dataset.")
+    time_orig = df["Time"].values
+    time_uniform = np.arange(time_orig[0], time_orig[-1], dt)
+    others = [c for c in df.columns if c != "Time"]
+    out = resample_linear(time_orig, df[others].values, time_uniform, ctx)
+    data = {"Time": time_uniform}
+    data.update({c: out[:, j] for j, c in enumerate(others)})
+    return pd.DataFrame(data)
+
+
+def load_and_resample_all(file_list, dt=UNIFORM_DT, ctx=None):
+    """main_fun.py:148-159: read each CSV, drop rows without Theta/Gamma/Time, resample independently, concat."""
+    import pandas as pd
+    dfs = []
+    for f in file_list:
+        df = pd.read_csv(f)
+        if {"Theta", "Gamma", "Time"}.issubset(df.columns):
+            dfs.append(uniform_resample(df.dropna(subset=["Theta", "Gamma", "Time"]), dt, ctx))
+        else:
+            print(f"[WARNING] Missing columns in {f}, skipping.")
+    return pd.concat(dfs, ignore_index=True)
+
+
+def load_trajectory_csv(path):
+    """The 24-column trajectory CSV of Rov_traj_gen.py:133-139 -> (2, T, 12) float64: per vehicle
+    [x, y, z, phi, theta, psi, u, v, w, p, q, r]."""
+    a = np.loadtxt(path, delimiter=",", skiprows=1, ndmin=2)
+    if a.shape[1] != 24:
+        raise ValueError(f"{path}: expected 24 columns, found {a.shape[1]}")
+    return np.ascontiguousarray(a.reshape(a.shape[0], 2, 12).transpose(1, 0, 2))

@@ -216,6 +216,25 @@ CAT_API int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx
  * the ranks all-gather it), out = one such pair. */
 CAT_API int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_t* out);
 
+/* replaces uniform_resample (main_fun.py:128-145): scipy interp1d(kind='linear', fill_value='extrapolate') of every
+ * column onto a new time grid.  time_in (n_in, increasing), cols (n_in, n_cols) row-major like DataFrame.values,
+ * time_out (n_out) -> out (n_out, n_cols); bit-identical to scipy 1.18's interp1d._call_linear. */
+CAT_API int cat_resample_linear_f64(void* ctx, int64_t n_in, const double* time_in, int32_t n_cols,
+                                    const double* cols, int64_t n_out, const double* time_out, double* out);
+
+/* feature term bank: every per-row term of the reference's other feature builders --
+ * build_theta_features / build_gamma_features (main_fun.py:267-415), build_clean_features (main_fun.py:197-265),
+ * extract_features (main_fun.py:166-193) -- in one pass, including the per-row solve_catenary + tension that the
+ * reference runs through np.vectorize(brentq).  Inputs as cat_features_f64; L cable length (m), w cable wet
+ * weight (N, test_cluster.py:23).  bank (T, 32) row-major:
+ *  0-2 P1 | 3-5 V1 | 6-8 A1 = np.gradient(V1, time) | 9-11 unit_rel | 12 clip(|rel|, 1e-5, 10) | 13 angle_proj |
+ *  14 v_surge = V1.unit_rel | 15 v_sway = |V1 x unit_rel| | 16 l | 17 dH | 18 C | 19 T = (w/L) l / (2 sinh(C l / 2)),
+ *  nan C -> (w/L) l / 2 | 20 tanh(angle_proj) | 21 A1.unit_rel | 22 |A1 - (A1.unit_rel) unit_rel| | 23 |V1| | 24 |A1| |
+ *  25 |A1| / (|V1| + 1e-8) | 26 theta | 27 gamma | 28 theta_prev | 29 gamma_prev | 30 |rel| | 31 0 */
+CAT_API int cat_feature_bank_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
+                                 const double* time, const double* theta, const double* gamma, double L, double w,
+                                 double* bank);
+
 /* ---- run-time equation programs ----------------------------------
  * Any PySR hall-of-fame row -- the ~3,900 equations under the reference's cluster_run/outputs and outputs
  * directories, or a model the user retrains (simple.py:60-75) -- evaluated without rebuilding the library:

@@ -726,3 +726,83 @@ def integrate_second_order(pred, time, y0):
         dt = time[i] - time[i - 1]
         y[i] = y[i - 1] + rate[i - 1] * dt
     return y, rate
+
+
+# --------------------------------------------------------------------------
+# other feature layouts + resampler: checker for features.py
+# --------------------------------------------------------------------------
+def _experiment_arrays(df):
+    g = lambda k: np.asarray(df[k], np.float64)
+    P0 = np.stack([g("rod_end X"), g("rod_end Y"), g("rod_end Z")], 1) / 1000
+    P1 = np.stack([g("robot_cable_attach_point X"), g("robot_cable_attach_point Y"),
+                   g("robot_cable_attach_point Z")], 1) / 1000
+    V1 = np.stack([g("rob_cor_speed X"), g("rob_cor_speed Y"), g("rob_cor_speed Z")], 1)
+    t = g("Time")
+    A1 = np.stack([np.gradient(V1[:, j], t) for j in range(3)], 1)
+    return P0, P1, V1, A1, t, g("Theta"), g("Gamma")
+
+
+def feature_terms(df, L=3.0, cable_wet_weight=1.521):
+    """Every per-row term of main_fun.py:167-415 restated (same operations, same association)."""
+    P0, P1, V1, A1, t, th, ga = _experiment_arrays(df)
+    rel = P1 - P0
+    nrm = np.linalg.norm(rel, axis=1, keepdims=True)
+    unit = rel / (nrm + 1e-8)                                   # main_fun.py:283
+    v_surge = np.sum(V1 * unit, axis=1, keepdims=True)          # :286
+    v_sway = np.linalg.norm(np.cross(V1, unit), axis=1, keepdims=True)   # :287
+    l = np.linalg.norm(rel[:, :2], axis=1, keepdims=True)       # :290
+    dH = rel[:, 2].reshape(-1, 1)                               # :291
+    wl = cable_wet_weight / L                                   # :300
+    C = solve_catenary(l.ravel(), dH.ravel(), L).reshape(-1, 1)  # :301
+    with np.errstate(all="ignore"):
+        T = (wl * l) / (2 * np.sinh(C * l / 2))                 # :302
+    T = np.where(np.isnan(T), wl * l / 2, T)                    # :303
+    v1n = np.linalg.norm(V1, axis=1, keepdims=True)
+    ap = np.clip(v_surge / (v1n + 1e-8), -1, 1)                 # :313
+    a_dot = np.sum(A1 * unit, axis=1, keepdims=True)
+    a_perp = A1 - a_dot * unit                                  # :317-318
+    a1n = np.linalg.norm(A1, axis=1, keepdims=True)
+    return dict(P1=P1, V1=V1, A1=A1, unit_rel=unit, dist_clip=np.clip(nrm, 1e-5, 10), angle_proj=ap,
+                v_surge=v_surge, v_sway=v_sway, l=l, delta_H=dH, C=C, T=T, angle_proj_tanh=np.tanh(ap),
+                a1_dot_unitrel=a_dot, a1_perp_norm=np.linalg.norm(a_perp, axis=1, keepdims=True), v1_norm=v1n,
+                a1_norm=a1n, acc_vel_ratio=a1n / (v1n + 1e-8), theta=th.reshape(-1, 1), gamma=ga.reshape(-1, 1))
+
+
+def build_theta_features(df, L, cable_wet_weight):
+    """main_fun.py:267-340."""
+    f = feature_terms(df, L, cable_wet_weight)
+    return np.hstack([f["theta"], f["v_surge"], f["v_sway"], f["l"], f["delta_H"], f["T"], f["angle_proj_tanh"],
+                      f["A1"][:, 1:2], f["a1_perp_norm"]])
+
+
+def build_gamma_features(df, L, cable_wet_weight):
+    """main_fun.py:344-415."""
+    f = feature_terms(df, L, cable_wet_weight)
+    return np.hstack([f["gamma"], f["v_sway"], f["v_surge"], f["l"], f["delta_H"], f["T"], f["angle_proj_tanh"],
+                      f["A1"][:, 1:2], f["a1_perp_norm"]])
+
+
+def build_clean_features(df):
+    """main_fun.py:197-265."""
+    f = feature_terms(df)
+    return np.hstack([f["v_surge"], f["a1_dot_unitrel"], f["v_sway"], f["a1_perp_norm"], f["v1_norm"], f["a1_norm"],
+                      f["acc_vel_ratio"], f["v1_norm"] ** 2, f["a1_norm"] ** 2, f["dist_clip"], f["angle_proj_tanh"],
+                      f["V1"][:, 1:2], f["A1"][:, 1:2]])
+
+
+def extract_features16(df):
+    """main_fun.py:167-193."""
+    f = feature_terms(df)
+    return np.hstack([f["P1"], f["V1"], f["A1"], f["unit_rel"], f["dist_clip"], f["angle_proj"], f["theta"],
+                      f["gamma"]])
+
+
+def resample_linear(time_in, values, time_out):
+    """scipy interp1d(kind='linear', fill_value='extrapolate') restated (main_fun.py:139-140; scipy 1.18
+    interp1d._call_linear): searchsorted, clip to [1, n-1], ((x_new-x_lo)/(x_hi-x_lo)) y_hi + ((x_hi-x_new)/(x_hi-x_lo)) y_lo."""
+    x = np.asarray(time_in, np.float64)
+    y = np.asarray(values, np.float64)
+    xn = np.asarray(time_out, np.float64)
+    idx = np.clip(np.searchsorted(x, xn), 1, len(x) - 1)
+    lo, hi = idx - 1, idx
+    return ((xn - x[lo]) / (x[hi] - x[lo]))[:, None] * y[hi] + ((x[hi] - xn) / (x[hi] - x[lo]))[:, None] * y[lo]
