@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(256) k_solve_param(long long n, const T* __res
 #ifndef CAT_SHAPE_MINB
 #define CAT_SHAPE_MINB 5    // resident blocks per SM the register budget is cut for
 #endif
-#define CAT_SHAPE_RESEED 8     // re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
+#define CAT_SHAPE_RESEED 8     // (power of two) re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
 
 template <typename T> struct CatShapeSpan {
   T two_u;      // C * l
@@ -53,27 +53,28 @@ template <typename T> struct CatShapeMap {
   T a[3], b[3];   // sample = A + s a + zoff b
 };
 
-// Shared-memory record of one configuration, sized by what `which` asks for (occupancy: the full record is
-// 328 B in fp64, the final-curve-only record 136 B):  A[3] | spans needed x 7 | maps requested x 6, as T values
-// (valid is stored as 0/1 in T).  The stride is made odd so the 128 phase-1 writers hit distinct banks.
-#define CAT_SHAPE_SPAN_W 7
-#define CAT_SHAPE_MAP_W 6
-__host__ __device__ __forceinline__ int cat_shape_record_len(int which) {
+// Shared-memory record of one configuration, sized by what `which` asks for (the full record is 352 B in fp64,
+// the final-curve-only record 144 B), as PAIRS of T so that phase 2 reads it with 16-byte LDS (fp64):
+//   (A0,A1) (A2,-) | per needed span: (two_u,v_low) (inv_C,cm_low) (cmD,shD) (valid,-) | per requested map:
+//   (a0,a1) (a2,b0) (b1,b2).  Phase-2 reads are warp-uniform (broadcast), so only alignment matters there.
+#define CAT_SHAPE_SPAN_W 4   // pairs
+#define CAT_SHAPE_MAP_W 3    // pairs
+template <typename T> struct alignas(2 * sizeof(T)) CatPair {
+  T x, y;
+};
+__host__ __device__ __forceinline__ int cat_shape_record_len(int which) {   // in pairs
   const int nspan = ((which & CAT_OUT_ORIGINAL) ? 1 : 0) + ((which & ~CAT_OUT_ORIGINAL & 15) ? 1 : 0);
   int nmap = 0;
   for (int m = 0; m < 4; ++m) nmap += (which >> m) & 1;
-  return (3 + CAT_SHAPE_SPAN_W * nspan + CAT_SHAPE_MAP_W * nmap) | 1;
+  return 2 + CAT_SHAPE_SPAN_W * nspan + CAT_SHAPE_MAP_W * nmap;
 }
 
 template <typename T>
-__device__ __forceinline__ void cat_shape_store_span(T* r, const CatShapeSpan<T>& sp) {
-  r[0] = sp.two_u;
-  r[1] = sp.v_low;
-  r[2] = sp.inv_C;
-  r[3] = sp.cm_low;
-  r[4] = sp.cmD;
-  r[5] = sp.shD;
-  r[6] = T(sp.valid);
+__device__ __forceinline__ void cat_shape_store_span(CatPair<T>* r, const CatShapeSpan<T>& sp) {
+  r[0] = CatPair<T>{sp.two_u, sp.v_low};
+  r[1] = CatPair<T>{sp.inv_C, sp.cm_low};
+  r[2] = CatPair<T>{sp.cmD, sp.shD};
+  r[3] = CatPair<T>{T(sp.valid), T(0)};
 }
 
 template <typename T, typename M>
@@ -132,10 +133,10 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
                                                           T* __restrict__ C_out, unsigned char* __restrict__ valid) {
   typedef CatMath<T> M;
   extern __shared__ __align__(16) unsigned char cat_shape_smem[];
-  T* const rec = reinterpret_cast<T*>(cat_shape_smem);
+  CatPair<T>* const rec = reinterpret_cast<CatPair<T>*>(cat_shape_smem);
   const int rec_len = cat_shape_record_len(which);
   const bool need0 = (which & CAT_OUT_ORIGINAL) != 0;
-  const int span1_at = 3 + (need0 ? CAT_SHAPE_SPAN_W : 0);
+  const int span1_at = 2 + (need0 ? CAT_SHAPE_SPAN_W : 0);
   const int maps_at = span1_at + ((which & ~CAT_OUT_ORIGINAL & 15) ? CAT_SHAPE_SPAN_W : 0);
   const long long base = (long long)blockIdx.x * CAT_SHAPE_TILE;
   const int tid = threadIdx.x;
@@ -148,13 +149,12 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
       CatShapeSpan<T> sp[2];
       CatShapeMap<T> map[4];
     } c;
-    T* const r = rec + tid * rec_len;
+    CatPair<T>* const r = rec + tid * rec_len;
     const T a[3] = {A[3 * i], A[3 * i + 1], A[3 * i + 2]};
     const T b[3] = {B[3 * i], B[3 * i + 1], B[3 * i + 2]};
     const T Li = L[i * L_stride];
-    r[0] = a[0];
-    r[1] = a[1];
-    r[2] = a[2];
+    r[0] = CatPair<T>{a[0], a[1]};
+    r[1] = CatPair<T>{a[2], T(0)};
     const T conn[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]};
     const T ez[3] = {T(0), T(0), T(1)};
     const T zero3[3] = {T(0), T(0), T(0)};
@@ -219,18 +219,16 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
       cat_shape_map_set<T>(c.map[3], a3, b3);
     }
     if (valid) valid[i] = (unsigned char)vbits;
-    if (need0) cat_shape_store_span<T>(r + 3, c.sp[0]);
+    if (need0) cat_shape_store_span<T>(r + 2, c.sp[0]);
     if (need_rot) cat_shape_store_span<T>(r + span1_at, c.sp[1]);
     int slot = 0;
 #pragma unroll
     for (int m = 0; m < 4; ++m) {
       if (!(which & (1 << m))) continue;
-      T* rm = r + maps_at + CAT_SHAPE_MAP_W * slot;
-#pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        rm[j] = c.map[m].a[j];
-        rm[3 + j] = c.map[m].b[j];
-      }
+      CatPair<T>* rm = r + maps_at + CAT_SHAPE_MAP_W * slot;
+      rm[0] = CatPair<T>{c.map[m].a[0], c.map[m].a[1]};
+      rm[1] = CatPair<T>{c.map[m].a[2], c.map[m].b[0]};
+      rm[2] = CatPair<T>{c.map[m].b[1], c.map[m].b[2]};
       ++slot;
     }
   }
@@ -239,57 +237,64 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
   const int n_here = (int)((n - base < CAT_SHAPE_TILE) ? (n - base) : CAT_SHAPE_TILE);
   const int lane = tid & 31, warp = tid >> 5, n_warps = CAT_SHAPE_TILE / 32;
   const long long blk = n * (long long)n_pts * 3;   // elements per output block
+  // output-block offset and record offset of each requested map (slot = rank of m among the requested ones)
+  long long m_out[4];
+  int m_rec[4];
+  {
+    int slot = 0;
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      m_out[m] = slot * blk;
+      m_rec[m] = maps_at + CAT_SHAPE_MAP_W * slot;
+      slot += (which >> m) & 1;
+    }
+  }
+  const T lane_f = T(lane);
+  const int n_hops = (n_pts + 31) >> 5;
   for (int ci = warp; ci < n_here; ci += n_warps) {
-    const T* const r = rec + ci * rec_len;
-    const T A0 = r[0], A1 = r[1], A2 = r[2];
-    T* const o_cfg = out + (base + ci) * (long long)n_pts * 3;
+    const CatPair<T>* const r = rec + ci * rec_len;
+    const CatPair<T> rA = r[0];
+    const T A0 = rA.x, A1 = rA.y, A2 = r[1].x;
+    T* const o_lane = out + ((base + ci) * (long long)n_pts + lane) * 3;
 #pragma unroll
     for (int spi = 0; spi < 2; ++spi) {
-      const int outs = spi == 0 ? (which & CAT_OUT_ORIGINAL) : (which & ~CAT_OUT_ORIGINAL);
+      const int outs = spi == 0 ? (which & CAT_OUT_ORIGINAL) : (which & ~CAT_OUT_ORIGINAL & 15);
       if (!outs) continue;
-      const T* const rs = r + (spi == 0 ? 3 : span1_at);
-      CatShapeSpan<T> sp;
-      sp.two_u = rs[0];
-      sp.v_low = rs[1];
-      sp.inv_C = rs[2];
-      sp.cm_low = rs[3];
-      sp.cmD = rs[4];
-      sp.shD = rs[5];
-      sp.valid = rs[6] != T(0);
+      const CatPair<T>* const rs = r + (spi == 0 ? 2 : span1_at);
+      const CatPair<T> s0 = rs[0], s1 = rs[1], s2 = rs[2];
+      const T two_u = s0.x, v_low = s0.y, inv_C = s1.x, cm_low = s1.y, cmD = s2.x, shD = s2.y;
+      const bool ok = rs[3].x != T(0);
       T cm = T(0), sh = T(0);
-      int hops = 0;
-      for (int pt = lane; pt < n_pts; pt += 32, ++hops) {
-        const bool last = pt == n_pts - 1;
-        const T s = last ? T(1) : T(pt) * inv_nm1;
-        T zoff = T(0);
-        if (sp.valid) {
-          if (hops % CAT_SHAPE_RESEED == 0) {
-            const T t = sp.two_u * s - sp.v_low;
-            T sm;
-            cat_hyp<T, M>(M::abs_(t), sm, cm, sh);
-            sh = t < T(0) ? -sh : sh;
-          } else {
-            // cosh(t + D) - 1 = cm + cm cmD + cmD + sh shD ;  sinh(t + D) = sh + sh cmD + (cm + 1) shD
-            const T cn = M::fma_(cm, sp.cmD, cm) + M::fma_(sh, sp.shD, sp.cmD);
-            const T sn = M::fma_(sh, sp.cmD, sh) + M::fma_(cm, sp.shD, sp.shD);
-            cm = cn;
-            sh = sn;
-          }
-          zoff = (cm - sp.cm_low) * sp.inv_C;
+      T ptf = lane_f;          // T(pt), stepped exactly
+      T* o = o_lane;           // &out[cfg][pt][0] of the first requested block, stepped by 32 points
+      // uniform trip count (idle lanes of the last hop compute and do not store): no divergent loop exit
+      for (int hop = 0; hop < n_hops; ++hop, ptf += T(32), o += 96) {
+        const int pt = lane + 32 * hop;
+        const T s = (pt == n_pts - 1) ? T(1) : ptf * inv_nm1;
+        if ((hop & (CAT_SHAPE_RESEED - 1)) == 0) {   // warp-uniform
+          const T t = two_u * s - v_low;
+          T sm;
+          cat_hyp<T, M>(M::abs_(t), sm, cm, sh);
+          sh = t < T(0) ? -sh : sh;
+        } else {
+          // cosh(t + D) - 1 = cm + cm cmD + cmD + sh shD ;  sinh(t + D) = sh + sh cmD + (cm + 1) shD
+          const T cn = M::fma_(cm, cmD, cm) + M::fma_(sh, shD, cmD);
+          const T sn = M::fma_(sh, cmD, sh) + M::fma_(cm, shD, shD);
+          cm = cn;
+          sh = sn;
         }
-        T* o = o_cfg + (long long)pt * 3;
-        int slot = 0;
+        const T zoff = ok ? (cm - cm_low) * inv_C : T(0);   // chord fallback: spans outside the solve domain
+        if (pt >= n_pts) continue;
+        // sample = A + s a + zoff b as two FMAs per coordinate
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
-          if (!(which & (1 << m))) continue;
-          if ((m == 0) == (spi == 0)) {
-            const T* mp = r + maps_at + CAT_SHAPE_MAP_W * slot;   // a[3] | b[3]
-            T* om = o + slot * blk;
-            om[0] = A0 + M::fma_(zoff, mp[3], s * mp[0]);
-            om[1] = A1 + M::fma_(zoff, mp[4], s * mp[1]);
-            om[2] = A2 + M::fma_(zoff, mp[5], s * mp[2]);
-          }
-          ++slot;
+          if ((m == 0) != (spi == 0) || !(outs & (1 << m))) continue;
+          const CatPair<T>* mp = r + m_rec[m];   // (a0,a1) (a2,b0) (b1,b2)
+          const CatPair<T> p0 = mp[0], p1 = mp[1], p2 = mp[2];
+          T* om = o + m_out[m];
+          om[0] = M::fma_(zoff, p1.y, M::fma_(s, p0.x, A0));
+          om[1] = M::fma_(zoff, p2.x, M::fma_(s, p0.y, A1));
+          om[2] = M::fma_(zoff, p2.y, M::fma_(s, p1.x, A2));
         }
       }
     }

@@ -146,7 +146,7 @@ template <typename T>
 int shape_dev_on(CatCtx* c, cudaStream_t st, int64_t n, const T* A, const T* B, const T* L, int64_t L_stride,
                  const T* theta, const T* gamma, int32_t n_pts, int32_t which, T* out, T* C_out, uint8_t* valid) {
   if (n == 0) return CAT_OK;
-  const size_t smem = (size_t)CAT_SHAPE_TILE * cat_shape_record_len(which) * sizeof(T);
+  const size_t smem = (size_t)CAT_SHAPE_TILE * cat_shape_record_len(which) * 2 * sizeof(T);
   k_shape<T><<<nblk(n, CAT_SHAPE_TILE), CAT_SHAPE_TILE, smem, st>>>(n, A, B, L, L_stride, theta, gamma, n_pts, which,
                                                                  T(kCLo), T(kCHi), out, C_out, valid);
   LAUNCHED();
