@@ -34,6 +34,16 @@ METRIC = "rk4_tether_rollout_steps_per_sec"
 UNIT = "rollout-steps/s"
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """Write the result line to the process's real stdout (see main)."""
+    fh = _REAL_STDOUT or sys.stdout
+    fh.write(line + "\n")
+    fh.flush()
+
+
 def config3_inputs(K, H, seed, sigma):
     """Controls ~ N(0, diag(sigma^2)) clipped to 3 sigma, SoA [H][3][K]."""
     rng = np.random.default_rng(seed)
@@ -119,7 +129,7 @@ def run_reference(args):
         dt = time.perf_counter() - t0
     v = K * H * args.steps / dt
     sample = f"{K} of 65536 candidates x H={H} per step (oracle port, NumPy fp64, fork pool over candidate chunks)"
-    print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+    emit(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
                       "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
                       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                       "data": "synthetic", "config": {"workload": "config3", "candidates": K, "horizon": H,
@@ -302,6 +312,26 @@ def run_ours(args):
                 "flops_per_rollout_step": FLOPS_PER_ROLLOUT_STEP,
                 "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
+    # ---- closed loop: the receding-horizon controller (device-resident, one CUDA graph per control step) ----
+    ctx.set_stream(None)
+    closed = {}
+    for mode in ("argmin", "mppi"):
+        n_ctrl = 60
+        rh = cb.RecedingHorizonController(cb.default_mpc_params(w_trk=1e3, w_du=1e-6),
+                                          cb.circle_reference(n_ctrl + H, p["dt"], period=4.0), K, H,
+                                          sigma=(40.0, 40.0, 20.0), u_max=(300.0, 300.0, 300.0), mode=mode, lam=0.02,
+                                          seed=3, max_steps=n_ctrl, ctx=ctx)
+        rh.run(10)
+        ctx.sync()
+        ctx.timer_start()
+        rh.run(n_ctrl - 10)
+        ms = ctx.timer_stop_ms() / (n_ctrl - 10)
+        log = rh.read()["log"][0]
+        rh.close()
+        closed[mode] = {"ms_per_control_step": ms, "rollout_steps_per_s": K * H / (ms * 1e-3),
+                        "kernels_per_step": 3 if mode == "mppi" else 2, "host_bytes_per_step": 0,
+                        "final_tracking_error_m": float(np.linalg.norm(
+                            log[-1, :3] - cb.circle_reference(n_ctrl + H, p["dt"], period=4.0)[n_ctrl - 1]))}
     # ---- CPU baseline: the oracle port on this box's host cores, bounded sample ----
     from oracle import catenary_oracle as orc
     Ks = 16384
@@ -323,8 +353,8 @@ def run_ours(args):
                       "controls": "explicit fp64 SoA [H][3][K]", "exchange": "nccl all_gather 16 B/rank + device fold on a side stream, double-buffered" if world > 1 else "none",
                       "l2": "3 rotating control sets (236 MB) > 126 MB L2"},
            "p50_ms": lat[len(lat) // 2], "p99_ms": lat[int(len(lat) * 0.99)], "latency_samples": len(lat),
-           "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
-    print(json.dumps(out))
+           "clocks": clocks, "e2e": e2e, "closed_loop": closed, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+    emit(json.dumps(out))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -337,6 +367,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
+    # stdout carries exactly ONE line (the JSON): libraries that write to fd 1 (NCCL prints its version banner there
+    # on communicator creation) are sent to stderr, and the JSON goes to the saved descriptor at the end.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         if args.steps > 20:
             args.steps = 20                     # each CPU step is ~1 s of all-core work; keep the arm to minutes
