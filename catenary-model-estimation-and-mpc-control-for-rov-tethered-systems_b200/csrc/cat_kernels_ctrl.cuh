@@ -13,6 +13,7 @@
 struct CatCtrlDev {
   int mode;        // CAT_CTRL_*
   int max_steps;   // log capacity
+  int slices;      // MPPI: candidate slices per horizon step (grid.z of k_ctrl_mppi), >= 1
   double lambda;
 };
 
@@ -40,32 +41,38 @@ __device__ __forceinline__ void cat_block_sum4(double (&v)[4]) {
 }
 
 // MPPI blend: u_star[prob][h][:] = sum_k w_k u_k[h] / sum_k w_k, w_k = exp(-(J_k - Jmin)/lambda), NaN J -> 0.
-// grid (H, n_problems), 256 threads; the candidates' controls are regenerated from the Philox counter.
+// grid (H, n_problems, slices), 256 threads: block (h, prob, z) sums slice z of the candidates into
+// partial[prob][h][z][4] = (sum w u_x, sum w u_y, sum w u_z, sum w); k_ctrl_advance adds the slices in order.
+// The candidates' controls are regenerated from the Philox counter, not stored.
 template <typename T>
 __global__ void __launch_bounds__(256) k_ctrl_mppi(const CatMpcDev<T> q, const CatCtrlDev x,
                                                    const T* __restrict__ costs,
                                                    const double* __restrict__ best_cost,
                                                    const long long* __restrict__ best_idx,
-                                                   double* __restrict__ u_star) {
+                                                   double* __restrict__ partial) {
   typedef CatMath<T> M;
-  const int h = blockIdx.x, prob = blockIdx.y;
+  const int h = blockIdx.x, prob = blockIdx.y, z = blockIdx.z;
   const unsigned long long seed_eff = q.seed + (unsigned long long)(*q.step);
   const double jmin = best_cost[prob];
-  double* out = u_star + ((long long)prob * q.H + h) * 3;
-  if (!(jmin == jmin)) {   // NaN winner: fall back to the best candidate itself
+  double* out = partial + (((long long)prob * q.H + h) * x.slices + z) * 4;
+  if (!(jmin == jmin)) {   // NaN winner: fall back to the best candidate itself (weight 1 in slice 0)
     if (threadIdx.x == 0) {
-      T u[3];
-      cat_nominal_control<T, M>(q, seed_eff, prob, best_idx[prob], h, u);
+      T u[3] = {T(0), T(0), T(0)};
+      if (z == 0) cat_nominal_control<T, M>(q, seed_eff, prob, best_idx[prob], h, u);
       out[0] = (double)u[0];
       out[1] = (double)u[1];
       out[2] = (double)u[2];
+      out[3] = z == 0 ? 1.0 : 0.0;
     }
     return;
   }
+  const long long per = ((q.K + x.slices - 1) / x.slices + 255) / 256 * 256;
+  const long long k_lo = (long long)z * per;
+  const long long k_hi = k_lo + per < q.K ? k_lo + per : q.K;
   const double inv_l = -1.0 / x.lambda;
   double acc[4] = {0.0, 0.0, 0.0, 0.0};
   const T* jc = costs + (long long)prob * q.K;
-  for (long long k = threadIdx.x; k < q.K; k += blockDim.x) {
+  for (long long k = k_lo + threadIdx.x; k < k_hi; k += blockDim.x) {
     const double j = (double)jc[k];
     double w = exp((j - jmin) * inv_l);
     if (!(j == j)) w = 0.0;
@@ -78,9 +85,10 @@ __global__ void __launch_bounds__(256) k_ctrl_mppi(const CatMpcDev<T> q, const C
   }
   cat_block_sum4(acc);
   if (threadIdx.x == 0) {
-    out[0] = acc[0] / acc[3];
-    out[1] = acc[1] / acc[3];
-    out[2] = acc[2] / acc[3];
+    out[0] = acc[0];
+    out[1] = acc[1];
+    out[2] = acc[2];
+    out[3] = acc[3];
   }
 }
 
@@ -172,10 +180,17 @@ __global__ void __launch_bounds__(64) k_ctrl_advance(const CatMpcDev<T> q, const
   const long long bi = best_idx[prob];
   for (int h = threadIdx.x; h < q.H; h += blockDim.x) {
     if (x.mode == CAT_CTRL_MPPI) {
-      const double* us = u_star + ((long long)prob * q.H + h) * 3;
-      s_u[3 * h + 0] = us[0];
-      s_u[3 * h + 1] = us[1];
-      s_u[3 * h + 2] = us[2];
+      const double* ps = u_star + ((long long)prob * q.H + h) * x.slices * 4;   // slice partial sums
+      double a0 = ps[0], a1 = ps[1], a2 = ps[2], aw = ps[3];
+      for (int z = 1; z < x.slices; ++z) {
+        a0 += ps[4 * z + 0];
+        a1 += ps[4 * z + 1];
+        a2 += ps[4 * z + 2];
+        aw += ps[4 * z + 3];
+      }
+      s_u[3 * h + 0] = a0 / aw;
+      s_u[3 * h + 1] = a1 / aw;
+      s_u[3 * h + 2] = a2 / aw;
     } else {
       T u[3];
       cat_nominal_control<T, M>(q, seed_eff, prob, bi, h, u);

@@ -29,6 +29,7 @@ struct CatCtx {
   cudaStream_t aux_stream;    // second lane of the chunked shape pipeline
   cudaStream_t stream;        // stream in use (own_stream or a caller-owned one)
   cudaEvent_t ev0, ev1, ev_aux;
+  cudaEvent_t ev_chunk[8];    // H2D chunk k of the pipelined host MPC step is on the device
   std::string err;
   int64_t launches;
   void* slot[N_SLOTS];
@@ -396,9 +397,47 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   if (costs) SCRATCH(SLOT_E, np * (size_t)p->K * sizeof(T), d_costs);
   CU(cudaMemcpyAsync(d_prob, problems, np * sizeof(CatMpcProblem), cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemcpyAsync(d_ref, p_ref, np * (size_t)p->H * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  if (!rng) CU(cudaMemcpyAsync(d_ctl, controls, n_ctl * sizeof(T), cudaMemcpyHostToDevice, c->stream));
-  rc = mpc_step_dev<T>(c, p, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs);
-  if (rc) return rc;
+  if (!rng && np == 1 && p->K >= 32768) {
+    // One problem, explicit controls (config 3: 78.6 MB): the step is PCIe-bound, so the candidates go up in 8
+    // chunks on the aux stream and chunk i's rollout overlaps chunk i+1's copy; the chunk winners fold on the
+    // device in candidate order (same total order as one launch: lowest cost, then lowest global index).
+    const int NC = 8;
+    CatMpcDev<T> q;
+    rc = mpc_fill<T>(c, p, q);
+    if (rc) return rc;
+    long long* d_pairs;
+    SCRATCH(SLOT_F, (size_t)NC * 16, d_pairs);
+    const bool aos = (p->flags & CAT_MPC_CONTROLS_AOS) != 0;
+    const long long K = p->K, H3 = 3LL * p->H;
+    int used = 0;
+    for (int i = 0; i < NC; ++i) {
+      const long long k0 = ((K * i / NC) + 127) / 128 * 128;
+      long long k1 = (i == NC - 1) ? K : ((K * (i + 1) / NC) + 127) / 128 * 128;
+      if (k1 > K) k1 = K;
+      if (k1 <= k0) continue;
+      if (aos)
+        CU(cudaMemcpyAsync(d_ctl + k0 * H3, controls + k0 * H3, (size_t)(k1 - k0) * H3 * sizeof(T),
+                           cudaMemcpyHostToDevice, c->aux_stream));
+      else
+        CU(cudaMemcpy2DAsync(d_ctl + k0, (size_t)K * sizeof(T), controls + k0, (size_t)K * sizeof(T),
+                             (size_t)(k1 - k0) * sizeof(T), (size_t)H3, cudaMemcpyHostToDevice, c->aux_stream));
+      CU(cudaEventRecord(c->ev_chunk[i], c->aux_stream));
+      CU(cudaStreamWaitEvent(c->stream, c->ev_chunk[i], 0));
+      CatMpcDev<T> qi = q;
+      qi.K = k1 - k0;
+      qi.k_offset = p->k_offset + k0;
+      rc = mpc_launch<T>(c, qi, d_prob, d_ctl + k0 * q.sk, d_ref, (double*)(d_pairs + 2 * used),
+                         d_pairs + 2 * used + 1, d_costs ? d_costs + k0 : nullptr, nullptr, nullptr);
+      if (rc) return rc;
+      ++used;
+    }
+    k_reduce_winners<<<1, 32, 0, c->stream>>>(used, d_pairs, (long long*)d_bc);   // -> d_bc[0], d_bi[0]
+    LAUNCHED();
+  } else {
+    if (!rng) CU(cudaMemcpyAsync(d_ctl, controls, n_ctl * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    rc = mpc_step_dev<T>(c, p, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs);
+    if (rc) return rc;
+  }
   CU(cudaMemcpyAsync(best_cost, d_bc, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaMemcpyAsync(best_idx, d_bi, np * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
   if (costs)
@@ -550,6 +589,7 @@ struct CatCtrl {
   CatCtrlConfig cfg;
   int64_t ref_len;
   int steps;                 // control steps enqueued so far
+  int slices;                // MPPI candidate slices per horizon step
   CatMpcProblem* d_prob;
   double *d_unom, *d_ustar, *d_ref, *d_log, *d_bc;
   long long* d_bi;
@@ -599,11 +639,12 @@ int ctrl_enqueue_step(CatCtrl* k) {
   x.mode = k->cfg.mode;
   x.max_steps = k->cfg.max_steps;
   x.lambda = k->cfg.lambda;
+  x.slices = k->slices;
   const bool mppi = k->cfg.mode == CAT_CTRL_MPPI;
   rc = mpc_launch<T>(c, q, k->d_prob, nullptr, k->d_ref, k->d_bc, k->d_bi, (T*)k->d_costs, k->d_bb, k->d_tk);
   if (rc) return rc;
   if (mppi) {
-    k_ctrl_mppi<T><<<dim3((unsigned)q.H, (unsigned)q.n_problems), 256, 0, c->stream>>>(
+    k_ctrl_mppi<T><<<dim3((unsigned)q.H, (unsigned)q.n_problems, (unsigned)k->slices), 256, 0, c->stream>>>(
         q, x, (const T*)k->d_costs, k->d_bc, k->d_bi, k->d_ustar);
     LAUNCHED();
   }
@@ -642,6 +683,14 @@ int ctrl_create(CatCtx* c, bool f32, const CatMpcParams* p, const CatCtrlConfig*
   k->ref_len = ref_len;
   const size_t np = (size_t)p->n_problems, H = (size_t)p->H;
   const size_t n_blocks = ((size_t)p->K + 31) / 32;   // upper bound for any block size >= 32
+  // MPPI reduction grid: enough (h, problem, slice) blocks for ~4 per SM, at least 1024 candidates per slice
+  {
+    long long want = (4LL * c->sm_count + (long long)(np * H) - 1) / (long long)(np * H);
+    const long long cap = (p->K + 1023) / 1024;
+    if (want > cap) want = cap;
+    if (want > 64) want = 64;
+    k->slices = want < 1 ? 1 : (int)want;
+  }
   const size_t esz = f32 ? sizeof(float) : sizeof(double);
   bool ok = true;
   auto dm = [&](void** ptr, size_t bytes) {
@@ -652,7 +701,7 @@ int ctrl_create(CatCtx* c, bool f32, const CatMpcParams* p, const CatCtrlConfig*
   };
   dm((void**)&k->d_prob, np * sizeof(CatMpcProblem));
   dm((void**)&k->d_unom, np * H * 3 * sizeof(double));
-  dm((void**)&k->d_ustar, np * H * 3 * sizeof(double));
+  dm((void**)&k->d_ustar, np * H * (size_t)k->slices * 4 * sizeof(double));
   dm((void**)&k->d_ref, np * (size_t)ref_len * 3 * sizeof(double));
   dm((void**)&k->d_log, np * (size_t)cfg->max_steps * CAT_CTRL_LOG_W * sizeof(double));
   dm((void**)&k->d_bc, np * 16);
@@ -674,7 +723,7 @@ int ctrl_create(CatCtx* c, bool f32, const CatMpcParams* p, const CatCtrlConfig*
   if (e == cudaSuccess)
     e = cudaMemcpyAsync(k->d_ref, p_ref_traj, np * (size_t)ref_len * 3 * sizeof(double), cudaMemcpyHostToDevice,
                         c->stream);
-  if (e == cudaSuccess) e = cudaMemsetAsync(k->d_ustar, 0, np * H * 3 * sizeof(double), c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(k->d_ustar, 0, np * H * (size_t)k->slices * 4 * sizeof(double), c->stream);
   if (e == cudaSuccess) e = cudaMemsetAsync(k->d_step, 0, 16, c->stream);
   if (e == cudaSuccess) e = cudaMemsetAsync(k->d_ticket, 0, 16, c->stream);
   if (e == cudaSuccess) e = cudaMemsetAsync(k->d_tk, 0, np * sizeof(unsigned int), c->stream);
@@ -771,6 +820,7 @@ int cat_init(int device, void** ctx) {
   ok = ok && cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking) == cudaSuccess;
   ok = ok && cudaEventCreate(&c->ev0) == cudaSuccess && cudaEventCreate(&c->ev1) == cudaSuccess;
   ok = ok && cudaEventCreateWithFlags(&c->ev_aux, cudaEventDisableTiming) == cudaSuccess;
+  for (int i = 0; i < 8; ++i) ok = ok && cudaEventCreateWithFlags(&c->ev_chunk[i], cudaEventDisableTiming) == cudaSuccess;
   ok = ok && cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device) == cudaSuccess;
   if (!ok) {
     cudaGetLastError();
@@ -792,6 +842,7 @@ int cat_destroy(void* ctx) {
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
   cudaEventDestroy(c->ev_aux);
+  for (int i = 0; i < 8; ++i) cudaEventDestroy(c->ev_chunk[i]);
   cudaStreamDestroy(c->own_stream);
   cudaStreamDestroy(c->aux_stream);
   delete c;
