@@ -7,7 +7,8 @@ from ._lib import (CatenaryLibraryError, LIB_PATH, OUT_FINAL, OUT_ORIGINAL, OUT_
 from .context import Context, default_context
 from .dynamics import (EquationModel, equation_id, equation_table, extract_features, integrate_theta_gamma,
                        predict, rk4_integration)
-from .geometry import (Catenary, catenary_shapes, lowest_point, rodrigues_rotation, solve_catenary, span_terms,
+from .geometry import (Catenary, catenary_equation, catenary_shapes, compute_catenary_3D, generate_catenary,
+                       solve_catenary_params, lowest_point, rodrigues_rotation, solve_catenary, span_terms,
                        transform_catenary)
 from .mpc import (circle_reference, default_mpc_params, make_params, make_problems, mpc_fleet_step,
                   mpc_sample_step, reduce_winners)

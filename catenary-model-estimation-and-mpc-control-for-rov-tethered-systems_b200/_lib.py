@@ -87,6 +87,8 @@ SIGNATURES = {
     "cat_sample_controls_dev_f64": (_int, [_vp, _PP, _vp]),
     "cat_reduce_winners_f64": (_int, [_int, _vp, _vp, _vp, _vp]),
     "cat_reduce_winners_dev_f64": (_int, [_vp, _int, _vp, _vp]),
+    "cat_catenary3d_f64": (_int, [_vp, _i64, _vp, _vp, _vp, _i64, _i32, _vp]),
+    "cat_catenary_equation_f64": (_int, [_vp, _i64, _vp, _vp, _i64, _vp]),
     "cat_resample_linear_f64": (_int, [_vp, _i64, _vp, _i32, _vp, _i64, _vp, _vp]),
     "cat_feature_bank_f64": (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, C.c_double, C.c_double, _vp]),
     "cat_expr_eval_f64": (_int, [_vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),

@@ -386,3 +386,85 @@ __global__ void __launch_bounds__(256) k_span_terms(long long n, const T* __rest
   if (z_low) z_low[i] = cat_z_low<T, M>(s, li, Li, T(0), hi);
   if (tension) tension[i] = ok ? M::div_(w * li, T(2) * s.sh) : w * li * T(0.5);
 }
+
+// ------------------------------------------------------------------------------------------
+// compute_catenary_3D (models/catenary_3d.py:5-39), batched: the reference's alternative sampler --
+// taut rope -> np.linspace(p0, p1); else the fixed point a <- a L / (2 a sinh(d / 2a)) from a = d/2
+// (at most 100 passes, stop when |a_new - a| < 1e-6) and the symmetric sag profile
+// sag(t) = a cosh(d/2a) - a cosh((t d - d/2)/a) subtracted from the chord's z.
+// k_catenary3d_solve: one thread per rope -> a (0 marks the taut case);  k_catenary3d_points: one thread
+// per sample, AoS (n, n_pts, 3) output so a warp writes 768 contiguous bytes.
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) k_catenary3d_solve(long long n, const T* __restrict__ p0,
+                                                          const T* __restrict__ p1, const T* __restrict__ L,
+                                                          long long L_stride, T* __restrict__ a_out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const T dx = p1[3 * i] - p0[3 * i], dy = p1[3 * i + 1] - p0[3 * i + 1], dz = p1[3 * i + 2] - p0[3 * i + 2];
+  const T dist = sqrt(dx * dx + dy * dy + dz * dz);
+  const T rope = L[i * L_stride];
+  if (rope <= dist) {
+    a_out[i] = T(0);
+    return;
+  }
+  T a = dist / T(2);
+  for (int it = 0; it < 100; ++it) {
+    const T lhs = T(2) * a * sinh(dist / (T(2) * a));
+    const T a_new = a * rope / lhs;
+    const bool done = fabs(a_new - a) < T(1e-6);
+    a = a_new;
+    if (done) break;
+  }
+  a_out[i] = a;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_catenary3d_points(long long n, int n_pts, const T* __restrict__ p0,
+                                                           const T* __restrict__ p1, const T* __restrict__ a_in,
+                                                           T* __restrict__ out) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n * (long long)n_pts) return;
+  const long long c = g / n_pts;
+  const int i = (int)(g - c * n_pts);
+  const T x0 = p0[3 * c], y0 = p0[3 * c + 1], z0 = p0[3 * c + 2];
+  const T dx = p1[3 * c] - x0, dy = p1[3 * c + 1] - y0, dz = p1[3 * c + 2] - z0;
+  const T a = a_in[c];
+  T* o = out + g * 3;
+  if (a == T(0)) {                       // np.linspace(p0, p1, n): start + i * (delta / (n-1)), last = stop
+    if (i == n_pts - 1 && n_pts > 1) {
+      o[0] = p1[3 * c];
+      o[1] = p1[3 * c + 1];
+      o[2] = p1[3 * c + 2];
+    } else {
+      const T div = T(n_pts > 1 ? n_pts - 1 : 1);
+      o[0] = x0 + T(i) * (dx / div);
+      o[1] = y0 + T(i) * (dy / div);
+      o[2] = z0 + T(i) * (dz / div);
+    }
+    return;
+  }
+  const T dist = sqrt(dx * dx + dy * dy + dz * dz);
+  const T half = dist / T(2);
+  const T off = a * cosh(half / a);
+  const T t = T(i) / T(n_pts - 1);
+  const T sag = off - a * cosh((t * dist - half) / a);
+  o[0] = x0 + dx * t;
+  o[1] = y0 + dy * t;
+  o[2] = (z0 + dz * t) - sag;
+}
+
+// catenary_equation (models/catenary-3d-visualization/src/catenary_model.py:10-12): y = (cosh(C x) - 1) / C,
+// C one value (stride 0) or one per sample.  cosh - 1 is formed without cancellation (cat_hyp).
+template <typename T>
+__global__ void __launch_bounds__(256) k_catenary_equation(long long n, const T* __restrict__ x,
+                                                           const T* __restrict__ C, long long C_stride,
+                                                           T* __restrict__ y) {
+  typedef CatMath<T> M;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const T c = C[i * C_stride];
+  T sm, cm, sh;
+  cat_hyp<T, M>(M::abs_(c * x[i]), sm, cm, sh);
+  y[i] = cm / c;
+}

@@ -1167,6 +1167,52 @@ int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_
 }
 
 // ---- roofline denominators --------------------------------------------------------------------------
+int cat_catenary3d_f64(void* ctx, int64_t n, const double* p0, const double* p1, const double* L, int64_t L_stride,
+                       int32_t n_pts, double* out) {
+  CTX();
+  NEED(n >= 0 && n_pts >= 1 && (L_stride == 0 || L_stride == 1));
+  if (n == 0) return CAT_OK;
+  NEED(p0 && p1 && L && out);
+  int rc = bind(c);
+  if (rc) return rc;
+  double *d0, *d1, *dL, *da, *dout;
+  const size_t b3 = (size_t)n * 3 * sizeof(double);
+  SCRATCH(SLOT_A, b3, d0);
+  SCRATCH(SLOT_B, b3, d1);
+  SCRATCH(SLOT_C, (L_stride ? (size_t)n : 1) * sizeof(double), dL);
+  SCRATCH(SLOT_D, (size_t)n * sizeof(double), da);
+  SCRATCH(SLOT_E, (size_t)n * n_pts * 3 * sizeof(double), dout);
+  CU(cudaMemcpyAsync(d0, p0, b3, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d1, p1, b3, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dL, L, (L_stride ? (size_t)n : 1) * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_catenary3d_solve<double><<<nblk(n, 256), 256, 0, c->stream>>>(n, d0, d1, dL, L_stride, da);
+  LAUNCHED();
+  k_catenary3d_points<double><<<nblk(n * (long long)n_pts, 256), 256, 0, c->stream>>>(n, n_pts, d0, d1, da, dout);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dout, (size_t)n * n_pts * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+int cat_catenary_equation_f64(void* ctx, int64_t n, const double* x, const double* C, int64_t C_stride, double* y) {
+  CTX();
+  NEED(n >= 0 && (C_stride == 0 || C_stride == 1));
+  if (n == 0) return CAT_OK;
+  NEED(x && C && y);
+  int rc = bind(c);
+  if (rc) return rc;
+  double *dx, *dC, *dy;
+  SCRATCH(SLOT_A, (size_t)n * sizeof(double), dx);
+  SCRATCH(SLOT_B, (C_stride ? (size_t)n : 1) * sizeof(double), dC);
+  SCRATCH(SLOT_C, (size_t)n * sizeof(double), dy);
+  CU(cudaMemcpyAsync(dx, x, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dC, C, (C_stride ? (size_t)n : 1) * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_catenary_equation<double><<<nblk(n, 256), 256, 0, c->stream>>>(n, dx, dC, C_stride, dy);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(y, dy, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
 int cat_resample_linear_f64(void* ctx, int64_t n_in, const double* time_in, int32_t n_cols, const double* cols,
                             int64_t n_out, const double* time_out, double* out) {
   CTX();

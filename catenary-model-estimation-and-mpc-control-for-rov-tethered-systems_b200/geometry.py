@@ -211,3 +211,58 @@ def transform_catenary(point_A, point_B, catenary_fn, theta_rad, gamma_rad, *, c
     ctx.check(ctx.lib.cat_rodrigues_f64(ctx.handle, n, _lib.ptr(aligned), _lib.ptr(k_gamma), 0, _lib.ptr(ang2), 0,
                                         _lib.ptr(A), _lib.ptr(final)))
     return original, theta_rotated, aligned, final
+
+
+def compute_catenary_3D(p0, p1, rope_length, num_points, *, ctx=None):
+    """models/catenary_3d.py:5-39: (3,),(3,),scalar,int -> (num_points,3); batched: (n,3),(n,3),(n,)|scalar ->
+    (n,num_points,3).  Taut rope -> np.linspace(p0, p1); else the reference's fixed-point in ``a`` and symmetric
+    sag profile."""
+    ctx = ctx or default_context()
+    a = np.ascontiguousarray(p0, np.float64)
+    b = np.ascontiguousarray(p1, np.float64)
+    single = a.ndim == 1
+    a2, b2 = np.ascontiguousarray(a.reshape(-1, 3)), np.ascontiguousarray(b.reshape(-1, 3))
+    if a2.shape != b2.shape:
+        raise ValueError("p0 and p1 must have the same shape (..., 3)")
+    n = a2.shape[0]
+    L = np.ascontiguousarray(rope_length, np.float64).reshape(-1)
+    if L.size not in (1, n):
+        raise ValueError("rope_length must be a scalar or one value per rope")
+    out = np.empty((n, int(num_points), 3))
+    ctx.check(ctx.lib.cat_catenary3d_f64(ctx.handle, n, _lib.ptr(a2), _lib.ptr(b2), _lib.ptr(L),
+                                         0 if L.size == 1 else 1, int(num_points), _lib.ptr(out)))
+    return out[0] if single else out
+
+
+def catenary_equation(x, C, *, ctx=None):
+    """catenary_model.py:10-12: (cosh(C x) - 1) / C, elementwise (C scalar or like x)."""
+    ctx = ctx or default_context()
+    xa = np.ascontiguousarray(x, np.float64)
+    Ca = np.ascontiguousarray(C, np.float64).reshape(-1)
+    if Ca.size not in (1, xa.size):
+        raise ValueError("C must be a scalar or have the shape of x")
+    y = np.empty(xa.size)
+    ctx.check(ctx.lib.cat_catenary_equation_f64(ctx.handle, xa.size, _lib.ptr(xa.reshape(-1)), _lib.ptr(Ca),
+                                                0 if Ca.size == 1 else 1, _lib.ptr(y)))
+    return y.reshape(xa.shape)
+
+
+def solve_catenary_params(L, l, H, *, ctx=None):
+    """catenary_model.py:14-20: the C with 2 sinh(C l / 2) / C = L on (1e-5, 10) -- the level-support case of
+    ``solve_catenary`` (H is unused by the reference too).  The reference gets it from a bounded scalar
+    MINIMISER of the squared residual with xatol 1e-5, so it agrees with this root to ~1e-5, not 1e-9; returns
+    None where no root exists in the bracket (the reference's minimiser returns a bound-hugging value there)."""
+    C = solve_catenary(l, 0.0, L, ctx=ctx)
+    C = float(np.asarray(C).reshape(-1)[0]) if np.ndim(l) == 0 else C
+    if np.ndim(l) == 0:
+        return None if (np.isnan(C) or C < 1e-5) else C
+    return C
+
+
+def generate_catenary(x_range, L, l, H, *, ctx=None):
+    """catenary_model.py:22-31: 100 samples of the level-support profile on [-l/2, l/2] -> (x, y)."""
+    C = solve_catenary_params(L, l, H, ctx=ctx)
+    if C is None:
+        raise ValueError("Failed to compute catenary parameter.")
+    x = np.linspace(-l / 2, l / 2, 100)
+    return x, catenary_equation(x, C, ctx=ctx)

@@ -216,6 +216,16 @@ CAT_API int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx
  * the ranks all-gather it), out = one such pair. */
 CAT_API int cat_reduce_winners_dev_f64(void* ctx, int n, const int64_t* gathered, int64_t* out);
 
+/* replaces compute_catenary_3D (models/catenary_3d.py:5-39), batched: p0, p1 (n,3), rope length L (n or one,
+ * L_stride 0) -> out (n, n_pts, 3).  Taut rope (L <= |p1-p0|) -> np.linspace(p0, p1, n_pts); else the reference's
+ * fixed point a <- a L / (2 a sinh(d/2a)) (<= 100 passes, 1e-6) and its symmetric sag profile. */
+CAT_API int cat_catenary3d_f64(void* ctx, int64_t n, const double* p0, const double* p1, const double* L,
+                               int64_t L_stride, int32_t n_pts, double* out);
+/* replaces catenary_equation (models/catenary-3d-visualization/src/catenary_model.py:10-12):
+ * y[i] = (cosh(C x[i]) - 1) / C, C one value (C_stride 0) or n. */
+CAT_API int cat_catenary_equation_f64(void* ctx, int64_t n, const double* x, const double* C, int64_t C_stride,
+                                      double* y);
+
 /* replaces uniform_resample (main_fun.py:128-145): scipy interp1d(kind='linear', fill_value='extrapolate') of every
  * column onto a new time grid.  time_in (n_in, increasing), cols (n_in, n_cols) row-major like DataFrame.values,
  * time_out (n_out) -> out (n_out, n_cols); bit-identical to scipy 1.18's interp1d._call_linear. */

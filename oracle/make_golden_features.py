@@ -58,6 +58,22 @@ def main():
     rs2 = mf.uniform_resample(df, 0.0125)
     out["ref_resampled_fine"] = rs2.values
     np.savez_compressed(os.path.join(OUT, "feature_layouts.npz"), **out)
+    # ---- catenary_model.py:10-31 (level-support planar profile), lifted defs, scipy's bounded minimiser ----
+    from scipy.optimize import minimize_scalar
+    cm = ref.lift(os.path.join("models", "catenary-3d-visualization", "src", "catenary_model.py"),
+                  ["catenary_equation", "solve_catenary_params", "generate_catenary"],
+                  {"minimize_scalar": minimize_scalar})
+    cases = np.array([[3.0, 1.0], [3.0, 2.0], [3.0, 2.9], [12.0, 10.0], [5.0, 0.5], [3.0, 2.999]])
+    Cs, xs, ys = [], [], []
+    for L_, l_ in cases:
+        Cs.append(cm["solve_catenary_params"](L_, l_, 0.0))
+        x, y = cm["generate_catenary"](None, L_, l_, 0.0)
+        xs.append(x)
+        ys.append(y)
+    xe = np.linspace(-2, 2, 41)
+    np.savez_compressed(os.path.join(OUT, "catenary_model.npz"), cases=cases, ref_C=np.array(Cs), ref_x=np.array(xs),
+                        ref_y=np.array(ys), eq_x=xe, eq_C=np.array([0.05, 0.7, 3.0]),
+                        ref_eq=np.array([cm["catenary_equation"](xe, c) for c in (0.05, 0.7, 3.0)]))
     print({k: v.shape for k, v in out.items() if k.startswith("ref_")},
           "nan tension rows:", int(np.isnan(mf.solve_catenary(out["ref_theta_features"][:, 3],
                                                               out["ref_theta_features"][:, 4], L)).sum()))
