@@ -289,6 +289,24 @@ class Catenary:
         return float(C), H, D, pts
 
 
+def catenary_3d_parameter(p0, p1, rope_length):
+    """The ``a`` compute_catenary_3D ends with (0 for a taut rope).  NOTE: the reference's fixed point
+    a <- a L / (2 a sinh(d/2a)) is repelling for a slack rope -- started at d/2 it grows geometrically for the
+    full 100 passes (a ~ 1e8 for d = 10, L = 12), so the sampled sag a cosh(d/2a) - a cosh(x/a) is formed with
+    an absolute cancellation error of ~a * 2^-52.  Parity tolerances on this function are scaled with a."""
+    d = np.asarray(p1, np.float64) - np.asarray(p0, np.float64)
+    dist = np.sqrt(d[0] ** 2 + d[1] ** 2 + d[2] ** 2)
+    if rope_length <= dist:
+        return 0.0
+    a = dist / 2
+    for _ in range(100):
+        a_new = a * rope_length / (2 * a * np.sinh(dist / (2 * a)))
+        if abs(a_new - a) < 1e-6:
+            return float(a_new)
+        a = a_new
+    return float(a)
+
+
 def compute_catenary_3D(p0, p1, rope_length, num_points):
     """models/catenary_3d.py:5-39 restated (fixed-point in a, symmetric sag profile)."""
     p0 = np.asarray(p0, np.float64)
