@@ -392,7 +392,7 @@ __global__ void __launch_bounds__(256) k_span_terms(long long n, const T* __rest
 // taut rope -> np.linspace(p0, p1); else the fixed point a <- a L / (2 a sinh(d / 2a)) from a = d/2
 // (at most 100 passes, stop when |a_new - a| < 1e-6) and the symmetric sag profile
 // sag(t) = a cosh(d/2a) - a cosh((t d - d/2)/a) subtracted from the chord's z.
-// k_catenary3d_solve: one thread per rope -> a (0 marks the taut case);  k_catenary3d_points: one thread
+// k_catenary3d_solve: one thread per rope -> a (-1 marks the taut case);  k_catenary3d_points: one thread
 // per sample, AoS (n, n_pts, 3) output so a warp writes 768 contiguous bytes.
 // ------------------------------------------------------------------------------------------
 template <typename T>
@@ -405,7 +405,7 @@ __global__ void __launch_bounds__(256) k_catenary3d_solve(long long n, const T* 
   const T dist = sqrt(dx * dx + dy * dy + dz * dz);
   const T rope = L[i * L_stride];
   if (rope <= dist) {
-    a_out[i] = T(0);
+    a_out[i] = T(-1);   // taut marker (a itself can legitimately end at 0, inf or NaN: the reference's map is repelling)
     return;
   }
   T a = dist / T(2);
@@ -431,7 +431,7 @@ __global__ void __launch_bounds__(256) k_catenary3d_points(long long n, int n_pt
   const T dx = p1[3 * c] - x0, dy = p1[3 * c + 1] - y0, dz = p1[3 * c + 2] - z0;
   const T a = a_in[c];
   T* o = out + g * 3;
-  if (a == T(0)) {                       // np.linspace(p0, p1, n): start + i * (delta / (n-1)), last = stop
+  if (a == T(-1)) {                      // taut: np.linspace(p0, p1, n): start + i * (delta / (n-1)), last = stop
     if (i == n_pts - 1 && n_pts > 1) {
       o[0] = p1[3 * c];
       o[1] = p1[3 * c + 1];

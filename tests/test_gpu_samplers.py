@@ -12,7 +12,9 @@ pytestmark = pytest.mark.gpu
 def _atol(p0, p1, L):
     """The reference's fixed point diverges (oracle.catenary_3d_parameter): its own sag values carry an absolute
     cancellation error of ~a * 2^-52, so that is the floor of any comparison."""
-    return 1e-12 + 32 * 2.0 ** -52 * abs(orc.catenary_3d_parameter(p0, p1, float(L)))
+    with np.errstate(all="ignore"):
+        a = abs(orc.catenary_3d_parameter(p0, p1, float(L)))
+    return 1e-12 + (32 * 2.0 ** -52 * a if np.isfinite(a) and a < 1e12 else 0.0)
 
 
 def test_compute_catenary_3d_golden_and_batch(cb):
@@ -31,8 +33,9 @@ def test_compute_catenary_3d_golden_and_batch(cb):
     got = cb.compute_catenary_3D(p0, p1, L, 64)
     assert got.shape == (n, 64, 3)
     for i in list(range(0, n, 97)) + list(np.flatnonzero(np.linalg.norm(p1 - p0, axis=1) >= L)[:5]):
-        assert_close(got[i], orc.compute_catenary_3D(p0[i], p1[i], float(L[i]), 64), 1e-9, _atol(p0[i], p1[i], L[i]),
-                     f"rope {i}")
+        with np.errstate(all="ignore"):
+            want = orc.compute_catenary_3D(p0[i], p1[i], float(L[i]), 64)
+        assert_close(got[i], want, 1e-9, _atol(p0[i], p1[i], L[i]), f"rope {i}")
     one = cb.compute_catenary_3D(p0, p1, 3.0, 10)            # scalar length broadcast
     assert_close(one[3], orc.compute_catenary_3D(p0[3], p1[3], 3.0, 10), 1e-9, _atol(p0[3], p1[3], 3.0), "scalar L")
     assert np.array_equal(cb.compute_catenary_3D(p0[0], p0[0] + [4.0, 0, 0], 3.0, 5),
