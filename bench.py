@@ -332,6 +332,17 @@ def run_ours(args):
                         "kernels_per_step": 3 if mode == "mppi" else 2, "host_bytes_per_step": 0,
                         "final_tracking_error_m": float(np.linalg.norm(
                             log[-1, :3] - cb.circle_reference(n_ctrl + H, p["dt"], period=4.0)[n_ctrl - 1]))}
+    # ---- config 1 (the reference's own CPU-runnable case): 5,000-step trajectory, host arrays in and out ----
+    feat = importlib.import_module(cb.__name__ + ".features")
+    cols1 = feat.config1_trajectory(5000)
+    feat.config1_pipeline(cols1, ctx=ctx)
+    t0 = time.perf_counter()
+    for _ in range(5):
+        feat.config1_pipeline(cols1, ctx=ctx)
+    c1_s = (time.perf_counter() - t0) / 5
+    config1 = {"steps": 5000, "gpu_ms": c1_s * 1e3, "gpu_steps_per_s": 5000 / c1_s,
+               "what": "extract_features + scaler + RK4 of both ODEs + per-step solve_catenary + final curve "
+                       "(T,100,3), NumPy in / NumPy out through the C ABI"}
     # ---- CPU baseline: the oracle port on this box's host cores, bounded sample ----
     from oracle import catenary_oracle as orc
     Ks = 16384
@@ -343,6 +354,27 @@ def run_ours(args):
         orc.mpc_rollout_costs(orc.default_mpc_params(), Uc, pref)
         reps += 1
     cpu_v = reps * Ks * H / (time.perf_counter() - t0)
+    # config 1 on the CPU, the reference's way: per-step Python loops (rk4_integration with one predict per stage,
+    # brentq per row, transform_catenary's per-point list comprehensions), bounded samples, extrapolated per step
+    ns = 400
+    Xo = orc.scale_features(orc.extract_features({k: v[:ns] for k, v in cols1.items()}))
+    t1 = time.perf_counter()
+    th_o = orc.rk4_integration(orc.EquationModel("dtheta_dt"), Xo, cols1["Time"][:ns], cols1["Theta"][0])
+    ga_o = orc.rk4_integration(orc.EquationModel("dgamma_dt"), Xo, cols1["Time"][:ns], cols1["Gamma"][0])
+    t_rk4 = (time.perf_counter() - t1) / ns
+    P1o = np.stack([cols1[f"robot_cable_attach_point {a}"][:ns] for a in "XYZ"], 1) / 1000
+    t1 = time.perf_counter()
+    orc.solve_catenary_brentq(np.hypot(P1o[:, 0], P1o[:, 1]), P1o[:, 2], 3.0)
+    t_solve = (time.perf_counter() - t1) / ns
+    t1 = time.perf_counter()
+    cat_o = orc.Catenary(3.0)
+    for i in range(40):
+        orc.transform_catenary(np.zeros(3), P1o[i], cat_o, th_o[i], ga_o[i])
+    t_shape = (time.perf_counter() - t1) / 40
+    config1["cpu_port_steps_per_s"] = 1.0 / (t_rk4 + t_solve + t_shape)
+    config1["cpu_port_us_per_step"] = {"rk4_both_odes": t_rk4 * 1e6, "solve_catenary_brentq": t_solve * 1e6,
+                                       "transform_catenary": t_shape * 1e6}
+    config1["cpu_sample"] = f"{ns} RK4 steps, {ns} brentq solves, 40 transform_catenary calls, 1 core, extrapolated"
     cpu = {"value": cpu_v, "unit": UNIT, "cores": 1, "kind": "port", "host_cores": os.cpu_count(),
            "sample": f"{reps} x ({Ks} of 65536 candidates x H={H}), vectorised NumPy fp64 oracle, 1 thread"}
     lat.sort()
@@ -353,7 +385,7 @@ def run_ours(args):
                       "controls": "explicit fp64 SoA [H][3][K]", "exchange": "nccl all_gather 16 B/rank + device fold on a side stream, double-buffered" if world > 1 else "none",
                       "l2": "3 rotating control sets (236 MB) > 126 MB L2"},
            "p50_ms": lat[len(lat) // 2], "p99_ms": lat[int(len(lat) * 0.99)], "latency_samples": len(lat),
-           "clocks": clocks, "e2e": e2e, "closed_loop": closed, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+           "clocks": clocks, "e2e": e2e, "closed_loop": closed, "config1": config1, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
     emit(json.dumps(out))
     if world > 1:
         dist.barrier()

@@ -139,3 +139,37 @@ def load_trajectory_csv(path):
     if a.shape[1] != 24:
         raise ValueError(f"{path}: expected 24 columns, found {a.shape[1]}")
     return np.ascontiguousarray(a.reshape(a.shape[0], 2, 12).transpose(1, 0, 2))
+
+
+def config1_trajectory(T=5000, seed=42):
+    """deterministic synthetic experiment in the CSV's data units -- P1 on a 0.4 m circle
+    (period 10 s) with a 0.25 m heave (period 25 s), V1 = dP1/dt + a +-30 mm/s PRBS on x (default_rng(42),
+    the seed of simple.py:77), Theta = 0.15 sin(2 pi t / 7), Gamma = 0.10 cos(2 pi t / 9), dt = 0.05 s."""
+    t = np.arange(T) * 0.05
+    rng = np.random.default_rng(seed)
+    w10, w25 = 2 * np.pi / 10, 2 * np.pi / 25
+    P1 = 1000 * np.stack([1 + 0.4 * np.cos(w10 * t), 1 + 0.4 * np.sin(w10 * t), -0.5 + 0.25 * np.sin(w25 * t)], 1)
+    V1 = 1000 * np.stack([-0.4 * w10 * np.sin(w10 * t), 0.4 * w10 * np.cos(w10 * t), 0.25 * w25 * np.cos(w25 * t)], 1)
+    V1[:, 0] += 30.0 * (2 * rng.integers(0, 2, T) - 1)
+    cols = {"Time": t, "Theta": 0.15 * np.sin(2 * np.pi * t / 7), "Gamma": 0.10 * np.cos(2 * np.pi * t / 9)}
+    for j, ax in enumerate("XYZ"):
+        cols[f"rod_end {ax}"] = np.zeros(T)
+        cols[f"robot_cable_attach_point {ax}"] = P1[:, j]
+        cols[f"rob_cor_speed {ax}"] = V1[:, j]
+    return cols
+
+
+def config1_pipeline(cols, L=3.0, ctx=None):
+    """The reference's config-1 flow on the GPU: extract_features + scaler (simple.py:15-41, test_temp.py:49) ->
+    rk4_integration of both ODEs (simulate_rk4_theta_gamma.py:74-75) -> per-step solve_catenary
+    (main_fun.py:418-431) -> transform_catenary with the integrated angles (fully_augmented_catenary.py:18).
+    -> dict(theta (T,), gamma (T,), C (T,), curves (T,100,3), valid (T,))."""
+    from .dynamics import EquationModel, extract_features, rk4_integration
+    from .geometry import catenary_shapes
+    X = extract_features(cols, scaled=True, ctx=ctx)
+    t = np.asarray(cols["Time"], np.float64)
+    theta = rk4_integration(EquationModel("dtheta_dt", ctx=ctx), X, t, float(cols["Theta"][0]), ctx=ctx)
+    gamma = rk4_integration(EquationModel("dgamma_dt", ctx=ctx), X, t, float(cols["Gamma"][0]), ctx=ctx)
+    P0, P1, _, _, _, _ = experiment_columns(cols)
+    (curves,), C, valid = catenary_shapes(P0, P1, L, theta, gamma, ctx=ctx)
+    return dict(theta=theta, gamma=gamma, C=C, curves=curves, valid=valid)

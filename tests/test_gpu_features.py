@@ -83,3 +83,29 @@ def test_trajectory_csv_and_expression_in_rk4(cb, tmp_path):
     a = cb.rk4_integration(cb.EquationModel("dtheta_dt"), X, time, 0.1)
     b = cb.rk4_integration(cb.ExpressionModel(row["sympy_format"], 18), X, time, 0.1)
     assert_close(b, a, 1e-12, 1e-15, "ExpressionModel through rk4_integration")
+
+
+def test_config1_full_pipeline(cb):
+    """T = 5,000 synthetic trajectory through features -> scaler -> RK4 of both ODEs ->
+    per-step catenary parameter -> theta/gamma-augmented curve, against the oracle."""
+    import importlib
+    feat = importlib.import_module(cb.__name__ + ".features")
+    cols = feat.config1_trajectory(5000)
+    got = feat.config1_pipeline(cols)
+    X = orc.scale_features(orc.extract_features(cols))
+    t = cols["Time"]
+    th = orc.rk4_integration_vec(orc.EquationModel("dtheta_dt"), X, t, cols["Theta"][0])
+    ga = orc.rk4_integration_vec(orc.EquationModel("dgamma_dt"), X, t, cols["Gamma"][0])
+    assert_close(got["theta"], th, 1e-9, 1e-12, "theta(t)")
+    assert_close(got["gamma"], ga, 1e-9, 1e-12, "gamma(t)")
+    P1 = np.stack([cols[f"robot_cable_attach_point {a}"] for a in "XYZ"], 1) / 1000
+    l = np.hypot(P1[:, 0], P1[:, 1])
+    assert_close(got["C"], orc.solve_catenary(l, P1[:, 2], 3.0), 1e-9, 0, "C(t)")
+    assert got["curves"].shape == (5000, 100, 3) and got["valid"].all()
+    cat = orc.Catenary(3.0)
+    for i in range(0, 5000, 101):
+        want = orc.transform_catenary(np.zeros(3), P1[i], cat, th[i], ga[i])[3]
+        assert_close(got["curves"][i], want, 1e-9, 1e-12, f"final curve at step {i}")
+    # the reference's own per-step loop on a prefix (one predict per stage, simulate_rk4_theta_gamma.py:52-68)
+    assert_close(got["theta"][:60], orc.rk4_integration(orc.EquationModel("dtheta_dt"), X[:60], t[:60], cols["Theta"][0]),
+                 1e-9, 1e-12, "reference loop prefix")
