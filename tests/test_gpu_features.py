@@ -103,9 +103,17 @@ def test_config1_full_pipeline(cb):
     assert_close(got["C"], orc.solve_catenary(l, P1[:, 2], 3.0), 1e-9, 0, "C(t)")
     assert got["curves"].shape == (5000, 100, 3) and got["valid"].all()
     cat = orc.Catenary(3.0)
+    n_fallback = 0
     for i in range(0, 5000, 101):
         want = orc.transform_catenary(np.zeros(3), P1[i], cat, th[i], ga[i])[3]
+        if want.shape[0] == 2:      # rotated span outside the solve domain: the reference falls back to [A, B'] (main_fun.py:67-69)
+            assert not (got["valid"][i] & 2)
+            assert_close(got["curves"][i][[0, -1]], want, 1e-9, 1e-12, f"chord fallback at step {i}")
+            n_fallback += 1
+            continue
+        assert got["valid"][i] & 2
         assert_close(got["curves"][i], want, 1e-9, 1e-12, f"final curve at step {i}")
+    assert n_fallback < 25
     # the reference's own per-step loop on a prefix (one predict per stage, simulate_rk4_theta_gamma.py:52-68)
     assert_close(got["theta"][:60], orc.rk4_integration(orc.EquationModel("dtheta_dt"), X[:60], t[:60], cols["Theta"][0]),
                  1e-9, 1e-12, "reference loop prefix")
