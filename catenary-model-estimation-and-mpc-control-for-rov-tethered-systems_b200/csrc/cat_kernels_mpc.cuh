@@ -269,7 +269,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     const T l2 = rx * rx + ry * ry;
     const T l = M::sqrt_(l2);
     const T d2 = l2 + rz * rz;
-    const CatSpan<T> sp = cat_span<T, M, false>(l, rz, q.L, q.c_lo, q.c_hi, warm);
+    const CatSpan<T> sp = cat_span<T, M, false, true>(l, rz, q.L, q.c_lo, q.c_hi, warm);
     warm = sp.warm;
     const T z_low = cat_z_low<T, M>(sp, l, q.L, P0[2], P0[2] + rz);
     // ---- cost, association as in the oracle ----

@@ -301,7 +301,7 @@ __device__ __forceinline__ T cat_halley_step(T u, T N, T D, T sm, T cm, T sh) {
 // sinh/cosh are exact at the old root).  A rollout step moves the span by ~1e-3 relative, so that
 // step lands within ~1e-9 of the root and ONE full iteration finishes; the loop still runs until
 // |du| is below tol.  Returns the root with sinh-u, cosh-1, sinh Taylor-corrected to it.
-template <typename T, typename M>
+template <typename T, typename M, bool FULL_WARP = false>
 __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w) {
   T u;
   if (w.u > T(0)) {
@@ -310,14 +310,26 @@ __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w)
     u = cat_u_guess<T, M>(M::div_(N, D));
   }
   T sm, cm, sh, du;
-  int it = 0;
-  bool more;
-  do {
-    cat_hyp<T, M>(u, sm, cm, sh);
-    du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
-    u -= du;
-    more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1));
-  } while (more && ++it < 60);
+  // The first iteration is straight-line code: with a warm start it is also the last one, and without a
+  // data-dependent loop around it the compiler can interleave this chain with the caller's independent work
+  // (the RK4 stages of the rollout).  Further iterations (cold starts, fast-moving spans) take the loop.
+  cat_hyp<T, M>(u, sm, cm, sh);
+  du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
+  u -= du;
+  bool more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1));
+  bool again;
+  if constexpr (FULL_WARP) again = __any_sync(0xffffffffu, more);   // every lane of the warp is here
+  else again = more;
+  if (again) {
+    int it = 1;
+    while (more && it < 60) {
+      cat_hyp<T, M>(u, sm, cm, sh);
+      du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
+      u -= du;
+      more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1));
+      ++it;
+    }
+  }
   // values at the updated u from those at u+du, second order (|du| <= 1e-6 min(u,1): remainder du^3/6 < 2e-19).
   // d/du: sm' = cm, cm' = sh, sh' = ch
   const T ch = cm + T(1);
@@ -355,23 +367,28 @@ template <typename T> __device__ __forceinline__ CatWarm<T> cat_cold() {
 }
 
 // NEED_C = false skips the division C = 2u/l: the domain test is done on 2u against c*l.
-template <typename T, typename M, bool NEED_C = true>
+template <typename T, typename M, bool NEED_C = true, bool FULL_WARP = false>
 __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, const CatWarm<T>& warm) {
   CatSpan<T> s;
   const T s2 = (L - dH) * (L + dH);
   const T sq = M::sqrt_(M::pos_(s2));
   const T N = s2 - l * l;
   const T D = l * (sq + l);
-  if (!(s2 > T(0)) || !(N > T(0)) || !(l > T(0))) {
-    s.C = M::nan_();
-    s.u = T(0);
-    s.sh = T(0);
-    s.ch = T(1);
-    s.inside = false;
-    s.warm = cat_cold<T>();
-    return s;
+  const bool none = !(s2 > T(0)) || !(N > T(0)) || !(l > T(0));   // no root: taut, vertical or degenerate span
+  if constexpr (!FULL_WARP) {
+    if (none) {
+      s.C = M::nan_();
+      s.u = T(0);
+      s.sh = T(0);
+      s.ch = T(1);
+      s.inside = false;
+      s.warm = cat_cold<T>();
+      return s;
+    }
   }
-  const CatWarm<T> r = cat_solve_u<T, M>(N, D, warm);
+  // FULL_WARP (the rollout): no early exit -- a rootless lane solves a harmless stand-in (N = D = 1) and is
+  // masked afterwards, so the warp stays converged and the common path is one basic block
+  const CatWarm<T> r = cat_solve_u<T, M, FULL_WARP>(FULL_WARP && none ? T(1) : N, FULL_WARP && none ? T(1) : D, warm);
   s.u = r.u;
   s.sh = r.sh;
   s.ch = r.cm + T(1);
@@ -384,6 +401,16 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, c
     s.C = (tu > c_lo * l && tu < c_hi * l) ? T(0) : M::nan_();
   }
   s.inside = M::abs_(dH) * s.ch <= L * r.sh;
+  if constexpr (FULL_WARP) {
+    if (none) {
+      s.C = M::nan_();
+      s.u = T(0);
+      s.sh = T(0);
+      s.ch = T(1);
+      s.inside = false;
+      s.warm = cat_cold<T>();
+    }
+  }
   return s;
 }
 
