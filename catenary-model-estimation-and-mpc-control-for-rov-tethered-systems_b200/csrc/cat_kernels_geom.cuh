@@ -38,7 +38,13 @@ __global__ void __launch_bounds__(256) k_solve_param(long long n, const T* __res
 #ifndef CAT_SHAPE_MINB
 #define CAT_SHAPE_MINB 5    // resident blocks per SM the register budget is cut for
 #endif
-#define CAT_SHAPE_RESEED 8     // (power of two) re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
+// lanes per configuration in phase 2 (power of two).  Measured on B200, 1,048,576 x 100 points, final curve:
+//   fp64: 32 lanes 0.53 ms, 16 lanes 0.57 ms, 8 lanes 0.91 ms -- the stores want one contiguous 768-byte run per
+//         warp instruction; splitting the warp over 2 or 4 curves costs more in the memory system than the saved
+//         cosh/sinh evaluations and idle lanes give back
+//   fp32: 16 lanes 0.28 ms vs 32 lanes 0.33 ms (each half-warp still writes a 192-byte run)
+template <typename T> struct CatShapeGroup { static constexpr int lanes = sizeof(T) == 4 ? 16 : 32; };
+#define CAT_SHAPE_RESEED 16    // (power of two) re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
 
 template <typename T> struct CatShapeSpan {
   T two_u;      // C * l
@@ -143,7 +149,7 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
   const long long i = base + tid;
   const bool need_rot = (which & (CAT_OUT_THETA_ROTATED | CAT_OUT_THETA_ALIGNED | CAT_OUT_FINAL)) != 0;
   const T inv_nm1 = (n_pts > 1) ? M::div_(T(1), T(n_pts - 1)) : T(0);
-  const T hop = T(32) * inv_nm1;
+  const T hop = T(CatShapeGroup<T>::lanes) * inv_nm1;
   if (i < n) {
     struct {
       CatShapeSpan<T> sp[2];
@@ -249,13 +255,18 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
       slot += (which >> m) & 1;
     }
   }
-  const T lane_f = T(lane);
-  const int n_hops = (n_pts + 31) >> 5;
-  for (int ci = warp; ci < n_here; ci += n_warps) {
+  // G lanes walk one configuration, so a warp serves 32/G configurations at once (G = 32 in fp64, 16 in fp32)
+  constexpr int G = CatShapeGroup<T>::lanes;
+  const int grp = lane / G, gl = lane % G;
+  const T lane_f = T(gl);
+  const int n_hops = (n_pts + G - 1) / G;
+  for (int c0 = warp * (32 / G); c0 < n_here; c0 += n_warps * (32 / G)) {
+    const bool have = c0 + grp < n_here;
+    const int ci = have ? c0 + grp : n_here - 1;   // idle groups shadow the last configuration and do not store
     const CatPair<T>* const r = rec + ci * rec_len;
     const CatPair<T> rA = r[0];
     const T A0 = rA.x, A1 = rA.y, A2 = r[1].x;
-    T* const o_lane = out + ((base + ci) * (long long)n_pts + lane) * 3;
+    T* const o_lane = out + ((base + ci) * (long long)n_pts + gl) * 3;
 #pragma unroll
     for (int spi = 0; spi < 2; ++spi) {
       const int outs = spi == 0 ? (which & CAT_OUT_ORIGINAL) : (which & ~CAT_OUT_ORIGINAL & 15);
@@ -266,10 +277,10 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
       const bool ok = rs[3].x != T(0);
       T cm = T(0), sh = T(0);
       T ptf = lane_f;          // T(pt), stepped exactly
-      T* o = o_lane;           // &out[cfg][pt][0] of the first requested block, stepped by 32 points
+      T* o = o_lane;           // &out[cfg][pt][0] of the first requested block, stepped by G points
       // uniform trip count (idle lanes of the last hop compute and do not store): no divergent loop exit
-      for (int hop = 0; hop < n_hops; ++hop, ptf += T(32), o += 96) {
-        const int pt = lane + 32 * hop;
+      for (int hop = 0; hop < n_hops; ++hop, ptf += T(G), o += 3 * G) {
+        const int pt = gl + G * hop;
         const T s = (pt == n_pts - 1) ? T(1) : ptf * inv_nm1;
         if ((hop & (CAT_SHAPE_RESEED - 1)) == 0) {   // warp-uniform
           const T t = two_u * s - v_low;
@@ -284,7 +295,7 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
           sh = sn;
         }
         const T zoff = ok ? (cm - cm_low) * inv_C : T(0);   // chord fallback: spans outside the solve domain
-        if (pt >= n_pts) continue;
+        if (pt >= n_pts || !have) continue;
         // sample = A + s a + zoff b as two FMAs per coordinate
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
