@@ -370,3 +370,42 @@ def test_errors_are_values_not_crashes(cb):
     with pytest.raises(ValueError):
         cb.catenary_shapes(np.zeros((2, 3)), np.zeros((3, 3)), 3.0)
     assert cb.default_context().launch_count > 0
+
+
+def test_mpc_host_step_chunked_pipeline(cb):
+    """K >= 32,768 with explicit controls goes up in 8 chunks (copy/rollout overlap) and the chunk winners fold on
+    the device: same costs and the same first-minimum as one launch, in both layouts, ragged K, ties and NaN
+    placed in different chunks."""
+    K, H = 40_037, 12
+    U = _controls(K, H, 77)
+    p = cb.default_mpc_params()
+    pref = cb.circle_reference(H, p["dt"])
+    U[39_000] = U[123]                                      # identical candidates in the last and the first chunk
+    U[20_500] = U[123]
+    Jo = orc.mpc_rollout_costs(orc.default_mpc_params(), U, pref)
+    bi, bc, J = cb.mpc_sample_step(p, U, pref)                                          # AoS, chunked
+    assert_close(J, Jo, RTOL64, 0, "chunked AoS costs")
+    assert bi == int(np.argmin(Jo)) and bc == J[bi]
+    Us = np.ascontiguousarray(U.transpose(1, 2, 0))
+    bi2, bc2, J2 = cb.mpc_sample_step(p, Us, pref, layout="H3K")                        # SoA, chunked (2-D copies)
+    assert bi2 == bi and bc2 == bc and np.array_equal(J2, J)
+    # make the duplicated candidate the global winner: the first of the three copies must win
+    U0 = np.zeros_like(U) + U[123]
+    best = orc.mpc_rollout_costs(orc.default_mpc_params(), U0[:1], pref)[0]
+    Ubig = U.copy()
+    Ubig[:, :, 0] += 4000.0                                  # everybody else far worse (tracking + du terms)
+    for k in (123, 20_500, 39_000):
+        Ubig[k] = U[123]
+    b3, c3, J3 = cb.mpc_sample_step(p, Ubig, pref)
+    assert b3 == 123 and abs(c3 - best) <= RTOL64 * best
+    b4, _, _ = cb.mpc_sample_step(p, np.ascontiguousarray(Ubig.transpose(1, 2, 0)), pref, layout="H3K")
+    assert b4 == 123
+    Ubig[30_001, 3, 1] = np.nan                              # NaN in a later chunk wins like np.argmin
+    b5, c5, _ = cb.mpc_sample_step(p, Ubig, pref)
+    assert b5 == 30_001 and np.isnan(c5)
+    # k_offset shifts the reported index of the chunked call too
+    b6, _, _ = cb.mpc_sample_step(p, U, pref, k_offset=1_000_000, return_costs=False)
+    assert b6 == bi + 1_000_000
+    # fp32 storage + compute through the same pipeline
+    b7, c7, J7 = cb.mpc_sample_step(p, U.astype(np.float32), pref, dtype=np.float32)
+    assert_close(J7, Jo, RTOL32, 0, "chunked fp32 costs")
