@@ -94,6 +94,8 @@ SIGNATURES = {
     "cat_expr_eval_f64": (_int, [_vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "cat_expr_eval_f32": (_int, [_vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "cat_expr_integrate_f64": (_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp]),
+    "cat_mpc_step_expr_f64": (_int, [_vp, _PP, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "cat_mpc_step_expr_f32": (_int, [_vp, _PP, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "cat_ctrl_create_f64": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
     "cat_ctrl_create_f32": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
     "cat_ctrl_run": (_int, [_vp, _i32]),

@@ -14,6 +14,7 @@
 #pragma once
 #include "cat_math.cuh"
 #include "gen/dyn_eqs.cuh"
+#include "cat_kernels_expr.cuh"
 #include "../../include/catenary_b200.h"
 
 #define CAT_MPC_BLOCK 128   // maximum; the host launches 64 when the batch is under ~1 wave (better SM balance)
@@ -34,6 +35,20 @@ template <typename T> struct CatMpcDev {
   const int* step;        // device-resident control-step counter t: RNG key = seed + t, reference window starts at t
   int ref_len;            // rows of p_ref per problem (H in a plain step)
   T u_max[3];
+  // run-time equation programs over the 18-feature layout (cat_kernels_expr.cuh); null = generated code.
+  // prog = [theta ops | gamma ops] (int2), consts = [theta consts | gamma consts] (double), device memory.
+  const int2* prog;
+  const double* prog_consts;
+  int n_ops_t, n_ops_g, n_c_t, n_c_g;
+};
+
+// shared-memory view of the staged programs (VM mode)
+template <typename T> struct CatMpcVm {
+  const int2* ops_t;
+  const int2* ops_g;
+  const T* c_t;
+  const T* c_g;
+  int n_t, n_g;
 };
 
 // candidate control of the receding-horizon controller: clamp(u_nom[h] + sigma*clip(N(0,1)), +-u_max);
@@ -52,10 +67,19 @@ __device__ __forceinline__ void cat_nominal_control(const CatMpcDev<T>& q, unsig
   }
 }
 
-template <typename T, bool GENERIC>
-__device__ __forceinline__ void cat_eval_pair(const CatMpcDev<T>& q, const T (&x)[18], T& ft, T& fg) {
+template <typename T, bool GENERIC, bool VM = false>
+__device__ __forceinline__ void cat_eval_pair(const CatMpcDev<T>& q, const CatMpcVm<T>& vm, const T (&x)[18], T& ft,
+                                              T& fg) {
   typedef CatMath<T> M;
-  if constexpr (GENERIC) {
+  if constexpr (VM) {
+    CatExprRow<T> row;
+    row.a = x;
+    row.b = nullptr;
+    row.mean = nullptr;
+    row.inv_scale = nullptr;
+    ft = cat_expr_run<T>(vm.ops_t, vm.n_t, vm.c_t, row);
+    fg = cat_expr_run<T>(vm.ops_g, vm.n_g, vm.c_g, row);
+  } else if constexpr (GENERIC) {
     ft = cat_eval_equation<T, M>(q.eq_theta, x);
     fg = cat_eval_equation<T, M>(q.eq_gamma, x);
   } else {
@@ -65,10 +89,14 @@ __device__ __forceinline__ void cat_eval_pair(const CatMpcDev<T>& q, const T (&x
 }
 
 // both equations on N feature rows at once (the stage-2/3 and stage-4 rows of one RK4 step)
-template <typename T, bool GENERIC, int N>
-__device__ __forceinline__ void cat_eval_pair_v(const CatMpcDev<T>& q, const T (&x)[N][18], T (&ft)[N], T (&fg)[N]) {
+template <typename T, bool GENERIC, int N, bool VM = false>
+__device__ __forceinline__ void cat_eval_pair_v(const CatMpcDev<T>& q, const CatMpcVm<T>& vm, const T (&x)[N][18],
+                                                T (&ft)[N], T (&fg)[N]) {
   typedef CatMath<T> M;
-  if constexpr (GENERIC) {
+  if constexpr (VM) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) cat_eval_pair<T, GENERIC, true>(q, vm, x[n], ft[n], fg[n]);
+  } else if constexpr (GENERIC) {
     cat_eval_equation_v<T, M, N>(q.eq_theta, x, ft);
     cat_eval_equation_v<T, M, N>(q.eq_gamma, x, fg);
   } else {
@@ -158,13 +186,32 @@ __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int pro
   }
 }
 
-template <typename T, bool GENERIC>
+template <typename T, bool GENERIC, bool VM = false>
 __global__ void __launch_bounds__(CAT_MPC_BLOCK, 4)   // <= 128 registers: config 3 needs 3.5 blocks per SM resident
 k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, const T* __restrict__ controls,
               const double* __restrict__ p_ref, T* __restrict__ costs, CatBest* __restrict__ block_best,
               unsigned int* __restrict__ tickets, double* __restrict__ best_cost,
               long long* __restrict__ best_idx) {
   typedef CatMath<T> M;
+  CatMpcVm<T> vm;
+  if constexpr (VM) {   // stage both programs into shared memory once per block
+    extern __shared__ __align__(16) unsigned char cat_mpc_smem[];
+    int2* s_ops = reinterpret_cast<int2*>(cat_mpc_smem);
+    T* s_c = reinterpret_cast<T*>(s_ops + q.n_ops_t + q.n_ops_g);
+    for (int i = threadIdx.x; i < q.n_ops_t + q.n_ops_g; i += blockDim.x) s_ops[i] = q.prog[i];
+    for (int i = threadIdx.x; i < q.n_c_t + q.n_c_g; i += blockDim.x) s_c[i] = T(q.prog_consts[i]);
+    __syncthreads();
+    vm.ops_t = s_ops;
+    vm.ops_g = s_ops + q.n_ops_t;
+    vm.c_t = s_c;
+    vm.c_g = s_c + q.n_c_t;
+    vm.n_t = q.n_ops_t;
+    vm.n_g = q.n_ops_g;
+  } else {
+    vm.ops_t = vm.ops_g = nullptr;
+    vm.c_t = vm.c_g = nullptr;
+    vm.n_t = vm.n_g = 0;
+  }
   const int prob = blockIdx.y;
   const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = k < q.K;
@@ -196,9 +243,9 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   cat_features18<T, M>(P0, P, V, A, th, ga, thp, gap, x0);
   cat_scale18<T>(x0);
   T k1t, k1g;
-  cat_eval_pair<T, GENERIC>(q, x0, k1t, k1g);
+  cat_eval_pair<T, GENERIC, VM>(q, vm, x0, k1t, k1g);
   bool carry_t, carry_g;
-  if constexpr (GENERIC) {
+  if constexpr (GENERIC || VM) {
     carry_t = q.carry_t != 0;
     carry_g = q.carry_g != 0;
   } else {
@@ -260,7 +307,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
 #pragma unroll
     for (int j = 0; j < 18; ++j) xs[0][j] = (x0[j] + xs[1][j]) * T(0.5);
     T kt[2], kg[2];
-    cat_eval_pair_v<T, GENERIC, 2>(q, xs, kt, kg);
+    cat_eval_pair_v<T, GENERIC, 2, VM>(q, vm, xs, kt, kg);
     const T k2t = kt[0], k4t = kt[1], k2g = kg[0], k4g = kg[1];
     const T thn = th + q.dt6 * (k1t + T(2) * k2t + T(2) * k2t + k4t);
     const T gan = ga + q.dt6 * (k1g + T(2) * k2g + T(2) * k2g + k4g);
@@ -307,7 +354,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       k1g = k4g;
     } else {
       T nt, ng;
-      cat_eval_pair<T, GENERIC>(q, x0, nt, ng);
+      cat_eval_pair<T, GENERIC, VM>(q, vm, x0, nt, ng);
       k1t = carry_t ? k4t : nt;
       k1g = carry_g ? k4g : ng;
     }

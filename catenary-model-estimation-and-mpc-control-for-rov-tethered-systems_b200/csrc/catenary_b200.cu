@@ -325,6 +325,9 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.clip = T(p->clip);
   for (int a = 0; a < 3; ++a) q.sigma[a] = T(p->sigma[a]);
   q.seed = p->seed;
+  q.prog = nullptr;
+  q.prog_consts = nullptr;
+  q.n_ops_t = q.n_ops_g = q.n_c_t = q.n_c_g = 0;
   q.u_nom = nullptr;
   q.step = nullptr;
   q.ref_len = p->H;
@@ -352,7 +355,11 @@ int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, 
     tk = (unsigned int*)pp;
   }
   const bool shipped = (q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED);
-  if (shipped)
+  if (q.prog) {   // run-time equation programs
+    const size_t smem = (size_t)(q.n_ops_t + q.n_ops_g) * sizeof(int2) + (size_t)(q.n_c_t + q.n_c_g + 2) * sizeof(T);
+    k_mpc_rollout<T, false, true><<<grid, block, smem, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
+                                                                    best_cost, best_idx);
+  } else if (shipped)
     k_mpc_rollout<T, false><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk, best_cost,
                                                            best_idx);
   else
@@ -373,9 +380,58 @@ int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems
   return mpc_launch<T>(c, q, problems, controls, p_ref, best_cost, best_idx, costs, nullptr, nullptr);
 }
 
+// optional run-time equation programs of a host MPC step (both or neither)
+struct CatHostPrograms {
+  int32_t n_ops_t, n_c_t, n_ops_g, n_c_g;
+  const int32_t *ops_t, *ops_g;
+  const double *c_t, *c_g;
+};
+
+int expr_validate(CatCtx* c, int32_t n_features, int32_t n_ops, const int32_t* ops, int32_t n_consts,
+                  const double* consts);
+
+// upload [theta ops | gamma ops] and [theta consts | gamma consts] into SLOT_G and point q at them; the k1 carry
+// holds for an equation that reads neither theta (column 14) nor gamma (column 15)
+template <typename T>
+int mpc_attach_programs(CatCtx* c, const CatHostPrograms* hp, CatMpcDev<T>& q) {
+  int rc = expr_validate(c, 18, hp->n_ops_t, hp->ops_t, hp->n_c_t, hp->c_t);
+  if (rc) return rc;
+  rc = expr_validate(c, 18, hp->n_ops_g, hp->ops_g, hp->n_c_g, hp->c_g);
+  if (rc) return rc;
+  const size_t b_ops = (size_t)(hp->n_ops_t + hp->n_ops_g) * sizeof(int2);
+  const size_t b_c = (size_t)(hp->n_c_t + hp->n_c_g + 1) * sizeof(double);
+  unsigned char* base;
+  SCRATCH(SLOT_G, b_ops + b_c, base);
+  int2* d_ops = (int2*)base;
+  double* d_c = (double*)(base + b_ops);
+  CU(cudaMemcpyAsync(d_ops, hp->ops_t, (size_t)hp->n_ops_t * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_ops + hp->n_ops_t, hp->ops_g, (size_t)hp->n_ops_g * sizeof(int2), cudaMemcpyHostToDevice,
+                     c->stream));
+  if (hp->n_c_t)
+    CU(cudaMemcpyAsync(d_c, hp->c_t, (size_t)hp->n_c_t * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if (hp->n_c_g)
+    CU(cudaMemcpyAsync(d_c + hp->n_c_t, hp->c_g, (size_t)hp->n_c_g * sizeof(double), cudaMemcpyHostToDevice,
+                       c->stream));
+  q.prog = d_ops;
+  q.prog_consts = d_c;
+  q.n_ops_t = hp->n_ops_t;
+  q.n_ops_g = hp->n_ops_g;
+  q.n_c_t = hp->n_c_t;
+  q.n_c_g = hp->n_c_g;
+  auto reads_angles = [](int n, const int32_t* ops) {
+    for (int i = 0; i < n; ++i)
+      if (ops[2 * i] == CAT_OP_VAR && (ops[2 * i + 1] == 14 || ops[2 * i + 1] == 15)) return true;
+    return false;
+  };
+  q.carry_t = reads_angles(hp->n_ops_t, hp->ops_t) ? 0 : 1;
+  q.carry_g = reads_angles(hp->n_ops_g, hp->ops_g) ? 0 : 1;
+  return CAT_OK;
+}
+
 template <typename T>
 int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
-                  const double* p_ref, double* best_cost, int64_t* best_idx, T* costs) {
+                  const double* p_ref, double* best_cost, int64_t* best_idx, T* costs,
+                  const CatHostPrograms* hp = nullptr) {
   NEED(p != nullptr && p->K >= 1 && p->H >= 1 && p->n_problems >= 1);
   const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
   NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
@@ -405,6 +461,10 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     CatMpcDev<T> q;
     rc = mpc_fill<T>(c, p, q);
     if (rc) return rc;
+    if (hp) {
+      rc = mpc_attach_programs<T>(c, hp, q);
+      if (rc) return rc;
+    }
     long long* d_pairs;
     SCRATCH(SLOT_F, (size_t)NC * 16, d_pairs);
     const bool aos = (p->flags & CAT_MPC_CONTROLS_AOS) != 0;
@@ -435,7 +495,16 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     LAUNCHED();
   } else {
     if (!rng) CU(cudaMemcpyAsync(d_ctl, controls, n_ctl * sizeof(T), cudaMemcpyHostToDevice, c->stream));
-    rc = mpc_step_dev<T>(c, p, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs);
+    if (hp) {
+      CatMpcDev<T> q;
+      rc = mpc_fill<T>(c, p, q);
+      if (rc) return rc;
+      rc = mpc_attach_programs<T>(c, hp, q);
+      if (rc) return rc;
+      rc = mpc_launch<T>(c, q, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs, nullptr, nullptr);
+    } else {
+      rc = mpc_step_dev<T>(c, p, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs);
+    }
     if (rc) return rc;
   }
   CU(cudaMemcpyAsync(best_cost, d_bc, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -1281,6 +1350,27 @@ int cat_expr_integrate_f64(void* ctx, int64_t n_traj, int64_t T, int32_t n_featu
   CTX();
   return expr_integrate_host<double>(c, n_traj, T, n_features, X, time, y0, n_ops, ops, n_consts, consts, method,
                                      y_out, ydot_out);
+}
+
+int cat_mpc_step_expr_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems, const double* controls,
+                          const double* p_ref, int32_t n_ops_theta, const int32_t* ops_theta, int32_t n_consts_theta,
+                          const double* consts_theta, int32_t n_ops_gamma, const int32_t* ops_gamma,
+                          int32_t n_consts_gamma, const double* consts_gamma, double* best_cost, int64_t* best_idx,
+                          double* costs) {
+  CTX();
+  const CatHostPrograms hp = {n_ops_theta, n_consts_theta, n_ops_gamma, n_consts_gamma,
+                              ops_theta,   ops_gamma,      consts_theta, consts_gamma};
+  return mpc_step_host<double>(c, p, problems, controls, p_ref, best_cost, best_idx, costs, &hp);
+}
+int cat_mpc_step_expr_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems, const float* controls,
+                          const double* p_ref, int32_t n_ops_theta, const int32_t* ops_theta, int32_t n_consts_theta,
+                          const double* consts_theta, int32_t n_ops_gamma, const int32_t* ops_gamma,
+                          int32_t n_consts_gamma, const double* consts_gamma, double* best_cost, int64_t* best_idx,
+                          float* costs) {
+  CTX();
+  const CatHostPrograms hp = {n_ops_theta, n_consts_theta, n_ops_gamma, n_consts_gamma,
+                              ops_theta,   ops_gamma,      consts_theta, consts_gamma};
+  return mpc_step_host<float>(c, p, problems, controls, p_ref, best_cost, best_idx, costs, &hp);
 }
 
 int cat_ctrl_create_f64(void* ctx, const CatMpcParams* p, const CatCtrlConfig* cfg, const CatMpcProblem* problems,

@@ -24,7 +24,8 @@ def default_mpc_params(**over):
              theta=float(np.radians(-10.0)), gamma=float(np.radians(20.0)),
              theta_prev=float(np.radians(-10.0)), gamma_prev=float(np.radians(20.0)),
              w_trk=1.0, w_du=1e-4, w_len=1e3, w_sag=1e3, w_ang=0.1, rho=0.95, z_floor=-2.0, margin=0.1,
-             c_lo=C_LO, c_hi=C_HI, nan_penalty=NAN_PENALTY, theta_cx=None, gamma_cx=None)
+             c_lo=C_LO, c_hi=C_HI, nan_penalty=NAN_PENALTY, theta_cx=None, gamma_cx=None,
+             theta_expr=None, gamma_expr=None)
     p.update(over)
     return p
 
@@ -65,6 +66,26 @@ def make_problems(params, n_problems=1):
     return pr
 
 
+def _programs(params):
+    """(theta Program, gamma Program) when params carries run-time equations ('theta_expr' / 'gamma_expr': an
+    equation string over x0..x17, an expr.Program or an expr.ExpressionModel), else None."""
+    te, ge = params.get("theta_expr"), params.get("gamma_expr")
+    if te is None and ge is None:
+        return None
+    if te is None or ge is None:
+        raise ValueError("theta_expr and gamma_expr go together")
+    from .expr import Program, compile_expression
+
+    def prog(e):
+        e = getattr(e, "program", e)
+        if not isinstance(e, Program):
+            e = compile_expression(e, 18)
+        if e.n_features != 18:
+            raise ValueError("MPC equations are over the 18-feature layout of simple.py:15-41")
+        return e
+    return prog(te), prog(ge)
+
+
 def mpc_sample_step(params, controls, p_ref, *, layout="KH3", return_costs=True, dtype=np.float64, seed=0,
                     sigma=None, clip=3.0, K=None, k_offset=0, ctx=None):
     """One sampling-MPC step -> (best_idx, best_cost, costs | None).
@@ -100,6 +121,16 @@ def mpc_sample_step(params, controls, p_ref, *, layout="KH3", return_costs=True,
     best_cost = np.empty(1)
     best_idx = np.empty(1, np.int64)
     costs = np.empty(K, dtype) if return_costs else None
+    progs = _programs(params)
+    if progs is not None:
+        # run-time equation programs (a retrained model's equation strings) instead of the generated code
+        pt, pg = progs
+        fn = ctx.lib.cat_mpc_step_expr_f64 if dtype == np.float64 else ctx.lib.cat_mpc_step_expr_f32
+        ctx.check(fn(ctx.handle, C.byref(s), _lib.ptr(pr), _lib.ptr(U), _lib.ptr(p_ref),
+                     len(pt.ops), _lib.ptr(pt.ops), len(pt.consts), _lib.ptr(pt.consts) if len(pt.consts) else None,
+                     len(pg.ops), _lib.ptr(pg.ops), len(pg.consts), _lib.ptr(pg.consts) if len(pg.consts) else None,
+                     _lib.ptr(best_cost), _lib.ptr(best_idx), _lib.ptr(costs)))
+        return int(best_idx[0]), float(best_cost[0]), costs
     fn = ctx.lib.cat_mpc_step_f64 if dtype == np.float64 else ctx.lib.cat_mpc_step_f32
     ctx.check(fn(ctx.handle, C.byref(s), _lib.ptr(pr), _lib.ptr(U), _lib.ptr(p_ref), _lib.ptr(best_cost),
                  _lib.ptr(best_idx), _lib.ptr(costs)))

@@ -272,6 +272,20 @@ CAT_API int cat_expr_integrate_f64(void* ctx, int64_t n_traj, int64_t T, int32_t
                                    int32_t n_consts, const double* consts, int32_t method, double* y_out,
                                    double* ydot_out);
 
+/* the sampling-MPC step with RUN-TIME equation programs for d(theta)/dt and d(gamma)/dt over the 18-feature layout
+ * of simple.py:15-41 (a model retrained with simple.py:60-75 is usable without rebuilding the library); p->eq_theta /
+ * p->eq_gamma are ignored.  Programs as in cat_expr_eval (n_features = 18).  Everything else as cat_mpc_step_*. */
+CAT_API int cat_mpc_step_expr_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+                                  const double* controls, const double* p_ref, int32_t n_ops_theta,
+                                  const int32_t* ops_theta, int32_t n_consts_theta, const double* consts_theta,
+                                  int32_t n_ops_gamma, const int32_t* ops_gamma, int32_t n_consts_gamma,
+                                  const double* consts_gamma, double* best_cost, int64_t* best_idx, double* costs);
+CAT_API int cat_mpc_step_expr_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+                                  const float* controls, const double* p_ref, int32_t n_ops_theta,
+                                  const int32_t* ops_theta, int32_t n_consts_theta, const double* consts_theta,
+                                  int32_t n_ops_gamma, const int32_t* ops_gamma, int32_t n_consts_gamma,
+                                  const double* consts_gamma, double* best_cost, int64_t* best_idx, float* costs);
+
 /* ---- receding-horizon controller around the sampling-MPC step ----
  * The role the (absent) pympc controller played at the reference's call sites: every control step samples K
  * candidate sequences around a nominal one, rolls them out (the kernel above), picks / blends the next nominal

@@ -485,6 +485,7 @@ def default_mpc_params(**over):
         rho=0.95, z_floor=-2.0, margin=0.1,
         c_lo=C_LO, c_hi=C_HI, nan_penalty=NAN_PENALTY,
         theta_cx=None, gamma_cx=None,              # hall-of-fame rows; None = shipped
+        theta_expr=None, gamma_expr=None,          # run-time equation strings over x0..x17 (override the rows)
     )
     p.update(over)
     return p
@@ -521,8 +522,12 @@ def mpc_rollout_costs(params, controls, p_ref, return_traj=False):
     m = load_model()
     mean = np.array(m["scaler_mean"])
     inv = 1.0 / np.array(m["scaler_scale"])
-    f_th = equation("dtheta_dt", p.get("theta_cx"), m)
-    f_ga = equation("dgamma_dt", p.get("gamma_cx"), m)
+    if p.get("theta_expr") is not None:             # run-time equation strings
+        f_th = LambdifiedModel(p["theta_expr"], 18).predict
+        f_ga = LambdifiedModel(p["gamma_expr"], 18).predict
+    else:
+        f_th = equation("dtheta_dt", p.get("theta_cx"), m)
+        f_ga = equation("dgamma_dt", p.get("gamma_cx"), m)
     U = np.asarray(controls, np.float64)
     K, H, _ = U.shape
     p_ref = np.asarray(p_ref, np.float64)

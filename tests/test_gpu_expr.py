@@ -106,3 +106,40 @@ def test_expr_errors_and_edges(cb):
         ex.ExpressionModel(bad).predict(np.zeros((2, 2)))
     y = m.integrate(np.ones((1, 4)), np.zeros(1), 0.5)
     assert y.tolist() == [0.5]
+
+
+def test_mpc_step_with_runtime_equations(cb):
+    """The sampling-MPC step driven by equation STRINGS (a retrained model) instead of generated code."""
+    rng = np.random.default_rng(21)
+    K, H = 3000, 30
+    sig = np.array(orc.load_model()["scaler_scale"][3:6])
+    U = np.clip(rng.normal(size=(K, H, 3)), -3, 3) * sig
+    pref = cb.circle_reference(H, 0.01)
+    mdl = orc.load_model()
+    ship_t = next(r for r in mdl["dtheta_dt"]["rows"] if r["complexity"] == mdl["dtheta_dt"]["shipped_complexity"])
+    ship_g = next(r for r in mdl["dgamma_dt"]["rows"] if r["complexity"] == mdl["dgamma_dt"]["shipped_complexity"])
+    # 1. the shipped pair as strings == the generated code path
+    _, _, J_gen = cb.mpc_sample_step(cb.default_mpc_params(), U, pref)
+    bi, bc, J_vm = cb.mpc_sample_step(cb.default_mpc_params(theta_expr=ship_t["sympy_format"],
+                                                            gamma_expr=ship_g["sympy_format"]), U, pref)
+    assert_close(J_vm, J_gen, 1e-11, 0, "VM vs generated (shipped pair)")
+    assert bi == int(np.argmin(J_gen))
+    # 2. equations that read the angles themselves (no k1 carry), other operators, against the oracle
+    te = "-0.03*x16 - 0.8*x14 + 0.02*sin(x17) - 0.01*tanh(x3*0.5) + 0.004*square(x9)"
+    ge = "0.5*(x15 - x17) - 0.3*x15*Abs(x13) + 0.002*cos(x4)"
+    po = orc.default_mpc_params(theta_expr=te, gamma_expr=ge)
+    Jo = orc.mpc_rollout_costs(po, U, pref)
+    bi, bc, J = cb.mpc_sample_step(cb.default_mpc_params(theta_expr=te, gamma_expr=ge), U, pref)
+    assert_close(J, Jo, 1e-9, 0, "VM rollout vs oracle")
+    assert bi == int(np.argmin(Jo))
+    # 3. ExpressionModel objects, SoA layout, fp32
+    ex = importlib.import_module(cb.__name__ + ".expr")
+    p2 = cb.default_mpc_params(theta_expr=ex.ExpressionModel(te, 18), gamma_expr=ex.ExpressionModel(ge, 18))
+    b2, _, J2 = cb.mpc_sample_step(p2, np.ascontiguousarray(U.transpose(1, 2, 0)), pref, layout="H3K")
+    assert b2 == bi and np.array_equal(J2, J)
+    _, _, J32 = cb.mpc_sample_step(p2, U.astype(np.float32), pref, dtype=np.float32)
+    assert_close(J32, Jo, 1e-4, 0, "VM rollout fp32")
+    with pytest.raises(ValueError):
+        cb.mpc_sample_step(cb.default_mpc_params(theta_expr=te), U, pref)
+    with pytest.raises(ValueError):
+        cb.mpc_sample_step(cb.default_mpc_params(theta_expr="x20", gamma_expr=ge), U, pref)
