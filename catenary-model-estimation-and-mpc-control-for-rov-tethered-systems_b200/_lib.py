@@ -96,6 +96,12 @@ SIGNATURES = {
     "cat_expr_integrate_f64": (_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp]),
     "cat_mpc_step_expr_f64": (_int, [_vp, _PP, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "cat_mpc_step_expr_f32": (_int, [_vp, _PP, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "cat_p2p_create": (_int, [_vp, _int, _int, C.POINTER(_vp), _vp]),
+    "cat_p2p_connect": (_int, [_vp, _vp]),
+    "cat_mpc_step_p2p_dev_f64": (_int, [_vp, _vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cat_mpc_step_p2p_dev_f32": (_int, [_vp, _vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cat_p2p_status": (_int, [_vp, C.POINTER(_int)]),
+    "cat_p2p_destroy": (_int, [_vp]),
     "cat_ctrl_create_f64": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
     "cat_ctrl_create_f32": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
     "cat_ctrl_run": (_int, [_vp, _i32]),

@@ -19,6 +19,22 @@
 
 #define CAT_MPC_BLOCK 128   // maximum; the host launches 64 when the batch is under ~1 wave (better SM balance)
 
+// Fused winner exchange over NVLink peer memory: every rank owns a slot buffer
+// [2 parities][n_ranks] x {cost bits, global idx, seq, pad} that its peers map through CUDA IPC.  The last
+// block of the rollout writes this rank's winner into slot [seq & 1][rank] of EVERY rank's buffer (payload,
+// system fence, then the sequence number), waits until its own buffer holds all n_ranks winners of this step and
+// folds them in rank order -- the job-wide (cost, idx) is in best_cost/best_idx when the kernel ends, with no
+// NCCL call and no second launch.  Two parities suffice: a rank cannot start step s+2 before every peer has
+// written step s+1, which a peer does only after it has finished reading step s.
+struct CatP2PDev {
+  long long* const* peers;   // device array [n_ranks]: slot buffer of each rank (own included); null = off
+  int rank, n_ranks;
+  unsigned int seq;          // step number, >= 1, identical on every rank
+  int* err;                  // set to 1 if a peer's winner did not arrive in time
+};
+#define CAT_P2P_SLOT_W 4     // long longs per slot
+#define CAT_P2P_MAX_RANKS 64
+
 // Kernel-side parameters in the compute type.  Derived constants are formed on the host in
 // double exactly as the oracle forms them (dt/1000, dt/6, rho*L, z_floor+margin).
 template <typename T> struct CatMpcDev {
@@ -40,6 +56,7 @@ template <typename T> struct CatMpcDev {
   const int2* prog;
   const double* prog_consts;
   int n_ops_t, n_ops_g, n_c_t, n_c_g;
+  CatP2PDev p2p;
 };
 
 // shared-memory view of the staged programs (VM mode)
@@ -154,7 +171,7 @@ __device__ __forceinline__ CatBest cat_block_argmin(double cost, long long idx) 
 // folds the slots, writes the winner and resets the ticket (re-entrant, graph-replayable).
 __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int prob, CatBest* __restrict__ block_best,
                                                 unsigned int* __restrict__ tickets, double* __restrict__ best_cost,
-                                                long long* __restrict__ best_idx) {
+                                                long long* __restrict__ best_idx, const CatP2PDev& p2p) {
   const CatBest b = cat_block_argmin(jc, ji);
   __shared__ bool s_last;
   if (threadIdx.x == 0) {
@@ -179,10 +196,59 @@ __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int pro
   }
   __syncthreads();   // s_cost/s_idx of cat_block_argmin are reused
   const CatBest r = cat_block_argmin(bc, bi);
+  if (p2p.peers == nullptr) {
+    if (threadIdx.x == 0) {
+      best_cost[prob] = r.cost;
+      best_idx[prob] = r.idx;
+      tickets[prob] = 0u;   // ready for the next launch / graph replay
+    }
+    return;
+  }
+  // ---- fused exchange of the rank winners through peer memory (one problem per launch) ----
+  __shared__ long long s_x[2 * CAT_P2P_MAX_RANKS];
   if (threadIdx.x == 0) {
-    best_cost[prob] = r.cost;
-    best_idx[prob] = r.idx;
-    tickets[prob] = 0u;   // ready for the next launch / graph replay
+    s_x[0] = __double_as_longlong(r.cost);
+    s_x[1] = r.idx;
+    tickets[prob] = 0u;
+  }
+  __syncthreads();
+  const long long my_c = s_x[0], my_i = s_x[1];
+  __syncthreads();
+  const int par = (int)(p2p.seq & 1u);
+  const int t = threadIdx.x;
+  if (t < p2p.n_ranks) {
+    volatile long long* dst = p2p.peers[t] + (long long)(par * p2p.n_ranks + p2p.rank) * CAT_P2P_SLOT_W;
+    dst[0] = my_c;
+    dst[1] = my_i;
+    __threadfence_system();            // payload visible system-wide before the sequence number
+    dst[2] = (long long)p2p.seq;
+    volatile long long* src = p2p.peers[p2p.rank] + (long long)(par * p2p.n_ranks + t) * CAT_P2P_SLOT_W;
+    int spins = 0;
+    while (src[2] != (long long)p2p.seq) {
+      __nanosleep(64);
+      if (++spins > (1 << 25)) {       // ~2-4 s: a peer is missing; report, fall back to what is there
+        *p2p.err = 1;
+        break;
+      }
+    }
+    __threadfence_system();
+    s_x[2 * t] = src[0];
+    s_x[2 * t + 1] = src[1];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double fc = __longlong_as_double(s_x[0]);
+    long long fi = s_x[1];
+    for (int g = 1; g < p2p.n_ranks; ++g) {
+      const double c = __longlong_as_double(s_x[2 * g]);
+      const long long i = s_x[2 * g + 1];
+      if (cat_better(c, i, fc, fi)) {
+        fc = c;
+        fi = i;
+      }
+    }
+    best_cost[prob] = fc;
+    best_idx[prob] = fi;
   }
 }
 
@@ -365,7 +431,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   // ---- argmin over the candidates of this problem ----
   const double jc = live ? (double)J : __longlong_as_double(0x7ff0000000000000LL);
   const long long ji = live ? (q.k_offset + k) : 0x7fffffffffffffffLL;
-  cat_grid_argmin(jc, ji, prob, block_best, tickets, best_cost, best_idx);
+  cat_grid_argmin(jc, ji, prob, block_best, tickets, best_cost, best_idx, q.p2p);
 }
 
 // fold of the per-rank winners gathered from G ranks, on the device: in = G x [cost bits, global idx]

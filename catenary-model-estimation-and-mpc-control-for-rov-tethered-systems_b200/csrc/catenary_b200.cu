@@ -328,6 +328,11 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.prog = nullptr;
   q.prog_consts = nullptr;
   q.n_ops_t = q.n_ops_g = q.n_c_t = q.n_c_g = 0;
+  q.p2p.peers = nullptr;
+  q.p2p.rank = 0;
+  q.p2p.n_ranks = 1;
+  q.p2p.seq = 0;
+  q.p2p.err = nullptr;
   q.u_nom = nullptr;
   q.step = nullptr;
   q.ref_len = p->H;
@@ -853,6 +858,48 @@ int ctrl_run(CatCtrl* k, int32_t n_steps) {
   return CAT_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// fused winner exchange over NVLink peer memory (CUDA IPC between the ranks of one node)
+struct CatP2P {
+  CatCtx* c;
+  int rank, n_ranks;
+  unsigned int seq;
+  long long* slots;          // this rank's buffer [2][n_ranks][CAT_P2P_SLOT_W]
+  long long** d_peers;       // device array of n_ranks buffer addresses
+  void* opened[CAT_P2P_MAX_RANKS];   // peers' mappings (null for self)
+  int* d_err;
+  bool connected;
+};
+
+void p2p_free(CatP2P* x) {
+  if (!x) return;
+  cudaSetDevice(x->c->device);
+  cudaStreamSynchronize(x->c->stream);
+  for (int i = 0; i < x->n_ranks; ++i)
+    if (x->opened[i]) cudaIpcCloseMemHandle(x->opened[i]);
+  if (x->slots) cudaFree(x->slots);
+  if (x->d_peers) cudaFree(x->d_peers);
+  if (x->d_err) cudaFree(x->d_err);
+  delete x;
+}
+
+template <typename T>
+int mpc_step_p2p_dev(CatCtx* c, CatP2P* x, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
+                     const double* p_ref, double* best_cost, long long* best_idx, T* costs) {
+  NEED(x != nullptr && x->c == c && x->connected);
+  CatMpcDev<T> q;
+  int rc = mpc_fill<T>(c, p, q);
+  if (rc) return rc;
+  const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
+  NEED(p->n_problems == 1 && problems && p_ref && best_cost && best_idx && (rng || controls));
+  q.p2p.peers = x->d_peers;
+  q.p2p.rank = x->rank;
+  q.p2p.n_ranks = x->n_ranks;
+  q.p2p.seq = ++x->seq;
+  q.p2p.err = x->d_err;
+  return mpc_launch<T>(c, q, problems, controls, p_ref, best_cost, best_idx, costs, nullptr, nullptr);
+}
+
 }  // namespace
 
 #define CTX()                          \
@@ -1371,6 +1418,94 @@ int cat_mpc_step_expr_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem*
   const CatHostPrograms hp = {n_ops_theta, n_consts_theta, n_ops_gamma, n_consts_gamma,
                               ops_theta,   ops_gamma,      consts_theta, consts_gamma};
   return mpc_step_host<float>(c, p, problems, controls, p_ref, best_cost, best_idx, costs, &hp);
+}
+
+int cat_p2p_create(void* ctx, int rank, int n_ranks, void** p2p, void* handle_out) {
+  CTX();
+  NEED(p2p != nullptr);
+  *p2p = nullptr;
+  NEED(handle_out && n_ranks >= 1 && n_ranks <= CAT_P2P_MAX_RANKS && rank >= 0 && rank < n_ranks);
+  int rc = bind(c);
+  if (rc) return rc;
+  CatP2P* x = new (std::nothrow) CatP2P();
+  if (!x) return fail(c, CAT_ENOMEM, "p2p allocation");
+  std::memset((void*)x, 0, sizeof(*x));
+  x->c = c;
+  x->rank = rank;
+  x->n_ranks = n_ranks;
+  const size_t bytes = (size_t)2 * n_ranks * CAT_P2P_SLOT_W * sizeof(long long);
+  cudaError_t e = cudaMalloc((void**)&x->slots, bytes);
+  if (e == cudaSuccess) e = cudaMemset(x->slots, 0, bytes);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&x->d_peers, (size_t)n_ranks * sizeof(long long*));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&x->d_err, 16);
+  if (e == cudaSuccess) e = cudaMemset(x->d_err, 0, 16);
+  cudaIpcMemHandle_t h;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, x->slots);
+  if (e != cudaSuccess) {
+    p2p_free(x);
+    return fail(c, CAT_ECUDA, "p2p buffers / cudaIpcGetMemHandle", e);
+  }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  std::memcpy(handle_out, &h, 64);
+  *p2p = x;
+  return CAT_OK;
+}
+int cat_p2p_connect(void* p2p, const void* all_handles) {
+  CatP2P* x = (CatP2P*)p2p;
+  if (!x) return CAT_EINVAL;
+  CatCtx* c = x->c;
+  NEED(all_handles != nullptr && !x->connected);
+  int rc = bind(c);
+  if (rc) return rc;
+  long long* table[CAT_P2P_MAX_RANKS];
+  for (int r = 0; r < x->n_ranks; ++r) {
+    if (r == x->rank) {
+      table[r] = x->slots;
+      continue;
+    }
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, (const char*)all_handles + (size_t)64 * r, 64);
+    void* ptr = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return fail(c, CAT_ECUDA, "cudaIpcOpenMemHandle (peer slot buffer)", e);
+    x->opened[r] = ptr;
+    table[r] = (long long*)ptr;
+  }
+  CU(cudaMemcpy(x->d_peers, table, (size_t)x->n_ranks * sizeof(long long*), cudaMemcpyHostToDevice));
+  x->connected = true;
+  return CAT_OK;
+}
+int cat_mpc_step_p2p_dev_f64(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
+                             const double* controls, const double* p_ref, double* best_cost, int64_t* best_idx,
+                             double* costs) {
+  CTX();
+  int rc = bind(c);
+  if (rc) return rc;
+  return mpc_step_p2p_dev<double>(c, (CatP2P*)p2p, p, problems, controls, p_ref, best_cost, (long long*)best_idx, costs);
+}
+int cat_mpc_step_p2p_dev_f32(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
+                             const float* controls, const double* p_ref, double* best_cost, int64_t* best_idx,
+                             float* costs) {
+  CTX();
+  int rc = bind(c);
+  if (rc) return rc;
+  return mpc_step_p2p_dev<float>(c, (CatP2P*)p2p, p, problems, controls, p_ref, best_cost, (long long*)best_idx, costs);
+}
+int cat_p2p_status(void* p2p, int* timed_out) {
+  CatP2P* x = (CatP2P*)p2p;
+  if (!x || !timed_out) return CAT_EINVAL;
+  CatCtx* c = x->c;
+  int rc = bind(c);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(c->stream));
+  CU(cudaMemcpy(timed_out, x->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+  return CAT_OK;
+}
+int cat_p2p_destroy(void* p2p) {
+  CatP2P* x = (CatP2P*)p2p;
+  if (!x) return CAT_EINVAL;
+  p2p_free(x);
+  return CAT_OK;
 }
 
 int cat_ctrl_create_f64(void* ctx, const CatMpcParams* p, const CatCtrlConfig* cfg, const CatMpcProblem* problems,

@@ -127,3 +127,61 @@ class PipelinedExchange:
 
     def drain(self):
         self.side.synchronize()
+
+
+class P2PWinnerExchange:
+    """Fused multi-GPU step: ONE kernel per step per rank.  The rollout's last block writes this
+    rank's (cost, global idx) into every peer's slot buffer over NVLink (CUDA IPC mappings), waits for the peers'
+    winners of the same step and folds them in rank order -- when the kernel ends, ``step.winner`` holds the
+    JOB-WIDE winner on every rank (same value as ``exchange_winner``), with no NCCL call and no second launch.
+    The process group is used once, at construction, to swap the 64-byte IPC handles."""
+
+    def __init__(self, step, group=None):
+        import ctypes as C
+
+        import torch
+        import torch.distributed as dist
+        self.step, self.torch = step, torch
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if step.n != 1:
+            raise ValueError("the fused exchange handles one problem per launch")
+        ctx = step.ctx
+        self.ctx = ctx
+        h = C.c_void_p()
+        handle = (C.c_ubyte * 64)()
+        ctx.check(ctx.lib.cat_p2p_create(ctx.handle, self.rank, self.world, C.byref(h), handle))
+        self.handle = h
+        mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=step.dev)
+        allh = torch.empty(64 * self.world, dtype=torch.uint8, device=step.dev)
+        dist.all_gather_into_tensor(allh, mine, group=group)
+        buf = (C.c_ubyte * (64 * self.world)).from_buffer_copy(bytes(allh.cpu().numpy().tobytes()))
+        rc = ctx.lib.cat_p2p_connect(self.handle, buf)
+        dist.barrier(group)                                 # every rank has mapped every buffer before step 1
+        ctx.check(rc)
+        self._fn = ctx.lib.cat_mpc_step_p2p_dev_f64 if step.dtype == np.float64 else ctx.lib.cat_mpc_step_p2p_dev_f32
+
+    def launch(self, winner=None):
+        """Enqueue one step on torch's current stream; ``winner`` (int64[2] device) receives [cost bits, idx]."""
+        import ctypes as C
+        st = self.step
+        w = st.winner if winner is None else winner
+        self.ctx.set_stream(self.torch.cuda.current_stream(st.dev).cuda_stream)
+        self.ctx.check(self._fn(self.ctx.handle, self.handle, C.byref(st.params), st.problems.data_ptr(),
+                                None if st.controls is None else st.controls.data_ptr(), st.p_ref.data_ptr(),
+                                w.data_ptr(), w.data_ptr() + 8, None if st.costs is None else st.costs.data_ptr()))
+
+    def result(self, winner=None):
+        """(best_idx, best_cost) of the whole job (blocks on the stream)."""
+        w = (self.step.winner if winner is None else winner).cpu().numpy()
+        return int(w[1]), float(w[:1].view(np.float64)[0])
+
+    def timed_out(self):
+        import ctypes as C
+        v = C.c_int()
+        self.ctx.check(self.ctx.lib.cat_p2p_status(self.handle, C.byref(v)))
+        return bool(v.value)
+
+    def close(self):
+        if getattr(self, "handle", None) and self.ctx.handle:
+            self.ctx.lib.cat_p2p_destroy(self.handle)
+        self.handle = None

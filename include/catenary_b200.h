@@ -286,6 +286,26 @@ CAT_API int cat_mpc_step_expr_f32(void* ctx, const CatMpcParams* p, const CatMpc
                                   int32_t n_ops_gamma, const int32_t* ops_gamma, int32_t n_consts_gamma,
                                   const double* consts_gamma, double* best_cost, int64_t* best_idx, float* costs);
 
+/* ---- fused multi-GPU winner exchange over NVLink peer memory --------------------
+ * One process per GPU on one node.  Each rank creates its slot buffer (cat_p2p_create -> a 64-byte CUDA IPC
+ * handle), the ranks exchange the handles by any means (torch.distributed all_gather) and map each other's
+ * buffers (cat_p2p_connect, handles in rank order).  cat_mpc_step_p2p_dev_* is then ONE kernel per step: the
+ * rollout's last block writes this rank's (cost, global idx) into every peer's buffer, waits for the peers'
+ * winners of the same step and folds them in rank order, so best_cost / best_idx (device pointers, one value
+ * each) hold the JOB-WIDE winner on every rank when the kernel ends -- no NCCL call, no second launch.  Every
+ * rank must launch the same sequence of steps; n_problems must be 1.  cat_p2p_status synchronises and reports
+ * whether any step gave up waiting for a peer (~seconds). */
+CAT_API int cat_p2p_create(void* ctx, int rank, int n_ranks, void** p2p, void* handle_out /* 64 bytes */);
+CAT_API int cat_p2p_connect(void* p2p, const void* all_handles /* n_ranks x 64 bytes, rank order */);
+CAT_API int cat_mpc_step_p2p_dev_f64(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
+                                     const double* controls, const double* p_ref, double* best_cost,
+                                     int64_t* best_idx, double* costs);
+CAT_API int cat_mpc_step_p2p_dev_f32(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
+                                     const float* controls, const double* p_ref, double* best_cost,
+                                     int64_t* best_idx, float* costs);
+CAT_API int cat_p2p_status(void* p2p, int* timed_out);
+CAT_API int cat_p2p_destroy(void* p2p);
+
 /* ---- receding-horizon controller around the sampling-MPC step ----
  * The role the (absent) pympc controller played at the reference's call sites: every control step samples K
  * candidate sequences around a nominal one, rolls them out (the kernel above), picks / blends the next nominal

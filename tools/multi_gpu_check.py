@@ -59,6 +59,40 @@ def main():
         want = cb.reduce_winners([w[0] for w in winners], [w[1] for w in winners])
         assert want == got, (want, got)
         out["config4"]["single_gpu_replay_agrees"] = True
+    # ---- the same job through the fused peer-memory exchange: one kernel per step, no NCCL on the data path ----
+    fused = dmod.P2PWinnerExchange(job.step)
+    for _ in range(3):
+        fused.launch()
+    got_f = fused.result()
+    assert got_f == got, (got_f, got)
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(n_it):
+        fused.launch()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_f = torch.tensor([e0.elapsed_time(e1) / n_it], device=f"cuda:{local}", dtype=torch.float64)
+    dist.all_reduce(ms_f, op=dist.ReduceOp.MAX)
+    assert fused.result() == got and not fused.timed_out()
+    # small job: exchange latency matters (config-3 shard size per rank)
+    small = dmod.ShardedMpcStep(p, cb.circle_reference(50, p["dt"]), 65536 * world, sigma, seed=5, device=local)
+    fs = dmod.P2PWinnerExchange(small.step)
+    lat = {}
+    for name, fn in (("nccl_host_fold", small.run), ("fused_p2p", lambda: (fs.launch(), fs.result())[1])):
+        for _ in range(5):
+            r = fn()
+        dist.barrier()
+        ts = []
+        for _ in range(200):
+            t0 = time.perf_counter()
+            r = fn()
+            ts.append(time.perf_counter() - t0)
+        lat[name] = {"p50_ms": sorted(ts)[100] * 1e3, "winner": list(r)}
+    assert lat["nccl_host_fold"]["winner"] == lat["fused_p2p"]["winner"], lat
+    out["config4"]["fused_p2p_ms_per_step"] = float(ms_f.item())
+    out["config4"]["fused_p2p_agrees"] = True
+    out["step_latency_65536_per_rank"] = lat
     # ---- config 5: fleet, sharded by problem, no communication ----
     n_prob, Kf, Hf = 4096, 4096, 50
     lo, hi = dmod.fleet_shard(n_prob, rank, world)
