@@ -174,12 +174,28 @@ def run_ours(args):
     dev_sets = [torch.from_numpy(b).to(f"cuda:{local}") for b in host_sets]
     step = devmod.MpcDeviceStep(p, pref, K, controls=host_sets[0], k_offset=rank * K, device=local, ctx=ctx)
 
-    pipe = dist_mod.PipelinedExchange(step) if world > 1 else None
+    # N > 1: the winners are exchanged INSIDE the rollout kernel through NVLink peer memory (CUDA IPC slot
+    # buffers, distributed.P2PWinnerExchange): one kernel per step, no NCCL on the data path.  If the IPC mapping
+    # is refused in this environment the NCCL path (side-stream all-gather + device fold, double-buffered) runs
+    # instead; config.exchange says which.
+    fused = pipe = None
+    if world > 1:
+        try:
+            fused = dist_mod.P2PWinnerExchange(step)
+        except Exception as exc:                                  # noqa: BLE001 -- any IPC failure -> NCCL path
+            sys.stderr.write(f"[bench] fused P2P exchange unavailable ({exc}); using NCCL\n")
+        ok = torch.tensor([1 if fused is not None else 0], device=f"cuda:{local}")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            fused = None
+            pipe = dist_mod.PipelinedExchange(step)
 
     def one(i, wait=False):
-        """One MPC step.  N > 1: rollout on the main stream, 16-byte all-gather + device fold on a side stream
-        (double-buffered, no host sync); ``wait`` blocks for the job-wide winner (the latency loop)."""
+        """One MPC step; ``wait`` blocks for the job-wide winner (the latency loop)."""
         step.set_controls(dev_sets[i % n_sets])
+        if fused is not None:
+            fused.launch()
+            return fused.result() if wait else None
         if pipe is None:
             step.launch()
             return None
@@ -216,10 +232,16 @@ def run_ours(args):
     launches = ctx.launch_count - l0
     if pipe is not None:
         launches += args.steps                                  # k_reduce_winners, one per step, on the side stream
-        # the pipelined exchange must agree with the plain host-side exchange
+    if world > 1:
+        # the in-kernel / pipelined exchange must agree with the plain NCCL all-gather + host fold
         step.launch()
         want = dist_mod.exchange_winner(step.winner)
-        got = pipe.result(pipe.submit())
+        if fused is not None:
+            fused.launch()
+            got = fused.result()
+            assert not fused.timed_out()
+        else:
+            got = pipe.result(pipe.submit())
         assert got == want, (got, want)
     ms_total = e0.elapsed_time(e1)
     if world > 1:
@@ -410,7 +432,10 @@ def run_ours(args):
            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
            "config": {"workload": "config3", "candidates_per_gpu": K, "horizon": H, "dt": p["dt"],
-                      "controls": "explicit fp64 SoA [H][3][K]", "exchange": "nccl all_gather 16 B/rank + device fold on a side stream, double-buffered" if world > 1 else "none",
+                      "controls": "explicit fp64 SoA [H][3][K]", "exchange": ("none" if world == 1 else
+                                   "fused in the rollout kernel: 16-B winners through NVLink peer memory (CUDA IPC), "
+                                   "rank-order fold in the last block" if fused is not None else
+                                   "nccl all_gather 16 B/rank + device fold on a side stream, double-buffered"),
                       "l2": "3 rotating control sets (236 MB) > 126 MB L2"},
            "p50_ms": lat[len(lat) // 2], "p99_ms": lat[int(len(lat) * 0.99)], "latency_samples": len(lat),
            "clocks": clocks, "e2e": e2e, "closed_loop": closed, "config1": config1, "fp32_fast_mode": fp32, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
