@@ -216,8 +216,9 @@ def run_ours(args):
     barrier()
     t_wait = time.time()
     while not sampler.lines and time.time() - t_wait < 5.0:      # nvidia-smi takes ~1 s to print its first sample
-        one(0)
-        torch.cuda.synchronize()
+        step.launch()                                            # rank-local keep-busy: NOT a collective step (the
+        torch.cuda.synchronize()                                 # ranks leave this loop after different trip counts)
+    barrier()
     # ---- device-timed throughput: K steps between two events on the launching stream ----
     l0 = ctx.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
