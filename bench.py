@@ -249,6 +249,42 @@ def run_ours(args):
         t = torch.tensor([ms_total], device=f"cuda:{local}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
+    # ---- for comparison at N > 1: the NCCL path (all-gather + device fold on a side stream, double-buffered so
+    #      the exchange of step i overlaps the rollout of step i+1; the winner arrives one step late) ----
+    nccl_cmp = None
+    if fused is not None:
+        pipe2 = dist_mod.PipelinedExchange(step)
+        for i in range(5):
+            step.set_controls(dev_sets[i % n_sets])
+            pipe2.submit()
+        pipe2.drain()
+        dist.barrier()
+        torch.cuda.synchronize()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for i in range(args.steps):
+            step.set_controls(dev_sets[i % n_sets])
+            pipe2.submit()
+        torch.cuda.current_stream().wait_stream(pipe2.side)
+        f1.record()
+        pipe2.drain()
+        dist.barrier()
+        torch.cuda.synchronize()
+        t = torch.tensor([f0.elapsed_time(f1)], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        nccl_ms = float(t.item()) / args.steps
+        lat2 = []
+        for i in range(100):
+            step.set_controls(dev_sets[i % n_sets])
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            pipe2.result(pipe2.submit())
+            b.record()
+            b.synchronize()
+            lat2.append(a.elapsed_time(b))
+        lat2.sort()
+        nccl_cmp = {"ms_per_step": nccl_ms, "value": world * K * H / (nccl_ms * 1e-3), "p50_ms": lat2[50],
+                    "what": "same steps through NCCL all_gather + device fold on a side stream (pipelined)"}
     # ---- per-step latency distribution (p50 MPC solve latency, D2H of the 16-byte winner included) ----
     lat = []
     n_lat = min(max(args.steps, 200), 2000)
@@ -439,7 +475,7 @@ def run_ours(args):
                                    "nccl all_gather 16 B/rank + device fold on a side stream, double-buffered"),
                       "l2": "3 rotating control sets (236 MB) > 126 MB L2"},
            "p50_ms": lat[len(lat) // 2], "p99_ms": lat[int(len(lat) * 0.99)], "latency_samples": len(lat),
-           "clocks": clocks, "e2e": e2e, "closed_loop": closed, "config1": config1, "fp32_fast_mode": fp32, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+           "clocks": clocks, "e2e": e2e, "closed_loop": closed, "config1": config1, "fp32_fast_mode": fp32, "nccl_exchange": nccl_cmp, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
     emit(json.dumps(out))
     if world > 1:
         dist.barrier()
