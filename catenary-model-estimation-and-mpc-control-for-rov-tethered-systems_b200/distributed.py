@@ -151,10 +151,11 @@ class P2PWinnerExchange:
         handle = (C.c_ubyte * 64)()
         ctx.check(ctx.lib.cat_p2p_create(ctx.handle, self.rank, self.world, C.byref(h), handle))
         self.handle = h
-        mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=step.dev)
-        allh = torch.empty(64 * self.world, dtype=torch.uint8, device=step.dev)
-        dist.all_gather_into_tensor(allh, mine, group=group)
-        buf = (C.c_ubyte * (64 * self.world)).from_buffer_copy(bytes(allh.cpu().numpy().tobytes()))
+        hdev = step.dev if dist.get_backend(group) == "nccl" else torch.device("cpu")   # gloo: host tensors
+        mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=hdev)
+        parts = [torch.empty(64, dtype=torch.uint8, device=hdev) for _ in range(self.world)]
+        dist.all_gather(parts, mine, group=group)
+        buf = (C.c_ubyte * (64 * self.world)).from_buffer_copy(b"".join(bytes(t.cpu().numpy().tobytes()) for t in parts))
         rc = ctx.lib.cat_p2p_connect(self.handle, buf)
         dist.barrier(group)                                 # every rank has mapped every buffer before step 1
         ctx.check(rc)
