@@ -15,7 +15,9 @@
  *    host<->device copies on the ctx stream; *_dev functions take DEVICE pointers, enqueue on the
  *    ctx stream and return without synchronising (cat_sync to wait).
  *  - one ctx = one device + one stream; calls on one ctx are serialised by the caller.
- *  - there is NO CPU fallback: without a CUDA device cat_init fails with CAT_ECUDA.
+ *  - there is NO CPU fallback: without a CUDA device cat_init fails with CAT_ENODEV.
+ *  - objects created on a ctx (cat_ctrl_create_*, cat_p2p_create) hold a pointer to it: destroy them before
+ *    cat_destroy(ctx).
  */
 #ifndef CATENARY_B200_H
 #define CATENARY_B200_H
