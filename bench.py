@@ -194,11 +194,11 @@ def run_ours(args):
         """One MPC step; ``wait`` blocks for the job-wide winner (the latency loop)."""
         step.set_controls(dev_sets[i % n_sets])
         if fused is not None:
-            fused.launch()
-            return fused.result() if wait else None
+            fused.launch(to_host=wait)
+            return fused.result_host() if wait else None
         if pipe is None:
-            step.launch()
-            return None
+            step.launch(to_host=wait)                       # latency loop: the kernel writes the 16-byte winner
+            return step.result_host() if wait else None     # into device-mapped pinned memory (no D2H copy)
         slot = pipe.submit()
         return pipe.result(slot) if wait else None
 
@@ -292,8 +292,7 @@ def run_ours(args):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         r = one(i, wait=True)
-        if r is None:
-            step.result()
+        assert r is not None
         b.record()
         b.synchronize()
         lat.append(a.elapsed_time(b))

@@ -997,7 +997,7 @@ int cat_host_alloc(void* ctx, size_t bytes, void** out) {
   NEED(out != nullptr);
   int rc = bind(c);
   if (rc) return rc;
-  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 16, cudaHostAllocDefault);
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 16, cudaHostAllocMapped | cudaHostAllocPortable);   // device-visible under UVA
   if (e != cudaSuccess) return fail(c, CAT_ENOMEM, "cudaHostAlloc", e);
   return CAT_OK;
 }

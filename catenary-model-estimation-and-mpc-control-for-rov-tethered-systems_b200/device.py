@@ -47,22 +47,41 @@ class MpcDeviceStep:
         self.best_cost = self.winner[:n].view(torch.float64)
         self.best_idx = self.winner[n:]
         self.costs = torch.empty((n, K), dtype=tdt, device=self.dev) if keep_costs else None
+        self._host_winner = None
         self._fn = self.ctx.lib.cat_mpc_step_dev_f64 if self.dtype == np.float64 else self.ctx.lib.cat_mpc_step_dev_f32
 
     def set_controls(self, controls_dev):
         """Swap in another device tensor of candidate controls (same layout and dtype)."""
         self.controls = controls_dev
 
-    def launch(self, winner=None):
+    def host_winner(self):
+        """int64 [2n] view of page-locked, device-mapped host memory: with ``launch(to_host=True)`` the kernel's
+        last block writes [cost bits | idx] straight into it over PCIe, so the step needs no D2H copy."""
+        if self._host_winner is None:
+            self._host_winner = self.ctx.pinned_empty((2 * self.n,), np.int64)
+            self._host_winner[:] = 0
+        return self._host_winner
+
+    def launch(self, winner=None, to_host=False):
         """Enqueue the step on torch's current stream; returns immediately.  ``winner``: alternative int64
-        [2n] device buffer for [cost bits | idx] (double-buffering across pipelined steps)."""
+        [2n] device buffer for [cost bits | idx] (double-buffering across pipelined steps); ``to_host``: write
+        the winner into ``host_winner()`` instead (read it with ``result_host``)."""
         torch = self.torch
-        w = self.winner if winner is None else winner
+        if to_host:
+            wp = self.host_winner().ctypes.data
+        else:
+            wp = (self.winner if winner is None else winner).data_ptr()
         self.ctx.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
         self.ctx.check(self._fn(self.ctx.handle, C.byref(self.params), self.problems.data_ptr(),
                                 None if self.controls is None else self.controls.data_ptr(), self.p_ref.data_ptr(),
-                                w.data_ptr(), w.data_ptr() + 8 * self.n,
+                                wp, wp + 8 * self.n,
                                 None if self.costs is None else self.costs.data_ptr()))
+
+    def result_host(self):
+        """(best_idx (n,), best_cost (n,)) of the last ``launch(to_host=True)``: a stream synchronise, no copy."""
+        self.torch.cuda.current_stream(self.dev).synchronize()
+        w = self.host_winner()
+        return w[self.n:].copy(), w[:self.n].view(np.float64).copy()
 
     def result(self):
         """(best_idx (n,), best_cost (n,)) on the host (one small D2H + sync)."""

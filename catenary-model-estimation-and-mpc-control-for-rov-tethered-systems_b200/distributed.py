@@ -161,15 +161,20 @@ class P2PWinnerExchange:
         ctx.check(rc)
         self._fn = ctx.lib.cat_mpc_step_p2p_dev_f64 if step.dtype == np.float64 else ctx.lib.cat_mpc_step_p2p_dev_f32
 
-    def launch(self, winner=None):
-        """Enqueue one step on torch's current stream; ``winner`` (int64[2] device) receives [cost bits, idx]."""
+    def launch(self, winner=None, to_host=False):
+        """Enqueue one step on torch's current stream; ``winner`` (int64[2] device) receives [cost bits, idx];
+        ``to_host`` writes it into the step's device-mapped host buffer instead (``step.result_host()``)."""
         import ctypes as C
         st = self.step
-        w = st.winner if winner is None else winner
+        wp = st.host_winner().ctypes.data if to_host else (st.winner if winner is None else winner).data_ptr()
         self.ctx.set_stream(self.torch.cuda.current_stream(st.dev).cuda_stream)
         self.ctx.check(self._fn(self.ctx.handle, self.handle, C.byref(st.params), st.problems.data_ptr(),
                                 None if st.controls is None else st.controls.data_ptr(), st.p_ref.data_ptr(),
-                                w.data_ptr(), w.data_ptr() + 8, None if st.costs is None else st.costs.data_ptr()))
+                                wp, wp + 8, None if st.costs is None else st.costs.data_ptr()))
+
+    def result_host(self):
+        i, c = self.step.result_host()
+        return int(i[0]), float(c[0])
 
     def result(self, winner=None):
         """(best_idx, best_cost) of the whole job (blocks on the stream)."""

@@ -359,6 +359,9 @@ def test_device_step_matches_host_call(cb):
     i2, c2 = st.result()
     assert int(i2[0]) == bi and float(c2[0]) == bc
     assert np.array_equal(st.costs.cpu().numpy()[0], J)
+    st.launch(to_host=True)                                 # winner written by the kernel into mapped pinned memory
+    i3, c3 = st.result_host()
+    assert int(i3[0]) == bi and float(c3[0]) == bc
 
 
 def test_errors_are_values_not_crashes(cb):
