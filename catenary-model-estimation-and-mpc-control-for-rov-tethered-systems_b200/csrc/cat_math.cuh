@@ -203,11 +203,22 @@ template <> struct CatMath<float> {
   }
   static __device__ __forceinline__ float exp_(float x) { return __expf(x); }
   static __device__ __forceinline__ float log_(float x) { return __logf(x); }
-  static __device__ __forceinline__ float sqrt_(float x) { return __fsqrt_rn(x); }
+  // fast mode = single MUFU instructions (sqrt.approx / rcp.approx, <= 1-2 ulp), not the IEEE-rounded
+  // sequences: __fsqrt_rn / __frcp_rn cost a MUFU + Newton step + a special-case branch each, which was 15% of
+  // the fp32 rollout's instructions and most of its branches (profiles/r1_ncu_full_k_mpc_rollout_f32.csv)
+  static __device__ __forceinline__ float sqrt_(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+  }
   static __device__ __forceinline__ float abs_(float x) { return fabsf(x); }
-  static __device__ __forceinline__ float rcp_(float x) { return __frcp_rn(x); }
+  static __device__ __forceinline__ float rcp_(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+  }
   static __device__ __forceinline__ float div_(float a, float b) { return __fdividef(a, b); }
-  static __device__ __forceinline__ float rcp_fast_(float x) { return __frcp_rn(x); }
+  static __device__ __forceinline__ float rcp_fast_(float x) { return rcp_(x); }
   static __device__ __forceinline__ float min_(float a, float b) { return fminf(a, b); }
   static __device__ __forceinline__ float max_(float a, float b) { return fmaxf(a, b); }
   static __device__ __forceinline__ float fma_(float a, float b, float c) { return fmaf(a, b, c); }
