@@ -14,3 +14,4 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 ncu --set full --clock-control none --import-source on -k regex:k_mpc_rollout -s 3 -c 2 -f -o gpurun_out/mpc_full python tools/prof_mpc.py 65536 50 8 > gpurun_out/ncu_mpc.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_shape -s 1 -c 1 -f -o gpurun_out/shape_full python tools/prof_shape.py > gpurun_out/ncu_shape.log 2>&1
 ls -la gpurun_out
+ncu --set full --clock-control none --import-source on -k regex:k_mpc_rollout -s 3 -c 1 -f -o gpurun_out/mpc_f32 python tools/prof_mpc.py 65536 50 8 x f32 > gpurun_out/ncu_f32.log 2>&1
