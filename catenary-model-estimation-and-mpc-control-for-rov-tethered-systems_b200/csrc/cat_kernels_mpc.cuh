@@ -252,7 +252,7 @@ __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int pro
   }
 }
 
-template <typename T, bool GENERIC, bool VM = false>
+template <typename T, bool GENERIC, bool VM = false, bool RNG = false>
 __global__ void __launch_bounds__(CAT_MPC_BLOCK, 4)   // <= 128 registers: config 3 needs 3.5 blocks per SM resident
 k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, const T* __restrict__ controls,
               const double* __restrict__ p_ref, T* __restrict__ costs, CatBest* __restrict__ block_best,
@@ -292,7 +292,9 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   T J = T(0);
   CatWarm<T> warm = cat_cold<T>();
 
-  const bool rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
+  // control source fixed at compile time: the explicit-controls kernel carries no Philox / Box-Muller code
+  // (a third of the loop's SASS) and the sampling kernel no control loads
+  constexpr bool rng = RNG;
   const T* uc = rng ? nullptr : controls + (long long)prob * q.sp + kk * q.sk;
   // controller mode: the step counter lives in HBM so that one captured graph serves every control step
   int t0 = 0;

@@ -360,16 +360,20 @@ int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, 
     tk = (unsigned int*)pp;
   }
   const bool shipped = (q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED);
+  const bool rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
+  const size_t smem =
+      q.prog ? (size_t)(q.n_ops_t + q.n_ops_g) * sizeof(int2) + (size_t)(q.n_c_t + q.n_c_g + 2) * sizeof(T) : 0;
+#define CAT_MPC_LAUNCH(GEN, VM, RNG) \
+  k_mpc_rollout<T, GEN, VM, RNG><<<grid, block, smem, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk, \
+                                                                   best_cost, best_idx)
   if (q.prog) {   // run-time equation programs
-    const size_t smem = (size_t)(q.n_ops_t + q.n_ops_g) * sizeof(int2) + (size_t)(q.n_c_t + q.n_c_g + 2) * sizeof(T);
-    k_mpc_rollout<T, false, true><<<grid, block, smem, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk,
-                                                                    best_cost, best_idx);
-  } else if (shipped)
-    k_mpc_rollout<T, false><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk, best_cost,
-                                                           best_idx);
-  else
-    k_mpc_rollout<T, true><<<grid, block, 0, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk, best_cost,
-                                                          best_idx);
+    if (rng) CAT_MPC_LAUNCH(false, true, true); else CAT_MPC_LAUNCH(false, true, false);
+  } else if (shipped) {
+    if (rng) CAT_MPC_LAUNCH(false, false, true); else CAT_MPC_LAUNCH(false, false, false);
+  } else {
+    if (rng) CAT_MPC_LAUNCH(true, false, true); else CAT_MPC_LAUNCH(true, false, false);
+  }
+#undef CAT_MPC_LAUNCH
   LAUNCHED();
   return CAT_OK;
 }
