@@ -287,6 +287,11 @@ __device__ __forceinline__ T cat_u_guess(T e) {
   return lr + M::log_(lr + M::log_(M::max_(lr, T(1))));
 }
 
+// the same, out of line: in the rollout only the first solve of a candidate is cold, and ~350 SASS
+// instructions of log/sqrt/div code leave its loop body
+template <typename T, typename M>
+__device__ __noinline__ T cat_u_guess_cold(T e) { return cat_u_guess<T, M>(e); }
+
 // One safeguarded Halley step for the root of  G(u) = D (sinh u - u) - N u,  N = L^2 - dH^2 - l^2,
 // D = l (sqrt(L^2 - dH^2) + l):  the same root as g(u) = (sinh u - u) - e u with e = N / D, without
 // forming the quotient.  G' = D (cosh u - 1) - N, G'' = D sinh u.  The quotient of the step uses the
@@ -296,14 +301,14 @@ __device__ __forceinline__ T cat_halley_step(T u, T N, T D, T sm, T cm, T sh) {
   const T G = D * sm - N * u;
   const T Gp = D * cm - N;
   const T den = T(2) * Gp * Gp - G * (D * sh);
-  T du;
-  if (Gp > T(0) && den > T(0)) {
-    du = T(2) * G * Gp * M::rcp_fast_(den);    // Halley
-  } else if (Gp > T(0)) {
-    du = G * M::rcp_fast_(Gp);                 // Newton
-  } else {
-    du = -(T(0.5) * u + T(0.1));               // left of the minimum of G: move right
-  }
+  // Branch-free: the three cases share one reciprocal (selected operands, identical arithmetic per lane), so
+  // the step is straight-line code inside the caller's basic block.
+  const bool newton = Gp > T(0);
+  const bool halley = newton && den > T(0);
+  const T num = halley ? T(2) * G * Gp : G;
+  const T dn = halley ? den : Gp;
+  T du = num * M::rcp_fast_(dn);               // Halley, else Newton (junk when !newton, replaced below)
+  if (!newton) du = -(T(0.5) * u + T(0.1));    // left of the minimum of G: move right
   if (!(du < u)) du = T(0.5) * u;              // keep u > 0
   return du;
 }
@@ -318,7 +323,8 @@ __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w)
   if (w.u > T(0)) {
     u = w.u - cat_halley_step<T, M>(w.u, N, D, w.sm, w.cm, w.sh);
   } else {
-    u = cat_u_guess<T, M>(M::div_(N, D));
+    if constexpr (FULL_WARP) u = cat_u_guess_cold<T, M>(M::div_(N, D));
+    else u = cat_u_guess<T, M>(M::div_(N, D));
   }
   T sm, cm, sh, du;
   // The first iteration is straight-line code: with a warm start it is also the last one, and without a
@@ -429,9 +435,9 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, c
 template <typename T, typename M>
 __device__ __forceinline__ T cat_z_low(const CatSpan<T>& s, T l, T L, T zA, T zB) {
   const T zmin = zB < zA ? zB : zA;
-  if (!(s.C == s.C) || !s.inside) return zmin;
-  // (zA+zB)/2 + (l sh - L ch u) / (2 sh u)
-  return T(0.5) * (zA + zB) + (l * s.sh - L * s.ch * s.u) * M::rcp_fast_(T(2) * s.sh * s.u);
+  // (zA+zB)/2 + (l sh - L ch u) / (2 sh u); select instead of an early return (no branch in the rollout loop)
+  const T zv = T(0.5) * (zA + zB) + (l * s.sh - L * s.ch * s.u) * M::rcp_fast_(T(2) * s.sh * s.u);
+  return (!(s.C == s.C) || !s.inside) ? zmin : zv;
 }
 
 // ------------------------------------------------------------------------------------------
