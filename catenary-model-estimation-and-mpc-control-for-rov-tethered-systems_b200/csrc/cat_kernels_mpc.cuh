@@ -290,7 +290,12 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   T A[3] = {T(pb->A1[0]), T(pb->A1[1]), T(pb->A1[2])};
   T th = T(pb->theta), ga = T(pb->gamma), thp = T(pb->theta_prev), gap = T(pb->gamma_prev);
   T J = T(0);
-  CatWarm<T> warm = cat_cold<T>();
+  // warm-start record of the catenary solve, seeded from the initial pose (a step moves the span by ~1e-3)
+  CatWarm<T> warm;
+  {
+    const T wx = P[0] - P0[0], wy = P[1] - P0[1];
+    warm = cat_warm_guess<T, M>(M::sqrt_(wx * wx + wy * wy), P[2] - P0[2], q.L);
+  }
 
   // control source fixed at compile time: the explicit-controls kernel carries no Philox / Box-Muller code
   // (a third of the loop's SASS) and the sampling kernel no control loads
@@ -417,7 +422,16 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     for (int j = 0; j < 18; ++j) x0[j] = xs[1][j];
     x0[14] = (th - CatScaler<T>::mean(14)) * CatScaler<T>::inv_scale(14);
     x0[15] = (ga - CatScaler<T>::mean(15)) * CatScaler<T>::inv_scale(15);
-    if (carry_t && carry_g) {
+    if constexpr (!GENERIC && !VM) {
+      // shipped pair: which slopes carry over is known at compile time; only the other one is evaluated (an
+      // unused sin still leaves its range check, branch and slow-path call behind -- the compiler cannot
+      // prove the CUDA reduction routine free of side effects)
+      constexpr bool CT = (CAT_DTHETA_LIVE_MASK & 0xC000u) == 0, CG = (CAT_DGAMMA_LIVE_MASK & 0xC000u) == 0;
+      k1t = k4t;
+      k1g = k4g;
+      if constexpr (!CT) k1t = cat_dtheta_dt<T, M>(x0);
+      if constexpr (!CG) k1g = cat_dgamma_dt<T, M>(x0);
+    } else if (carry_t && carry_g) {
       k1t = k4t;
       k1g = k4g;
     } else {

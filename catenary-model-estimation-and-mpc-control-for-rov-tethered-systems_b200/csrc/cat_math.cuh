@@ -63,7 +63,8 @@ __device__ __forceinline__ void cat_sin_vec_f64(double (&a)[N]) {
     r[n] = fma(-qf, CAT_PI_C[4], rr);
     z[n] = r[n] * r[n];
     p[n] = CAT_SIN_C[9];
-    bad = bad || !(fabs(a[n]) < 1.0e5);
+    // |a| >= 1e5, inf or NaN, tested on the high word (integer pipe; 0x40F86A00 = high word of 1e5)
+    bad = bad || (__double2hiint(a[n]) & 0x7fffffff) >= 0x40F86A00;
   }
 #pragma unroll
   for (int i = 8; i >= 0; --i) {
@@ -79,7 +80,7 @@ __device__ __forceinline__ void cat_sin_vec_f64(double (&a)[N]) {
   if (bad) {
 #pragma unroll
     for (int n = 0; n < N; ++n)
-      if (!(fabs(a[n]) < 1.0e5)) r[n] = sin(a[n]);
+      if ((__double2hiint(a[n]) & 0x7fffffff) >= 0x40F86A00) r[n] = sin(a[n]);
   }
 #pragma unroll
   for (int n = 0; n < N; ++n) a[n] = r[n];
@@ -91,9 +92,10 @@ __device__ __forceinline__ double cat_sin_f64(double x) {
   return a[0];
 }
 
-// sqrt(x) for x >= 0 without the IEEE special-case path: MUFU.RSQ64H seed + two coupled Newton steps
-// (~1 ulp).  Every special input (0, denormal, inf, negative, NaN) makes the fast result NaN and takes the
-// one cold branch to the IEEE routine.
+// sqrt(x) without the IEEE special-case path and without a branch: MUFU.RSQ64H seed + two coupled Newton
+// steps (~1 ulp) for normal positive x.  The special inputs are patched by integer selects on the high word,
+// so the routine stays inside the caller's basic block and adds nothing to the FP64 pipe:
+//   +-0 and denormals -> x itself (|error| < 1.5e-154 for a denormal), +inf and NaN -> x, negative -> NaN.
 __device__ __forceinline__ double cat_sqrt_f64(double x) {
   double y;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
@@ -104,8 +106,11 @@ __device__ __forceinline__ double cat_sqrt_f64(double x) {
   h = fma(h, e, h);
   e = fma(-g, g, x);           // residual x - g^2
   g = fma(e, h, g);
-  if (g != g) g = sqrt(x);     // x = 0, denormal, inf, negative or NaN: the seed is inf/0/NaN -> IEEE routine
-  return g;
+  const int hx = __double2hiint(x);
+  const bool special = (unsigned)(hx - 0x00100000) >= 0x7fe00000u;   // exponent 0, exponent 0x7ff, or sign set
+  const bool negative = (unsigned)hx >= 0x80100000u;                 // below -2^-1022 (incl. -inf, -NaN)
+  const double fix = __hiloint2double(negative ? 0x7ff80000 : hx, __double2loint(x));
+  return special ? fix : g;
 }
 
 // For u >= 0: sh = sinh u, cm = cosh u - 1, sm = sinh u - u, all without cancellation at small u and
@@ -287,11 +292,6 @@ __device__ __forceinline__ T cat_u_guess(T e) {
   return lr + M::log_(lr + M::log_(M::max_(lr, T(1))));
 }
 
-// the same, out of line: in the rollout only the first solve of a candidate is cold, and ~350 SASS
-// instructions of log/sqrt/div code leave its loop body
-template <typename T, typename M>
-__device__ __noinline__ T cat_u_guess_cold(T e) { return cat_u_guess<T, M>(e); }
-
 // One safeguarded Halley step for the root of  G(u) = D (sinh u - u) - N u,  N = L^2 - dH^2 - l^2,
 // D = l (sqrt(L^2 - dH^2) + l):  the same root as g(u) = (sinh u - u) - e u with e = N / D, without
 // forming the quotient.  G' = D (cosh u - 1) - N, G'' = D sinh u.  The quotient of the step uses the
@@ -320,11 +320,10 @@ __device__ __forceinline__ T cat_halley_step(T u, T N, T D, T sm, T cm, T sh) {
 template <typename T, typename M, bool FULL_WARP = false>
 __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w) {
   T u;
-  if (w.u > T(0)) {
+  if (FULL_WARP || w.u > T(0)) {   // FULL_WARP callers always hand in a record (cat_warm_guess before their loop)
     u = w.u - cat_halley_step<T, M>(w.u, N, D, w.sm, w.cm, w.sh);
   } else {
-    if constexpr (FULL_WARP) u = cat_u_guess_cold<T, M>(M::div_(N, D));
-    else u = cat_u_guess<T, M>(M::div_(N, D));
+    u = cat_u_guess<T, M>(M::div_(N, D));
   }
   T sm, cm, sh, du;
   // The first iteration is straight-line code: with a warm start it is also the last one, and without a
@@ -418,17 +417,30 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, c
     s.C = (tu > c_lo * l && tu < c_hi * l) ? T(0) : M::nan_();
   }
   s.inside = M::abs_(dH) * s.ch <= L * r.sh;
-  if constexpr (FULL_WARP) {
-    if (none) {
-      s.C = M::nan_();
-      s.u = T(0);
-      s.sh = T(0);
-      s.ch = T(1);
-      s.inside = false;
-      s.warm = cat_cold<T>();
-    }
-  }
+  // FULL_WARP: only C is masked.  u, sh, ch of a rootless lane are the stand-in's and are never read behind a
+  // NaN C (cat_z_low, the penalty); its warm record stays the stand-in root -- a consistent (u, sinh, cosh)
+  // triple from which the safeguarded iteration converges like from any other start.
+  if constexpr (FULL_WARP) s.C = none ? M::nan_() : s.C;
   return s;
+}
+
+// Warm-start record at the cold-start guess of a span, without solving: (u, sinh u - u, cosh u - 1, sinh u)
+// consistent at u.  The rollout builds it once per candidate from the initial pose, so every solve inside its
+// loop is the warm, branch-free form.
+template <typename T, typename M>
+__device__ __forceinline__ CatWarm<T> cat_warm_guess(T l, T dH, T L) {
+  const T s2 = (L - dH) * (L + dH);
+  const T sq = M::sqrt_(M::pos_(s2));
+  T N = s2 - l * l;
+  T D = l * (sq + l);
+  if (!(s2 > T(0)) || !(N > T(0)) || !(l > T(0))) {
+    N = T(1);
+    D = T(1);
+  }
+  CatWarm<T> w;
+  w.u = cat_u_guess<T, M>(M::div_(N, D));
+  cat_hyp<T, M>(w.u, w.sm, w.cm, w.sh);
+  return w;
 }
 
 // lowest z of the span (world frame), SURVEY.md 8a "per-step catenary terms"
