@@ -261,6 +261,28 @@ def test_mpc_constraints_active(cb):
         assert bi == int(np.argmin(Jo)), over
 
 
+def test_mpc_sine_arguments_beyond_fast_range(cb):
+    """Commanded speeds of ~1e7 mm/s put the scaled V1x far beyond the |x| < 1e5 range of the rollout's own
+    sine, mixed lane by lane with ordinary candidates: the deferred full-range re-evaluation must reproduce
+    NumPy's sin.  Only the angle term is weighted, so the cost is the integral of theta^2 + gamma^2 and every
+    stage slope matters; gamma_prev != gamma makes gamma (hence x17) move as well."""
+    K, H = 1024, 24
+    rng = np.random.default_rng(77)
+    U = _controls(K, H, 5)
+    far = rng.random(K) < 0.3
+    U[far, :, 0] = rng.uniform(-3e7, 3e7, size=(int(far.sum()), H))
+    U[::97, 3, 0] = 1.0e5 * 108.48977412955092 + 80.85390753943355   # scaled x3 lands at the threshold itself
+    over = dict(w_trk=0.0, w_du=0.0, w_len=0.0, w_sag=0.0, w_ang=1.0, nan_penalty=0.0,
+                gamma_prev=float(np.radians(20.5)))
+    po = orc.default_mpc_params(**over)
+    pref = cb.circle_reference(H, po["dt"])
+    Jo = orc.mpc_rollout_costs(po, U, pref)
+    bi, bc, J = cb.mpc_sample_step(cb.default_mpc_params(**over), U, pref)
+    assert np.isfinite(Jo).all()
+    assert_close(J, Jo, RTOL64, 0, "costs with far sine arguments")
+    assert bi == int(np.argmin(Jo))
+
+
 def test_mpc_other_equations(cb):
     K, H = 1024, 40
     U = _controls(K, H, 3)

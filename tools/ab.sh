@@ -1,0 +1,11 @@
+#!/bin/bash
+# A/B timing of library variants in ab/*.so on one box (box-to-box clocks differ by a few %): alternates the
+# variants so that drift hits all of them alike.  usage: tools/ab.sh [rounds]
+R=${1:-3}
+for r in $(seq $R); do
+  for f in ab/*.so; do
+    echo "== $f"
+    CAT_B200_LIB=$PWD/$f python tools/prof_mpc.py 65536 50 60 | cut -d'(' -f1
+    CAT_B200_LIB=$PWD/$f python tools/prof_mpc.py 65536 50 60 rng | cut -d'(' -f1
+  done
+done
