@@ -286,7 +286,15 @@ def generate(model_json=MODEL_JSON, out_file=OUT_FILE):
         + ", ".join(repr(float(v)) for v in mean) + "}; return T(v[i]); }",
         f"  static __host__ __device__ constexpr T inv_scale(int i) {{ constexpr double v[{nf}] = {{"
         + ", ".join(repr(1.0 / float(v)) for v in scale) + "}; return T(v[i]); }",
+        "  // the same map as one FMA: xs = x * inv_scale + offset, offset = -mean * inv_scale (the rollout kernel)",
+        "  static __host__ __device__ constexpr T offset(int i) { return T(-double(CatScaler<double>::mean(i)) * "
+        "double(CatScaler<double>::inv_scale(i))); }",
         "};",
+        "// (inv_scale, offset) pairs in constant memory: one 128-bit uniform load feeds the FMA of a feature,",
+        "// where two 64-bit literals would cost four UMOVs at every use",
+        f"__constant__ __align__(16) double CAT_SCALER_FMA[{2 * nf}] = {{"
+        + ", ".join(repr(1.0 / float(sc)) + ", " + repr(-float(m) * (1.0 / float(sc))) for m, sc in zip(mean, scale))
+        + "};",
         "",
     ]
     table = []          # (eq_id, name, complexity, live mask)

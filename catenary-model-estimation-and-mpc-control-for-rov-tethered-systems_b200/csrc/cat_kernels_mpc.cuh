@@ -122,10 +122,18 @@ __device__ __forceinline__ void cat_eval_pair_v(const CatMpcDev<T>& q, const Cat
   }
 }
 
+// StandardScaler of one feature as a single FMA (x * inv_scale - mean * inv_scale: within 1 ulp of the scaled
+// magnitude of (x - mean) * inv_scale); fp64 reads the pair from constant memory
+template <typename T>
+__device__ __forceinline__ T cat_scale1(T v, int j) {
+  if constexpr (sizeof(T) == 8) return fma(v, CAT_SCALER_FMA[2 * j], CAT_SCALER_FMA[2 * j + 1]);
+  else return fmaf(v, CatScaler<T>::inv_scale(j), CatScaler<T>::offset(j));
+}
+
 template <typename T>
 __device__ __forceinline__ void cat_scale18(T (&x)[18]) {
 #pragma unroll
-  for (int j = 0; j < 18; ++j) x[j] = (x[j] - CatScaler<T>::mean(j)) * CatScaler<T>::inv_scale(j);
+  for (int j = 0; j < 18; ++j) x[j] = cat_scale1<T>(x[j], j);
 }
 
 // block-wide (cost, idx) argmin; result valid in thread 0
@@ -388,8 +396,9 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     T kt[2], kg[2];
     cat_eval_pair_v<T, GENERIC, 2, VM>(q, vm, xs, kt, kg);
     const T k2t = kt[0], k4t = kt[1], k2g = kg[0], k4g = kg[1];
-    const T thn = th + q.dt6 * (k1t + T(2) * k2t + T(2) * k2t + k4t);
-    const T gan = ga + q.dt6 * (k1g + T(2) * k2g + T(2) * k2g + k4g);
+    // k1 + 2 k2 + 2 k3 + k4 with k3 == k2 (simulate_rk4_theta_gamma.py:65): 4 k2 is exact, one FMA
+    const T thn = M::fma_(q.dt6, M::fma_(T(4), k2t, k1t + k4t), th);
+    const T gan = M::fma_(q.dt6, M::fma_(T(4), k2g, k1g + k4g), ga);
     // ---- catenary terms of the new pose (main_fun.py:423) ----
     const T rx = Pn[0] - P0[0], ry = Pn[1] - P0[1], rz = Pn[2] - P0[2];
     const T l2 = rx * rx + ry * ry;
@@ -426,8 +435,8 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     // ---- stage-1 row and slopes of the next step ----
 #pragma unroll
     for (int j = 0; j < 18; ++j) x0[j] = xs[1][j];
-    x0[14] = (th - CatScaler<T>::mean(14)) * CatScaler<T>::inv_scale(14);
-    x0[15] = (ga - CatScaler<T>::mean(15)) * CatScaler<T>::inv_scale(15);
+    x0[14] = cat_scale1<T>(th, 14);
+    x0[15] = cat_scale1<T>(ga, 15);
     if constexpr (!GENERIC && !VM) {
       // shipped pair: which slopes carry over is known at compile time; only the other one is evaluated (an
       // unused sin still leaves its range check, branch and slow-path call behind -- the compiler cannot
