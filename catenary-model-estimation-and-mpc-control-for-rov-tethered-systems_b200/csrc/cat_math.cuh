@@ -291,6 +291,23 @@ __device__ __forceinline__ T cat_u_guess(T e) {
   return lr + M::log_(lr + M::log_(M::max_(lr, T(1))));
 }
 
+// (sinh u - u, cosh u - 1, sinh u) moved from u to u + d by the addition theorems, for |d| <= 0.03:
+//   cosh d - 1 = z (1/2 + z (1/24 + z/720)),  sinh d - d = d z (1/6 + z (1/120 + z/5040)),  z = d^2
+// (next terms z^4/40320 <= 1.7e-17 and d z^4/362880: below one ulp of the results).  17 flops against the 35
+// plus exponent arithmetic of cat_hyp, no range reduction, and no cancellation: every product is added to a
+// term of its own sign structure (sm absorbs sinh d - d directly).
+template <typename T, typename M>
+__device__ __forceinline__ void cat_hyp_shift(const CatWarm<T>& w, T d, T& sm, T& cm, T& sh) {
+  const T z = d * d;
+  const T cd = z * M::fma_(z, M::fma_(z, T(1.0 / 720.0), T(1.0 / 24.0)), T(0.5));          // cosh d - 1
+  const T sd = d * z * M::fma_(z, M::fma_(z, T(1.0 / 5040.0), T(1.0 / 120.0)), T(1.0 / 6.0));   // sinh d - d
+  const T shd = d + sd;
+  const T ch = w.cm + T(1);
+  sh = M::fma_(w.sh, cd, M::fma_(ch, shd, w.sh));
+  cm = M::fma_(ch, cd, M::fma_(w.sh, shd, w.cm));
+  sm = M::fma_(w.sh, cd, M::fma_(w.cm, shd, w.sm + sd));
+}
+
 // One safeguarded Halley step for the root of  G(u) = D (sinh u - u) - N u,  N = L^2 - dH^2 - l^2,
 // D = l (sqrt(L^2 - dH^2) + l):  the same root as g(u) = (sinh u - u) - e u with e = N / D, without
 // forming the quotient.  G' = D (cosh u - 1) - N, G'' = D sinh u.  The quotient of the step uses the
@@ -319,19 +336,26 @@ __device__ __forceinline__ T cat_halley_step(T u, T N, T D, T sm, T cm, T sh) {
 template <typename T, typename M, bool FULL_WARP = false>
 __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w) {
   T u;
-  if (FULL_WARP || w.u > T(0)) {   // FULL_WARP callers always hand in a record (cat_warm_guess before their loop)
-    u = w.u - cat_halley_step<T, M>(w.u, N, D, w.sm, w.cm, w.sh);
-  } else {
-    u = cat_u_guess<T, M>(M::div_(N, D));
-  }
   T sm, cm, sh, du;
+  bool far = false;
   // The first iteration is straight-line code: with a warm start it is also the last one, and without a
   // data-dependent loop around it the compiler can interleave this chain with the caller's independent work
   // (the RK4 stages of the rollout).  Further iterations (cold starts, fast-moving spans) take the loop.
-  cat_hyp<T, M>(u, sm, cm, sh);
+  if constexpr (FULL_WARP) {   // callers always hand in a record (cat_warm_guess before their loop)
+    // the warm step moves u by d ~ 1e-3 u: the record follows by the addition theorems instead of a fresh
+    // sinh/cosh evaluation; a step beyond their range is sent to the loop, which starts with cat_hyp(u)
+    const T d = -cat_halley_step<T, M>(w.u, N, D, w.sm, w.cm, w.sh);
+    u = w.u + d;
+    cat_hyp_shift<T, M>(w, d, sm, cm, sh);
+    far = !(M::abs_(d) <= T(0.03));
+  } else {
+    if (w.u > T(0)) u = w.u - cat_halley_step<T, M>(w.u, N, D, w.sm, w.cm, w.sh);
+    else u = cat_u_guess<T, M>(M::div_(N, D));
+    cat_hyp<T, M>(u, sm, cm, sh);
+  }
   du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
   u -= du;
-  bool more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1));
+  bool more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1)) || far;
   bool again;
   if constexpr (FULL_WARP) again = __any_sync(0xffffffffu, more);   // every lane of the warp is here
   else again = more;
