@@ -296,11 +296,18 @@ __device__ __forceinline__ T cat_u_guess(T e) {
 // (next terms z^4/40320 <= 1.7e-17 and d z^4/362880: below one ulp of the results).  17 flops against the 35
 // plus exponent arithmetic of cat_hyp, no range reduction, and no cancellation: every product is added to a
 // term of its own sign structure (sm absorbs sinh d - d directly).
+__constant__ __align__(16) double CAT_SHIFT_C[6] = {1.0 / 720.0, 1.0 / 5040.0, 1.0 / 24.0, 1.0 / 120.0, 1.0 / 6.0, 0.0};
+template <typename T> __device__ __forceinline__ T cat_shift_c(int i) {   // fp64: uniform loads, not literals
+  if constexpr (sizeof(T) == 8) return CAT_SHIFT_C[i];
+  else return i == 0 ? T(1.0 / 720.0) : i == 1 ? T(1.0 / 5040.0) : i == 2 ? T(1.0 / 24.0) : i == 3 ? T(1.0 / 120.0)
+                                                                                                 : T(1.0 / 6.0);
+}
+
 template <typename T, typename M>
 __device__ __forceinline__ void cat_hyp_shift(const CatWarm<T>& w, T d, T& sm, T& cm, T& sh) {
   const T z = d * d;
-  const T cd = z * M::fma_(z, M::fma_(z, T(1.0 / 720.0), T(1.0 / 24.0)), T(0.5));          // cosh d - 1
-  const T sd = d * z * M::fma_(z, M::fma_(z, T(1.0 / 5040.0), T(1.0 / 120.0)), T(1.0 / 6.0));   // sinh d - d
+  const T cd = z * M::fma_(z, M::fma_(z, cat_shift_c<T>(0), cat_shift_c<T>(2)), T(0.5));              // cosh d - 1
+  const T sd = d * z * M::fma_(z, M::fma_(z, cat_shift_c<T>(1), cat_shift_c<T>(3)), cat_shift_c<T>(4));   // sinh d - d
   const T shd = d + sd;
   const T ch = w.cm + T(1);
   sh = M::fma_(w.sh, cd, M::fma_(ch, shd, w.sh));
@@ -312,19 +319,26 @@ __device__ __forceinline__ void cat_hyp_shift(const CatWarm<T>& w, T d, T& sm, T
 // D = l (sqrt(L^2 - dH^2) + l):  the same root as g(u) = (sinh u - u) - e u with e = N / D, without
 // forming the quotient.  G' = D (cosh u - 1) - N, G'' = D sinh u.  The quotient of the step uses the
 // fast reciprocal: an error of 1e-15 relative in a step that is itself a correction is invisible.
-template <typename T, typename M>
+template <typename T, typename M, bool NEWTON = false>
 __device__ __forceinline__ T cat_halley_step(T u, T N, T D, T sm, T cm, T sh) {
   const T G = D * sm - N * u;
   const T Gp = D * cm - N;
-  const T den = T(2) * Gp * Gp - G * (D * sh);
-  // Branch-free: the three cases share one reciprocal (selected operands, identical arithmetic per lane), so
-  // the step is straight-line code inside the caller's basic block.
+  // Branch-free: the cases share one reciprocal (selected operands, identical arithmetic per lane), so the
+  // step is straight-line code inside the caller's basic block.
   const bool newton = Gp > T(0);
-  const bool halley = newton && den > T(0);
-  const T num = halley ? T(2) * G * Gp : G;
-  const T dn = halley ? den : Gp;
-  T du = num * M::rcp_fast_(dn);               // Halley, else Newton (junk when !newton, replaced below)
-  if (!newton) du = -(T(0.5) * u + T(0.1));    // left of the minimum of G: move right
+  T du;
+  if constexpr (NEWTON) {
+    // polishing step next to the root (the rollout after its warm Halley step): Newton's quadratic
+    // convergence from ~1e-9 is already below one ulp, at a third of the arithmetic
+    du = G * M::rcp_fast_(Gp);
+  } else {
+    const T den = T(2) * Gp * Gp - G * (D * sh);
+    const bool halley = newton && den > T(0);
+    const T num = halley ? T(2) * G * Gp : G;
+    const T dn = halley ? den : Gp;
+    du = num * M::rcp_fast_(dn);               // Halley, else Newton (junk when !newton, replaced below)
+  }
+  if (!newton) du = M::fma_(T(-0.5), u, T(-0.1));   // left of the minimum of G: move right
   if (!(du < u)) du = T(0.5) * u;              // keep u > 0
   return du;
 }
@@ -333,8 +347,13 @@ __device__ __forceinline__ T cat_halley_step(T u, T N, T D, T sm, T cm, T sh) {
 // sinh/cosh are exact at the old root).  A rollout step moves the span by ~1e-3 relative, so that
 // step lands within ~1e-9 of the root and ONE full iteration finishes; the loop still runs until
 // |du| is below tol.  Returns the root with sinh-u, cosh-1, sinh Taylor-corrected to it.
+template <typename T> struct CatSolve {
+  T u, sh, ch;       // the root, sinh and cosh there
+  CatWarm<T> rec;    // record to hand to the next solve of the same span
+};
+
 template <typename T, typename M, bool FULL_WARP = false>
-__device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w) {
+__device__ __forceinline__ CatSolve<T> cat_solve_u(T N, T D, const CatWarm<T>& w) {
   T u;
   T sm, cm, sh, du;
   bool far = false;
@@ -348,12 +367,13 @@ __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w)
     u = w.u + d;
     cat_hyp_shift<T, M>(w, d, sm, cm, sh);
     far = !(M::abs_(d) <= T(0.03));
+    du = cat_halley_step<T, M, true>(u, N, D, sm, cm, sh);
   } else {
     if (w.u > T(0)) u = w.u - cat_halley_step<T, M>(w.u, N, D, w.sm, w.cm, w.sh);
     else u = cat_u_guess<T, M>(M::div_(N, D));
     cat_hyp<T, M>(u, sm, cm, sh);
+    du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
   }
-  du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
   u -= du;
   bool more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1)) || far;
   bool again;
@@ -369,15 +389,30 @@ __device__ __forceinline__ CatWarm<T> cat_solve_u(T N, T D, const CatWarm<T>& w)
       ++it;
     }
   }
-  // values at the updated u from those at u+du, second order (|du| <= 1e-6 min(u,1): remainder du^3/6 < 2e-19).
+  // (sm, cm, sh) are values at u + du, the point of the last evaluation; |du| <= step_tol * min(u, 1).
   // d/du: sm' = cm, cm' = sh, sh' = ch
   const T ch = cm + T(1);
-  const T h2 = du * du * T(0.5);
-  CatWarm<T> r;
+  CatSolve<T> r;
   r.u = u;
-  r.sm = M::fma_(h2, sh, M::fma_(-cm, du, sm));
-  r.cm = M::fma_(h2, ch, M::fma_(-sh, du, cm));
-  r.sh = M::fma_(h2, sh, M::fma_(-ch, du, sh));
+  if constexpr (FULL_WARP) {
+    // outputs to first order (remainder du^2/2 <= 5e-13 relative); the record stays at the evaluation point,
+    // one polishing step (~1e-9 u) behind the root -- as good a start for the next warm step as the root
+    r.sh = M::fma_(-ch, du, sh);
+    r.ch = M::fma_(-sh, du, ch);
+    r.rec.u = u + du;
+    r.rec.sm = sm;
+    r.rec.cm = cm;
+    r.rec.sh = sh;
+  } else {
+    // second order (remainder du^3/6 < 2e-19): the record is moved to the root
+    const T h2 = du * du * T(0.5);
+    r.rec.u = u;
+    r.rec.sm = M::fma_(h2, sh, M::fma_(-cm, du, sm));
+    r.rec.cm = M::fma_(h2, ch, M::fma_(-sh, du, cm));
+    r.rec.sh = M::fma_(h2, sh, M::fma_(-ch, du, sh));
+    r.sh = r.rec.sh;
+    r.ch = r.rec.cm + T(1);
+  }
   return r;
 }
 
@@ -427,11 +462,11 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, c
   }
   // FULL_WARP (the rollout): no early exit -- a rootless lane solves a harmless stand-in (N = D = 1) and is
   // masked afterwards, so the warp stays converged and the common path is one basic block
-  const CatWarm<T> r = cat_solve_u<T, M, FULL_WARP>(FULL_WARP && none ? T(1) : N, FULL_WARP && none ? T(1) : D, warm);
+  const CatSolve<T> r = cat_solve_u<T, M, FULL_WARP>(FULL_WARP && none ? T(1) : N, FULL_WARP && none ? T(1) : D, warm);
   s.u = r.u;
   s.sh = r.sh;
-  s.ch = r.cm + T(1);
-  s.warm = r;
+  s.ch = r.ch;
+  s.warm = r.rec;
   if constexpr (NEED_C) {
     const T C = M::div_(T(2) * r.u, l);
     s.C = (C > c_lo && C < c_hi) ? C : M::nan_();
