@@ -44,6 +44,7 @@ template <typename T> struct CatMpcDev {
   int eq_theta, eq_gamma;
   int carry_t, carry_g;   // equation reads neither column 14 nor 15: k1 of the next step == k4 of this one
   T dt, dt_mm, dt6, L, w_trk, w_du, w_len, w_sag, w_ang, rhoL, rhoL2, z_thr, c_lo, c_hi, pen, clip;
+  T L2;   // L^2 (sag-term bound)
   T sigma[3];
   unsigned long long seed;
   // receding-horizon controller mode (cat_kernels_ctrl.cuh); all null / H in a plain step
@@ -406,15 +407,25 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     const T d2 = l2 + rz * rz;
     const CatSpan<T> sp = cat_span<T, M, false, true>(l, rz, q.L, q.c_lo, q.c_hi, warm);
     warm = sp.warm;
-    const T z_low = cat_z_low<T, M>(sp, l, q.L, P0[2], P0[2] + rz);
     // ---- cost, association as in the oracle ----
     const T ex = Pn[0] - Rh[0], ey = Pn[1] - Rh[1], ez = Pn[2] - Rh[2];
     const T dvx = Vn[0] - V[0], dvy = Vn[1] - V[1], dvz = Vn[2] - V[2];
-    // max(0, d - rho L): the square root is only taken when the term is active (or d is NaN) in some lane
-    // of the warp -- a warp-uniform branch, so the inactive case issues nothing
-    T over = T(0);
-    if (__any_sync(0xffffffffu, !(d2 <= q.rhoL2))) over = M::pos_(M::sqrt_(d2) - q.rhoL);
-    const T deep = M::pos_(q.z_thr - z_low);
+    // The two penalty terms are evaluated only when one of them can be active (or an input is NaN) in some lane
+    // of the warp -- a warp-uniform branch, so the inactive case issues nothing:
+    //  * max(0, d - rho L) is zero iff d^2 <= (rho L)^2: no square root;
+    //  * max(0, z_thr - z_low) is zero when a bound on the lowest point clears the threshold.  The cable from A
+    //    over its lowest point Q to B is no shorter than the broken line A-Q-B, so (mirror B at Q's level)
+    //    L^2 >= l^2 + (|dH| + 2t)^2 for Q at depth t below the lower end: z_low >= zmin - (sqrt(L^2-l^2) - |dH|)/2.
+    //    With g = zmin - z_thr >= 0 the term vanishes once (2g + |dH|)^2 >= L^2 - l^2; no lowest point then.
+    const T zmin = rz < T(0) ? P0[2] + rz : P0[2];
+    const T g = zmin - q.z_thr;
+    const T g2 = M::fma_(T(2), g, M::abs_(rz));
+    const bool quiet = d2 <= q.rhoL2 && g >= T(0) && g2 * g2 >= q.L2 - l2;
+    T over = T(0), deep = T(0);
+    if (__any_sync(0xffffffffu, !quiet)) {
+      over = M::pos_(M::sqrt_(d2) - q.rhoL);
+      deep = M::pos_(q.z_thr - cat_z_low<T, M>(sp, l, q.L, P0[2], P0[2] + rz));
+    }
     T c = q.w_trk * (ex * ex + ey * ey + ez * ez);
     c = c + q.w_du * (dvx * dvx + dvy * dvy + dvz * dvz);
     c = c + q.w_len * (over * over);

@@ -316,6 +316,7 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.w_ang = T(p->w_ang);
   q.rhoL = T(p->rho * p->L);
   q.rhoL2 = q.rhoL > T(0) ? q.rhoL * q.rhoL : T(-1);   // a non-positive threshold is always 'active'
+  q.L2 = q.L * q.L;
   q.carry_t = (CAT_EQ_TABLE[q.eq_theta].live_mask & 0xC000u) == 0;
   q.carry_g = (CAT_EQ_TABLE[q.eq_gamma].live_mask & 0xC000u) == 0;
   q.z_thr = T(p->z_floor + p->margin);
