@@ -30,6 +30,12 @@ K_PER_GPU = 65536
 H = 50
 FLOPS_PER_ROLLOUT_STEP = 972.0        # DFMA-equivalent fp64 flops, SURVEY.md 8(d)
 BYTES_PER_ROLLOUT_STEP = 24.0         # 3 fp64 controls read per rollout-step (explicit controls)
+# Instructions the fp64 kernel actually executes per warp and horizon step on its common path (SASS of
+# k_mpc_rollout<double,false,false,false>, counted with tools/sass_hist.py): 400 in all, 211 of
+# them on the FP64 pipe.  An FP64 instruction holds the issue port for two cycles and nothing issues beside it
+# (tools/ubench/fp64_latency.cu), so a warp-step costs 400 + 211 issue slots.
+EXEC_INSTR_PER_WARP_STEP = 400.0
+EXEC_FP64_PER_WARP_STEP = 211.0
 METRIC = "rk4_tether_rollout_steps_per_sec"
 UNIT = "rollout-steps/s"
 
@@ -137,6 +143,20 @@ def run_reference(args):
                       "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
                       "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                       "gpu_launches": 0}))
+
+
+def _executed(K, H, k_ms, dfma_per_s, clocks):
+    """What the dominant kernel executes, next to the algorithmic convention of `roofline`: FP64-pipe share
+    (thread-level FP64 instructions per second over the measured DFMA rate) and issue-slot share (slots per
+    second over sub-partitions x SM clock sampled under load).  Explains where the time goes; not a claim."""
+    warp_steps = (K / 32.0) * H / (k_ms * 1e-3)
+    sm_mhz = (clocks or {}).get("sm_mhz") or 0
+    slots = warp_steps * (EXEC_INSTR_PER_WARP_STEP + EXEC_FP64_PER_WARP_STEP)
+    out = {"instr_per_warp_step": EXEC_INSTR_PER_WARP_STEP, "fp64_instr_per_warp_step": EXEC_FP64_PER_WARP_STEP,
+           "fp64_pipe_frac": warp_steps * 32.0 * EXEC_FP64_PER_WARP_STEP / dfma_per_s,
+           "issue_slot_frac": slots / (148 * 4 * sm_mhz * 1e6) if sm_mhz else None,
+           "source": "SASS common path (tools/sass_hist.py), FP64 = 2 issue slots (tools/ubench/fp64_latency.cu)"}
+    return out
 
 
 def _f64_winner(step, controls):
@@ -374,6 +394,7 @@ def run_ours(args):
                 "frac": ach_tf / peak_tf, "traffic": traffic, "kernel": "k_mpc_rollout<double,false>",
                 "kernel_ms": k_ms, "peak_source": "cat_measure_peak(DFMA) measured in this run x 2 flops",
                 "flops_per_rollout_step": FLOPS_PER_ROLLOUT_STEP,
+                "executed": _executed(K, H, k_ms, dfma, clocks),
                 "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
     # ---- fp32 fast mode (north_star: 1e-4 relative): same workload, float controls, FFMA + MUFU roofline ----
