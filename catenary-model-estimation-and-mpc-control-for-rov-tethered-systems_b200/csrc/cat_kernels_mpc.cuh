@@ -81,7 +81,7 @@ __device__ __forceinline__ void cat_nominal_control(const CatMpcDev<T>& q, unsig
   for (int a = 0; a < 3; ++a) {
     const T z = kglob == 0 ? T(0) : out[a];
     const T v = T(un[a]) + z;
-    out[a] = M::min_(M::max_(v, -q.u_max[a]), q.u_max[a]);
+    out[a] = M::clamp_sym_(v, q.u_max[a]);
   }
 }
 

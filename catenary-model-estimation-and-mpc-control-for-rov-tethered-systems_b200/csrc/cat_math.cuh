@@ -113,6 +113,15 @@ __device__ __forceinline__ double cat_sqrt_f64(double x) {
   return special ? fix : g;
 }
 
+// |x| > c ? copysign(c, x) : x  (c > 0; NaN stays NaN like np.clip): one compare and integer selects instead of
+// the two NaN-quieting min/max sequences
+__device__ __forceinline__ double cat_clamp_sym_f64(double x, double c) {
+  const bool big = fabs(x) > c;
+  const int hx = __double2hiint(x);
+  return __hiloint2double(big ? (__double2hiint(c) | (hx & (int)0x80000000)) : hx,
+                          big ? __double2loint(c) : __double2loint(x));
+}
+
 // For u >= 0: sh = sinh u, cm = cosh u - 1, sm = sinh u - u, all without cancellation at small u and
 // without a division: u = k ln2 + r, |r| <= ln2/2;  sinh/cosh(k ln2) are exact combinations of
 // 2^k, 2^-k;  addition theorems.  For k = 0 this IS the series (A = 0, B = 1).
@@ -179,6 +188,7 @@ template <> struct CatMath<double> {
     e = fma(-x, y, 1.0);
     return fma(y, e, y);
   }
+  static __device__ __forceinline__ double clamp_sym_(double x, double c) { return cat_clamp_sym_f64(x, c); }
   static __device__ __forceinline__ double min_(double a, double b) { return fmin(a, b); }
   static __device__ __forceinline__ double max_(double a, double b) { return fmax(a, b); }
   static __device__ __forceinline__ double fma_(double a, double b, double c) { return fma(a, b, c); }
@@ -231,6 +241,7 @@ template <> struct CatMath<float> {
   static __device__ __forceinline__ float rcp_fast_(float x) { return rcp_(x); }
   static __device__ __forceinline__ float min_(float a, float b) { return fminf(a, b); }
   static __device__ __forceinline__ float max_(float a, float b) { return fmaxf(a, b); }
+  static __device__ __forceinline__ float clamp_sym_(float x, float c) { return fminf(fmaxf(x, -c), c); }
   static __device__ __forceinline__ float fma_(float a, float b, float c) { return fmaf(a, b, c); }
   template <int N> static __device__ __forceinline__ float ipow(float x) {
     float r = x;
@@ -619,6 +630,37 @@ __device__ __forceinline__ void cat_philox4x32_10(uint32_t c0, uint32_t c1, uint
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+// sin and cos of the Box-Muller angle 2 pi (r + 0.5) / 2^32 straight from the counter word r: the nearest quarter
+// turn comes off the top bits, so the argument reduction is exact integer arithmetic, and both functions share
+// one argument on [-pi/4, pi/4] with 6-coefficient interpolants (Chebyshev nodes, mpmath: |error| <= 1.4e-17 and
+// 9e-19).  16 flops + 2 for the argument, against ~35 + range logic for sincospi.
+__constant__ __align__(16) double CAT_SC_C[12] = {   // (sin, cos) coefficient pairs, highest degree first
+    1.5918129293821173e-10, -1.1382632424867702e-11,
+    -2.5051131844989112e-08, 2.087614626839412e-09,
+    2.755731610255237e-06, -2.755731727172975e-07,
+    -0.00019841269836758574, 2.480158729876569e-05,
+    0.008333333333330948, -0.0013888888888887398,
+    -0.16666666666666666, 0.041666666666666664};
+__device__ __forceinline__ void cat_sincos2pi_u32(uint32_t r, double& s, double& c) {
+  const uint32_t k = (r + 0x20000000u) >> 30;             // nearest quarter turn, 0..4
+  const int rem = (int)(r - (k << 30));                    // [-2^29, 2^29)
+  const double x = ((double)rem + 0.5) * 1.4629180792671596e-09;   // 2 pi / 2^32; |x| <= pi/4
+  const double z = x * x;
+  double ps = CAT_SC_C[0], pc = CAT_SC_C[1];
+#pragma unroll
+  for (int i = 1; i < 6; ++i) {
+    ps = fma(ps, z, CAT_SC_C[2 * i]);
+    pc = fma(pc, z, CAT_SC_C[2 * i + 1]);
+  }
+  const double sx = fma(x * z, ps, x);                     // sin x = x + x z S(z)
+  const double cx = fma(z * z, pc, fma(-0.5, z, 1.0));     // cos x = 1 - z/2 + z^2 C(z)
+  // angle = k pi/2 + x:  k&3 = 0: (sx, cx)  1: (cx, -sx)  2: (-sx, -cx)  3: (-cx, sx)
+  const bool swap = (k & 1u) != 0;
+  const double s0 = swap ? cx : sx, c0 = swap ? sx : cx;
+  s = __hiloint2double(__double2hiint(s0) ^ (int)((k & 2u) << 30), __double2loint(s0));
+  c = __hiloint2double(__double2hiint(c0) ^ (int)(((k + 1u) & 2u) << 30), __double2loint(c0));
+}
+
 // three clipped normals scaled by sigma, keyed by (seed, problem, global k, h)
 template <typename T, typename M>
 __device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t problem, uint64_t k, uint32_t h,
@@ -626,15 +668,21 @@ __device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t probl
   uint32_t r[4];
   cat_philox4x32_10((uint32_t)k, (uint32_t)(k >> 32), h, problem, (uint32_t)seed, (uint32_t)(seed >> 32), r);
   const T s = T(2.3283064365386963e-10);   // 2^-32
-  const T u0 = (T(r[0]) + T(0.5)) * s, u1 = (T(r[1]) + T(0.5)) * s;
-  const T u2 = (T(r[2]) + T(0.5)) * s, u3 = (T(r[3]) + T(0.5)) * s;
+  const T u0 = (T(r[0]) + T(0.5)) * s, u2 = (T(r[2]) + T(0.5)) * s;
   const T ra = M::sqrt_(T(-2) * M::log_(u0)), rb = M::sqrt_(T(-2) * M::log_(u2));
-  T sa, ca;
-  M::sincos2pi_(u1, &sa, &ca);
-  const T cb = M::cos2pi_(u3);
-  const T z0 = M::min_(M::max_(ra * ca, -clip), clip);
-  const T z1 = M::min_(M::max_(ra * sa, -clip), clip);
-  const T z2 = M::min_(M::max_(rb * cb, -clip), clip);
+  T sa, ca, cb;
+  if constexpr (sizeof(T) == 8) {
+    double sb;
+    cat_sincos2pi_u32(r[1], sa, ca);
+    cat_sincos2pi_u32(r[3], sb, cb);
+  } else {
+    const T u1 = (T(r[1]) + T(0.5)) * s, u3 = (T(r[3]) + T(0.5)) * s;
+    M::sincos2pi_(u1, &sa, &ca);
+    cb = M::cos2pi_(u3);
+  }
+  const T z0 = M::clamp_sym_(ra * ca, clip);
+  const T z1 = M::clamp_sym_(ra * sa, clip);
+  const T z2 = M::clamp_sym_(rb * cb, clip);
   out[0] = z0 * sigma[0];
   out[1] = z1 * sigma[1];
   out[2] = z2 * sigma[2];
