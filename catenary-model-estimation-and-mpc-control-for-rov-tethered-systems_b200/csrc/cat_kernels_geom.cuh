@@ -130,14 +130,20 @@ __device__ __forceinline__ void cat_shape_map_set(CatShapeMap<T>& m, const T a[3
   }
 }
 
-template <typename T>
+// W = the output mask as a compile-time constant (0: taken from which_rt at run time).  With W fixed the record
+// layout, the per-map tests of the point loop and the map loads are resolved at compile time: the maps of a
+// configuration sit in registers across its points (profiles/r1_ncu_full_k_shape_f64_v3c.csv: the run-time form
+// spends 55 instructions per 32-point hop, of which ~20 are mask tests, offset arithmetic and repeated LDS).
+template <typename T, int W>
 __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long long n, const T* __restrict__ A,
                                                           const T* __restrict__ B, const T* __restrict__ L,
                                                           long long L_stride, const T* __restrict__ theta,
-                                                          const T* __restrict__ gamma, int n_pts, int which,
+                                                          const T* __restrict__ gamma, int n_pts, int which_rt,
                                                           T c_lo, T c_hi, T* __restrict__ out,
                                                           T* __restrict__ C_out, unsigned char* __restrict__ valid) {
   typedef CatMath<T> M;
+  const int which = W ? W : which_rt;
+  constexpr bool HOIST = W != 0 && ((W & 1) + ((W >> 1) & 1) + ((W >> 2) & 1) + ((W >> 3) & 1)) <= 2;
   extern __shared__ __align__(16) unsigned char cat_shape_smem[];
   CatPair<T>* const rec = reinterpret_cast<CatPair<T>*>(cat_shape_smem);
   const int rec_len = cat_shape_record_len(which);
@@ -275,6 +281,17 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
       const CatPair<T> s0 = rs[0], s1 = rs[1], s2 = rs[2];
       const T two_u = s0.x, v_low = s0.y, inv_C = s1.x, cm_low = s1.y, cmD = s2.x, shD = s2.y;
       const bool ok = rs[3].x != T(0);
+      CatPair<T> mq[4][3];     // maps of this span's outputs, held in registers when the mask is a constant
+      if constexpr (HOIST) {
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          if ((m == 0) != (spi == 0) || !(outs & (1 << m))) continue;
+          const CatPair<T>* mp = r + m_rec[m];
+          mq[m][0] = mp[0];
+          mq[m][1] = mp[1];
+          mq[m][2] = mp[2];
+        }
+      }
       T cm = T(0), sh = T(0);
       T ptf = lane_f;          // T(pt), stepped exactly
       T* o = o_lane;           // &out[cfg][pt][0] of the first requested block, stepped by G points
@@ -301,7 +318,16 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
         for (int m = 0; m < 4; ++m) {
           if ((m == 0) != (spi == 0) || !(outs & (1 << m))) continue;
           const CatPair<T>* mp = r + m_rec[m];   // (a0,a1) (a2,b0) (b1,b2)
-          const CatPair<T> p0 = mp[0], p1 = mp[1], p2 = mp[2];
+          CatPair<T> p0, p1, p2;
+          if constexpr (HOIST) {
+            p0 = mq[m][0];
+            p1 = mq[m][1];
+            p2 = mq[m][2];
+          } else {
+            p0 = mp[0];
+            p1 = mp[1];
+            p2 = mp[2];
+          }
           T* om = o + m_out[m];
           om[0] = M::fma_(zoff, p1.y, M::fma_(s, p0.x, A0));
           om[1] = M::fma_(zoff, p2.x, M::fma_(s, p0.y, A1));

@@ -148,8 +148,20 @@ int shape_dev_on(CatCtx* c, cudaStream_t st, int64_t n, const T* A, const T* B, 
                  const T* theta, const T* gamma, int32_t n_pts, int32_t which, T* out, T* C_out, uint8_t* valid) {
   if (n == 0) return CAT_OK;
   const size_t smem = (size_t)CAT_SHAPE_TILE * cat_shape_record_len(which) * 2 * sizeof(T);
-  k_shape<T><<<nblk(n, CAT_SHAPE_TILE), CAT_SHAPE_TILE, smem, st>>>(n, A, B, L, L_stride, theta, gamma, n_pts, which,
-                                                                 T(kCLo), T(kCHi), out, C_out, valid);
+#define CAT_SHAPE_LAUNCH(W)                                                                                          \
+  k_shape<T, W><<<nblk(n, CAT_SHAPE_TILE), CAT_SHAPE_TILE, smem, st>>>(n, A, B, L, L_stride, theta, gamma, n_pts,       \
+                                                                      which, T(kCLo), T(kCHi), out, C_out, valid)
+  // Single-curve masks are compiled in for fp64 (A/B on one B200, 1,048,576 x 100 points: final curve 0.525 ->
+  // 0.448 ms, original curve 0.437 -> 0.423 ms).  The same specialisation is slower for all four curves (1.86 ->
+  // 2.21 ms: the unrolled per-map code spills at the 96-register cap) and in fp32 (0.267 -> 0.278 ms, two
+  // configurations per warp), so those take the run-time form.
+  const int w = sizeof(T) == 8 ? which : 0;
+  switch (w) {
+    case CAT_OUT_ORIGINAL: CAT_SHAPE_LAUNCH(1); break;     // Catenary.__call__ alone (catenary.py:25)
+    case CAT_OUT_FINAL: CAT_SHAPE_LAUNCH(8); break;        // fully augmented curve (main_fun.py:111, [3])
+    default: CAT_SHAPE_LAUNCH(0); break;
+  }
+#undef CAT_SHAPE_LAUNCH
   LAUNCHED();
   return CAT_OK;
 }

@@ -87,3 +87,20 @@ class MpcDeviceStep:
         """(best_idx (n,), best_cost (n,)) on the host (one small D2H + sync)."""
         w = self.winner.cpu().numpy()
         return w[self.n:].copy(), w[:self.n].view(np.float64).copy()
+
+
+def sample_controls(params, K, H, sigma, *, seed=0, clip=3.0, k_offset=0, problem_offset=0, n_problems=1, device=0,
+                    ctx=None, to_host=True):
+    """The candidate controls the rollout kernel draws on the device, materialised (cat_sample_controls_dev_f64):
+    sigma * clip(N(0,1), +-clip) from Philox4x32-10 keyed by (seed, problem, global k, h), mm/s.  Returns
+    (n_problems, H, 3, K) float64 -- the kernel's SoA layout -- as a NumPy array, or as the device tensor with
+    ``to_host=False``.  The definition is oracle.sample_controls."""
+    import torch
+    dev = torch.device("cuda", device)
+    ctx = ctx or Context(device)
+    prm = make_params(params, K, H, n_problems=n_problems, k_offset=k_offset, problem_offset=problem_offset,
+                      flags=_lib.MPC_RNG_CONTROLS, seed=seed, sigma=sigma, clip=clip)
+    out = torch.empty((int(n_problems), int(H), 3, int(K)), dtype=torch.float64, device=dev)
+    ctx.set_stream(torch.cuda.current_stream(dev).cuda_stream)
+    ctx.check(ctx.lib.cat_sample_controls_dev_f64(ctx.handle, C.byref(prm), out.data_ptr()))
+    return out.cpu().numpy() if to_host else out

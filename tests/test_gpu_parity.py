@@ -334,6 +334,21 @@ def test_mpc_device_rng_matches_oracle_philox(cb):
     assert gi == bi and gc == bc
 
 
+def test_device_sampler_values_match_oracle(cb):
+    """The sampled controls themselves (not only the costs they lead to): Philox words, the integer-keyed
+    -2 ln u and sin/cos 2 pi u of the fp64 sampler against NumPy's log/sin/cos, incl. high candidate indices
+    (k >= 2^32) and a non-zero problem id.  1e-13 relative: the transcendental parts are good to ~3e-16."""
+    import importlib
+    dev = importlib.import_module(cb.__name__ + ".device")
+    p = cb.default_mpc_params()
+    for K, H, seed, k0, prob in ((8192, 50, 1234, 0, 0), (4096, 100, 2 ** 40 + 7, 2 ** 33 + 5, 9)):
+        U = dev.sample_controls(p, K, H, SIGMA, seed=seed, k_offset=k0, problem_offset=prob)
+        assert U.shape == (1, H, 3, K)
+        Uo = orc.sample_controls(seed, k0 + np.arange(K, dtype=np.uint64), H, SIGMA, problem=prob)   # (K,H,3)
+        assert_close(U[0].transpose(2, 0, 1), Uo, 1e-13, 1e-11, f"sampled controls seed {seed}")   # atol: 2 pi u is rounded in the oracle
+        assert np.all(np.abs(U[0]) <= 3.0 * np.asarray(SIGMA)[None, :, None] * (1 + 1e-15))
+
+
 def test_mpc_fleet(cb):
     """Config 5 semantics at reduced size: independent problems, segmented argmin, no cross-talk."""
     n, K, H = 6, 1500, 20
