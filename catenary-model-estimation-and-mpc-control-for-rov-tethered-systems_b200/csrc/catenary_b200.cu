@@ -23,6 +23,9 @@ namespace {
 
 enum { SLOT_A = 0, SLOT_B, SLOT_C, SLOT_D, SLOT_E, SLOT_F, SLOT_G, SLOT_H, SLOT_BEST, SLOT_TICKET, N_SLOTS };
 
+struct CatCtx;
+int fail(CatCtx* c, int code, const char* what, cudaError_t e = cudaSuccess);
+
 struct CatCtx {
   int device;
   cudaStream_t own_stream;
@@ -36,9 +39,30 @@ struct CatCtx {
   size_t cap[N_SLOTS];
   int sm_count;
   int mpc_block;   // 0 = heuristic; else forced block size (CAT_MPC_BLOCK_SIZE env, tuning only)
+  // device-mapped pinned staging of the host MPC step: [0, kStageWin) winners written by the kernel's last block
+  // (no D2H copy), [kStageWin, kStageBytes) problems + reference rows going up in ONE async copy
+  unsigned char* h_stage;
+  unsigned char* d_stage;   // device alias of h_stage
 };
+constexpr size_t kStageWin = 4096, kStageBytes = 65536;
 
-int fail(CatCtx* c, int code, const char* what, cudaError_t e = cudaSuccess) {
+int stage(CatCtx* c) {
+  if (c->h_stage) return CAT_OK;
+  void* h = nullptr;
+  cudaError_t e = cudaHostAlloc(&h, kStageBytes, cudaHostAllocMapped | cudaHostAllocPortable);
+  if (e != cudaSuccess) return fail(c, CAT_ENOMEM, "cudaHostAlloc", e);
+  void* d = nullptr;
+  e = cudaHostGetDevicePointer(&d, h, 0);
+  if (e != cudaSuccess) {
+    cudaFreeHost(h);
+    return fail(c, CAT_ECUDA, "cudaHostGetDevicePointer", e);
+  }
+  c->h_stage = (unsigned char*)h;
+  c->d_stage = (unsigned char*)d;
+  return CAT_OK;
+}
+
+int fail(CatCtx* c, int code, const char* what, cudaError_t e) {
   if (c) {
     c->err = what;
     if (e != cudaSuccess) {
@@ -467,14 +491,33 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   double* d_bc;
   long long* d_bi;
   T* d_costs = nullptr;
-  SCRATCH(SLOT_A, np * sizeof(CatMpcProblem), d_prob);
+  // Few problems (the sampling-MPC step proper): problems and reference rows go up in ONE copy from pinned staging,
+  // and the kernel's last block writes the winners into device-mapped pinned memory, so the call makes no D2H
+  // copy and no pageable transfer (each of which costs a driver round trip of ~10 us on a 0.1 ms step).
+  const size_t b_prob = (np * sizeof(CatMpcProblem) + 15) & ~(size_t)15;
+  const size_t b_ref = np * (size_t)p->H * 3 * sizeof(double);
+  const bool staged = np * 16 <= kStageWin && b_prob + b_ref <= kStageBytes - kStageWin;
   if (!rng) SCRATCH(SLOT_B, n_ctl * sizeof(T), d_ctl);
-  SCRATCH(SLOT_C, np * (size_t)p->H * 3 * sizeof(double), d_ref);
-  SCRATCH(SLOT_D, np * 16, d_bc);
-  d_bi = (long long*)(d_bc + np);
   if (costs) SCRATCH(SLOT_E, np * (size_t)p->K * sizeof(T), d_costs);
-  CU(cudaMemcpyAsync(d_prob, problems, np * sizeof(CatMpcProblem), cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(d_ref, p_ref, np * (size_t)p->H * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if (staged) {
+    rc = stage(c);
+    if (rc) return rc;
+    unsigned char* d_up;
+    SCRATCH(SLOT_A, b_prob + b_ref, d_up);
+    std::memcpy(c->h_stage + kStageWin, problems, np * sizeof(CatMpcProblem));
+    std::memcpy(c->h_stage + kStageWin + b_prob, p_ref, b_ref);
+    CU(cudaMemcpyAsync(d_up, c->h_stage + kStageWin, b_prob + b_ref, cudaMemcpyHostToDevice, c->stream));
+    d_prob = (CatMpcProblem*)d_up;
+    d_ref = (double*)(d_up + b_prob);
+    d_bc = (double*)c->d_stage;
+  } else {
+    SCRATCH(SLOT_A, np * sizeof(CatMpcProblem), d_prob);
+    SCRATCH(SLOT_C, b_ref, d_ref);
+    SCRATCH(SLOT_D, np * 16, d_bc);
+    CU(cudaMemcpyAsync(d_prob, problems, np * sizeof(CatMpcProblem), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_ref, p_ref, b_ref, cudaMemcpyHostToDevice, c->stream));
+  }
+  d_bi = (long long*)(d_bc + np);
   if (!rng && np == 1 && p->K >= 32768) {
     // One problem, explicit controls (config 3: 78.6 MB): the step is PCIe-bound, so the candidates go up in 8
     // chunks on the aux stream and chunk i's rollout overlaps chunk i+1's copy; the chunk winners fold on the
@@ -529,11 +572,17 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     }
     if (rc) return rc;
   }
-  CU(cudaMemcpyAsync(best_cost, d_bc, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaMemcpyAsync(best_idx, d_bi, np * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+  if (!staged) {
+    CU(cudaMemcpyAsync(best_cost, d_bc, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(best_idx, d_bi, np * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+  }
   if (costs)
     CU(cudaMemcpyAsync(costs, d_costs, np * (size_t)p->K * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
+  if (staged) {   // the winners are already in host memory (written through the mapping before the kernel ended)
+    std::memcpy(best_cost, c->h_stage, np * sizeof(double));
+    std::memcpy(best_idx, c->h_stage + np * sizeof(double), np * sizeof(long long));
+  }
   return CAT_OK;
 }
 
@@ -942,6 +991,7 @@ int cat_init(int device, void** ctx) {
   c->device = device;
   c->launches = 0;
   c->mpc_block = 0;
+  c->h_stage = c->d_stage = nullptr;
   if (const char* e = std::getenv("CAT_MPC_BLOCK_SIZE")) {
     const int v = std::atoi(e);
     if (v == 32 || v == 64 || v == 128) c->mpc_block = v;
@@ -972,6 +1022,7 @@ int cat_destroy(void* ctx) {
   cudaStreamSynchronize(c->aux_stream);
   for (int s = 0; s < N_SLOTS; ++s)
     if (c->slot[s]) cudaFree(c->slot[s]);
+  if (c->h_stage) cudaFreeHost(c->h_stage);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
   cudaEventDestroy(c->ev_aux);
