@@ -58,12 +58,14 @@ def make_params(params, K, H, *, n_problems=1, k_offset=0, problem_offset=0, fla
 
 def make_problems(params, n_problems=1):
     """Structured array (PROBLEM_DTYPE) from a params dict; per-problem values may be given as (n,3)/(n,)."""
-    pr = np.zeros(n_problems, _lib.PROBLEM_DTYPE)
-    for k in ("P0", "P1", "V1", "A1"):
-        pr[k] = np.broadcast_to(np.asarray(params[k], np.float64), (n_problems, 3))
-    for k in ("theta", "gamma", "theta_prev", "gamma_prev"):
-        pr[k] = np.broadcast_to(np.asarray(params[k], np.float64), (n_problems,))
-    return pr
+    # the record is 16 packed doubles (P0 P1 V1 A1 theta gamma theta_prev gamma_prev): filled through a (n,16) view,
+    # a third of the cost of per-field structured assignment (this runs on every host MPC step)
+    flat = np.empty((n_problems, 16))
+    for j, k in enumerate(("P0", "P1", "V1", "A1")):
+        flat[:, 3 * j:3 * j + 3] = params[k]
+    for j, k in enumerate(("theta", "gamma", "theta_prev", "gamma_prev")):
+        flat[:, 12 + j] = params[k]
+    return flat.view(_lib.PROBLEM_DTYPE).reshape(n_problems)
 
 
 def _programs(params):
