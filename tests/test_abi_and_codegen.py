@@ -38,6 +38,24 @@ def test_struct_layouts_match_header(cb):
     assert L.CatMpcParams.dt.offset == 40 and L.CatMpcParams.seed.offset == 144
 
 
+def test_problem_records_are_the_c_struct(cb):
+    """make_problems fills CatMpcProblem through a flat (n,16) view: byte-identical to per-field assignment, scalar
+    and per-problem values broadcast alike."""
+    lib = importlib.import_module(cb.__name__ + "._lib")
+    rng = np.random.default_rng(3)
+    p = cb.default_mpc_params()
+    for n, prm in ((1, p), (5, dict(p, P1=rng.normal(size=(5, 3)), V1=rng.normal(size=(5, 3)), theta=rng.normal(size=5),
+                                    gamma_prev=rng.normal(size=5)))):
+        got = cb.make_problems(prm, n)
+        want = np.zeros(n, lib.PROBLEM_DTYPE)
+        for k in ("P0", "P1", "V1", "A1"):
+            want[k] = np.broadcast_to(np.asarray(prm[k], np.float64), (n, 3))
+        for k in ("theta", "gamma", "theta_prev", "gamma_prev"):
+            want[k] = np.broadcast_to(np.asarray(prm[k], np.float64), (n,))
+        assert got.dtype == lib.PROBLEM_DTYPE and got.shape == (n,) and got.flags["C_CONTIGUOUS"]
+        assert got.tobytes() == want.tobytes()
+
+
 def test_no_cpu_fallback_without_device(cb):
     import torch
     if torch.cuda.is_available():
