@@ -13,7 +13,9 @@ LIB_PATH = os.environ.get("CAT_B200_LIB") or os.path.join(_HERE, "libcatenary_b2
 
 CAT_OK, CAT_EINVAL, CAT_ECUDA, CAT_ENOMEM, CAT_ENODEV = 0, -1, -2, -3, -4
 OUT_ORIGINAL, OUT_THETA_ROTATED, OUT_THETA_ALIGNED, OUT_FINAL = 1, 2, 4, 8
-MPC_RNG_CONTROLS, MPC_CONTROLS_AOS = 1, 2
+MPC_RNG_CONTROLS, MPC_CONTROLS_AOS, MPC_CONTROLS_F32 = 1, 2, 4
+P2P_LOCKSTEP, P2P_PIPELINED = 0, 1
+ABI_VERSION = 3
 CTRL_ARGMIN, CTRL_MPPI = 0, 1
 CTRL_LOG_W = 16
 
@@ -59,6 +61,12 @@ SIGNATURES = {
     "cat_set_stream": (_int, [_vp, _vp, _int]),
     "cat_host_alloc": (_int, [_vp, C.c_size_t, C.POINTER(_vp)]),
     "cat_host_free": (_int, [_vp, _vp]),
+    "cat_host_register": (_int, [_vp, _vp, C.c_size_t]),
+    "cat_host_unregister": (_int, [_vp, _vp]),
+    "cat_mpc_workspace_create": (_int, [_vp, _i64, _i32, C.POINTER(_vp)]),
+    "cat_mpc_workspace_destroy": (_int, [_vp, _vp]),
+    "cat_set_workspace": (_int, [_vp, _vp]),
+    "cat_mpc_stats": (_int, [_vp, _int, _int, _vp]),
     "cat_timer_start": (_int, [_vp]),
     "cat_timer_stop_ms": (_int, [_vp, C.POINTER(C.c_float)]),
     "cat_solve_param_f64": (_int, [_vp, _i64, _vp, _vp, _vp, _i64, _vp]),
@@ -100,6 +108,10 @@ SIGNATURES = {
     "cat_p2p_connect": (_int, [_vp, _vp]),
     "cat_mpc_step_p2p_dev_f64": (_int, [_vp, _vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cat_mpc_step_p2p_dev_f32": (_int, [_vp, _vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cat_mpc_step_p2p_f64": (_int, [_vp, _vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cat_mpc_step_p2p_f32": (_int, [_vp, _vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cat_p2p_set_mode": (_int, [_vp, _int]),
+    "cat_p2p_flush_dev": (_int, [_vp, _vp, _vp, _vp]),
     "cat_p2p_status": (_int, [_vp, C.POINTER(_int)]),
     "cat_p2p_destroy": (_int, [_vp]),
     "cat_ctrl_create_f64": (_int, [_vp, _PP, _PC, _vp, _vp, _vp, _i64, C.POINTER(_vp)]),
@@ -132,6 +144,9 @@ def load():
                 fn = getattr(lib, name)      # AttributeError if the symbol is not exported
                 fn.restype = res
                 fn.argtypes = args
+            if lib.cat_abi_version() != ABI_VERSION:
+                raise CatenaryLibraryError(f"{LIB_PATH}: ABI {lib.cat_abi_version()}, this package needs {ABI_VERSION} "
+                                           "-- rebuild with __graft_entry__.build()")
             _lib = lib
     return _lib
 

@@ -2,8 +2,10 @@
 
     python build.py [--force] [--verbose]
 
-1. codegen.py: artifacts/model.json -> csrc/gen/dyn_eqs.cuh (PySR equations + scaler constants)
-2. nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -> libcatenary_b200.so
+1. codegen.py: artifacts/model.json -> csrc/gen/dyn_eqs.cuh (PySR equations + scaler constants),
+   artifacts/icdf_table.json -> csrc/gen/icdf_table.cuh (sampler table)
+2. nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -c, one process per translation unit, in parallel
+   -> csrc/build/*.o -> nvcc -shared -> libcatenary_b200.so
 """
 from __future__ import annotations
 
@@ -14,10 +16,19 @@ import sys
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
+OBJ = os.path.join(CSRC, "build")
 LIB = os.path.join(_HERE, "libcatenary_b200.so")
-SOURCES = ["catenary_b200.cu"]
-HEADERS = ["cat_math.cuh", "cat_kernels_geom.cuh", "cat_kernels_dyn.cuh", "cat_kernels_mpc.cuh", "cat_kernels_ctrl.cuh", "cat_kernels_expr.cuh",
-           os.path.join("gen", "dyn_eqs.cuh"), os.path.join("..", "..", "include", "catenary_b200.h")]
+# translation units: (object name, source, extra defines).  k_mpc_rollout is instantiated in its own units, one per
+# (compute type, equation source), so the heavy part of the build runs in parallel (2 min 11 s serial on 8 cores).
+UNITS = [("catenary_b200.o", "catenary_b200.cu", [])] + [
+    (f"mpc_inst_{t}_{k}.o", "mpc_inst.cu", [f"-DCAT_INST_T={t}", f"-DCAT_INST_KIND={k}"])
+    for t in ("double", "float") for k in (0, 1, 2)]
+HEADERS = ["cat_host.cuh", "cat_math.cuh", "cat_kernels_geom.cuh", "cat_kernels_dyn.cuh", "cat_kernels_mpc.cuh",
+           "cat_mpc_launch.cuh", "cat_kernels_ctrl.cuh", "cat_kernels_expr.cuh", "cat_kernels_feat.cuh",
+           os.path.join("gen", "dyn_eqs.cuh"), os.path.join("gen", "icdf_table.cuh"),
+           os.path.join("..", "..", "include", "catenary_b200.h")]
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
+         "-Xcompiler", "-fvisibility=hidden", "-DCAT_BUILD_SHARED"]
 
 
 def _nvcc():
@@ -27,12 +38,19 @@ def _nvcc():
     raise RuntimeError("nvcc not found (set NVCC=...)")
 
 
-def _stale():
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS] + [os.path.abspath(__file__)]
-    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+def _newest_dep(src):
+    deps = [os.path.join(CSRC, f) for f in [src] + HEADERS] + [os.path.abspath(__file__)]
+    return max(os.path.getmtime(d) for d in deps if os.path.exists(d))
+
+
+def _compile(unit, force, verbose):
+    obj, src, defs = unit
+    out = os.path.join(OBJ, obj)
+    if not force and os.path.exists(out) and os.path.getmtime(out) >= _newest_dep(src):
+        return obj, 0, ""
+    cmd = [_nvcc()] + FLAGS + defs + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", out]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    return obj, res.returncode, res.stdout + res.stderr
 
 
 def build(force=False, verbose=False):
@@ -42,19 +60,21 @@ def build(force=False, verbose=False):
     finally:
         sys.path.pop(0)
     codegen.generate()
-    if not force and not _stale():
-        return LIB
-    cmd = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-           "-shared", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-cudart", "static",
-           "-DCAT_BUILD_SHARED", "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
-    if verbose:
-        cmd.insert(1, "-Xptxas")
-        cmd.insert(2, "-v")
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if verbose or res.returncode != 0:
-        sys.stderr.write(res.stdout + res.stderr)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stderr[-4000:])
+    os.makedirs(OBJ, exist_ok=True)
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=min(len(UNITS), os.cpu_count() or 2)) as pool:
+        results = list(pool.map(lambda u: _compile(u, force, verbose), UNITS))
+    for obj, rc, log in results:
+        if verbose or rc != 0:
+            sys.stderr.write(f"--- {obj}\n{log}")
+        if rc != 0:
+            raise RuntimeError(f"nvcc failed on {obj}:\n" + log[-4000:])
+    objs = [os.path.join(OBJ, u[0]) for u in UNITS]
+    if force or not os.path.exists(LIB) or any(os.path.getmtime(o) > os.path.getmtime(LIB) for o in objs):
+        cmd = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static", "-o", LIB] + objs
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("link failed:\n" + (res.stdout + res.stderr)[-4000:])
     return LIB
 
 

@@ -19,6 +19,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 MODEL_JSON = os.path.join(_HERE, "artifacts", "model.json")
 OUT_DIR = os.path.join(_HERE, "csrc", "gen")
 OUT_FILE = os.path.join(OUT_DIR, "dyn_eqs.cuh")
+ICDF_JSON = os.path.join(_HERE, "artifacts", "icdf_table.json")
+ICDF_FILE = os.path.join(OUT_DIR, "icdf_table.cuh")
 
 _TOKEN = re.compile(r"\s*(?:(\d+\.?\d*(?:[eE][+-]?\d+)?|\.\d+(?:[eE][+-]?\d+)?)|([A-Za-z_]\w*)|(\*\*|[-+*/()]))")
 _FUNCS = {"sin": "sin", "cos": "cos", "tanh": "tanh", "exp": "exp", "log": "log",
@@ -373,12 +375,38 @@ def generate(model_json=MODEL_JSON, out_file=OUT_FILE):
         lines.append(f"  {{{i}, {1 if name == 'dgamma_dt' else 0}, {cx}, {mask}u}},")
     lines += ["};", ""]
     os.makedirs(os.path.dirname(out_file), exist_ok=True)
-    text = "\n".join(lines)
-    old = open(out_file).read() if os.path.exists(out_file) else None
+    generate_icdf()
+    return _write_if_changed(out_file, "\n".join(lines))
+
+
+def _write_if_changed(path, text):
+    old = open(path).read() if os.path.exists(path) else None
     if old != text:
-        with open(out_file, "w") as fh:
+        with open(path, "w") as fh:
             fh.write(text)
-    return out_file
+    return path
+
+
+def generate_icdf(table_json=ICDF_JSON, out_file=ICDF_FILE):
+    """artifacts/icdf_table.json (tools/make_icdf_table.py) -> csrc/gen/icdf_table.cuh: the piecewise-cubic inverse
+    normal CDF of the on-device control sampler, as one __device__ array of (c0, c1, c2, c3) rows."""
+    with open(table_json) as fh:
+        t = json.load(fh)
+    coef = t["coef"]
+    assert t["degree"] == 3 and t["sub_bits"] == 5 and len(coef) == (t["e_hi"] - t["e_lo"] + 1) << 5
+    lines = ["// GENERATED by codegen.py from artifacts/icdf_table.json (tools/make_icdf_table.py) -- do not edit.",
+             "// y(r') = -ndtri((r' + 0.5) / 2^32) on a floating-point-like grid: octave e = floor(log2 r'), 32 segments",
+             "// per octave, cubic in the remaining bits.  max |error| " + repr(t["max_abs_err"]) + ".",
+             "#pragma once",
+             f"#define CAT_ICDF_E_LO {t['e_lo']}",
+             f"#define CAT_ICDF_E_HI {t['e_hi']}",
+             f"#define CAT_ICDF_SEGMENTS {len(coef)}",
+             f"__device__ __align__(16) const double CAT_ICDF_TAB[{4 * len(coef)}] = {{"]
+    for row in coef:
+        lines.append("    " + ", ".join(repr(float(v)) for v in row) + ",")
+    lines += ["};", ""]
+    os.makedirs(os.path.dirname(out_file), exist_ok=True)
+    return _write_if_changed(out_file, "\n".join(lines))
 
 
 def equation_table(model_json=MODEL_JSON):

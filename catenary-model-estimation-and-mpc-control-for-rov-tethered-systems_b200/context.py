@@ -3,6 +3,7 @@ from __future__ import annotations
 
 import ctypes as C
 import threading
+import weakref
 
 import numpy as np
 
@@ -22,6 +23,8 @@ class Context:
         self.handle = h
         self.device = int(device)
         self._pinned = []
+        self._registered = {}     # address -> (nbytes, weakref.finalize) of page-locked caller arrays
+        self._unlockable = set()  # addresses cat_host_register refused (already page-locked, ...): do not retry
 
     # -- plumbing --------------------------------------------------------------------------
     def check(self, rc):
@@ -71,6 +74,57 @@ class Context:
         buf = (C.c_char * max(n, 1)).from_address(p.value)
         return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
+    # -- caller arrays ---------------------------------------------------------------------
+    REGISTER_MIN_BYTES = 4 << 20
+
+    def register(self, array):
+        """Page-lock a caller-owned, C-contiguous ndarray in place (cat_host_register) so the host entry points copy
+        it at PCIe speed; the registration ends when the array is garbage-collected (or at ``close``).  Returns True
+        if the array is (now) registered.  Arrays that do not own their memory are registered through their base."""
+        base = array
+        while isinstance(getattr(base, "base", None), np.ndarray):
+            base = base.base
+        if not isinstance(base, np.ndarray) or not base.flags["C_CONTIGUOUS"] or base.nbytes == 0:
+            return False
+        addr, nbytes = base.ctypes.data, base.nbytes
+        have = self._registered.get(addr)
+        if have is not None and have[0] >= nbytes:
+            return True
+        if have is not None:
+            have[1]()                                    # grown in place: re-register
+        if addr in self._unlockable:
+            return False
+        rc = self.lib.cat_host_register(self.handle, C.c_void_p(addr), nbytes)
+        if rc != _lib.CAT_OK:                            # pinned_empty memory, 64 ranges in use, unlockable pages
+            self._unlockable.add(addr)
+            return False
+        lib, handle, table = self.lib, self.handle, self._registered
+
+        def _release(addr=addr):
+            if table.pop(addr, None) is not None and handle.value:
+                lib.cat_host_unregister(handle, C.c_void_p(addr))
+        try:
+            fin = weakref.finalize(base, _release)
+        except TypeError:                                # not weak-referenceable: do not keep a dangling lock
+            lib.cat_host_unregister(handle, C.c_void_p(addr))
+            return False
+        self._registered[addr] = (nbytes, fin)
+        return True
+
+    def maybe_register(self, array):
+        """``register`` for arrays large enough to be worth the ~0.1 ms/MB page-locking cost, seen for the first
+        time; a no-op for small or already page-locked ones."""
+        if array is None or array.nbytes < self.REGISTER_MIN_BYTES:
+            return False
+        return self.register(array)
+
+    def stats(self, enable=True, reset=True):
+        """Cold-path counters of the rollout kernel (cat_mpc_stats): dict(solve_cold, sine_cold) warp-level entries
+        since the last reset; switches counting on/off for the launches that follow."""
+        out = (C.c_uint64 * 4)()
+        self.check(self.lib.cat_mpc_stats(self.handle, 1 if enable else 0, 1 if reset else 0, out))
+        return {"solve_cold": int(out[0]), "sine_cold": int(out[1])}
+
     def measure_peak(self, kind):
         """kind: 'dfma' | 'ffma' | 'mufu' -> operations per second (FMA = 1 op)."""
         v = C.c_double()
@@ -79,6 +133,8 @@ class Context:
 
     def close(self):
         if getattr(self, "handle", None):
+            for _, fin in list(self._registered.values()):
+                fin()
             for p in self._pinned:
                 self.lib.cat_host_free(self.handle, C.c_void_p(p))
             self._pinned = []

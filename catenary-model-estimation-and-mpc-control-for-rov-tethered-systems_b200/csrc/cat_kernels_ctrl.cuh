@@ -51,6 +51,8 @@ __global__ void __launch_bounds__(256) k_ctrl_mppi(const CatMpcDev<T> q, const C
                                                    const long long* __restrict__ best_idx,
                                                    double* __restrict__ partial) {
   typedef CatMath<T> M;
+  __shared__ CatIcdfSmem<T> s_icdf;
+  cat_icdf_stage<T>(s_icdf);
   const int h = blockIdx.x, prob = blockIdx.y, z = blockIdx.z;
   const unsigned long long seed_eff = q.seed + (unsigned long long)(*q.step);
   const double jmin = best_cost[prob];
@@ -58,7 +60,7 @@ __global__ void __launch_bounds__(256) k_ctrl_mppi(const CatMpcDev<T> q, const C
   if (!(jmin == jmin)) {   // NaN winner: fall back to the best candidate itself (weight 1 in slice 0)
     if (threadIdx.x == 0) {
       T u[3] = {T(0), T(0), T(0)};
-      if (z == 0) cat_nominal_control<T, M>(q, seed_eff, prob, best_idx[prob], h, u);
+      if (z == 0) cat_nominal_control<T, M>(q, seed_eff, prob, best_idx[prob], h, s_icdf, u);
       out[0] = (double)u[0];
       out[1] = (double)u[1];
       out[2] = (double)u[2];
@@ -77,7 +79,7 @@ __global__ void __launch_bounds__(256) k_ctrl_mppi(const CatMpcDev<T> q, const C
     double w = exp((j - jmin) * inv_l);
     if (!(j == j)) w = 0.0;
     T u[3];
-    cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + k, h, u);
+    cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + k, h, s_icdf, u);
     acc[0] += w * (double)u[0];
     acc[1] += w * (double)u[1];
     acc[2] += w * (double)u[2];
@@ -174,6 +176,8 @@ __global__ void __launch_bounds__(64) k_ctrl_advance(const CatMpcDev<T> q, const
                                                      unsigned int* __restrict__ ticket) {
   typedef CatMath<T> M;
   extern __shared__ double s_u[];   // [H][3]
+  __shared__ CatIcdfSmem<T> s_icdf;
+  if (x.mode != CAT_CTRL_MPPI) cat_icdf_stage<T>(s_icdf);   // block-uniform
   const int prob = blockIdx.x;
   const int t = *step;
   const unsigned long long seed_eff = q.seed + (unsigned long long)t;
@@ -193,7 +197,7 @@ __global__ void __launch_bounds__(64) k_ctrl_advance(const CatMpcDev<T> q, const
       s_u[3 * h + 2] = a2 / aw;
     } else {
       T u[3];
-      cat_nominal_control<T, M>(q, seed_eff, prob, bi, h, u);
+      cat_nominal_control<T, M>(q, seed_eff, prob, bi, h, s_icdf, u);
       s_u[3 * h + 0] = (double)u[0];
       s_u[3 * h + 1] = (double)u[1];
       s_u[3 * h + 2] = (double)u[2];

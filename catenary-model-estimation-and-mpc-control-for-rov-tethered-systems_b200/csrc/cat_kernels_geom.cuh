@@ -14,7 +14,7 @@ __global__ void __launch_bounds__(256) k_solve_param(long long n, const T* __res
   typedef CatMath<T> M;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const CatSpan<T> s = cat_span<T, M>(l[i], dH[i], L[i * L_stride], c_lo, c_hi, cat_cold<T>());
+  const CatSpan<T> s = cat_span_ldh<T, M>(l[i], dH[i], L[i * L_stride], c_lo, c_hi);   // fp32: N formed in fp64
   C_out[i] = s.C;
 }
 
@@ -83,12 +83,25 @@ __device__ __forceinline__ void cat_shape_store_span(CatPair<T>* r, const CatSha
   r[3] = CatPair<T>{T(sp.valid), T(0)};
 }
 
+// rel_exact (fp32 only, may be null): B - A formed in fp64 from the fp32 end points, so that N = L^2 - dH^2 - l^2
+// carries one rounding instead of the eps L^2 / N of the fp32 subtractions (cat_span_prep_exact)
 template <typename T, typename M>
-__device__ __forceinline__ void cat_shape_span_setup(const T rel[3], T L, T c_lo, T c_hi, T hop, CatShapeSpan<T>& sp,
-                                                     T* C_out) {
+__device__ __forceinline__ void cat_shape_span_setup(const T rel[3], const double* rel_exact, T L, T c_lo, T c_hi,
+                                                     T hop, CatShapeSpan<T>& sp, T* C_out) {
   const T l = M::sqrt_(rel[0] * rel[0] + rel[1] * rel[1]);
   const T dH = rel[2];
-  const CatSpan<T> s = cat_span<T, M>(l, dH, L, c_lo, c_hi, cat_cold<T>());
+  CatSpan<T> s;
+  if constexpr (sizeof(T) == 4) {
+    if (rel_exact) {
+      const double l2 = rel_exact[0] * rel_exact[0] + rel_exact[1] * rel_exact[1];
+      s = cat_span_from<T, M>(cat_span_prep_exact<M>(l, l2, rel_exact[2], (double)L), l, dH, L, c_lo, c_hi,
+                              cat_cold<T>());
+    } else {
+      s = cat_span<T, M>(l, dH, L, c_lo, c_hi, cat_cold<T>());
+    }
+  } else {
+    s = cat_span<T, M>(l, dH, L, c_lo, c_hi, cat_cold<T>());
+  }
   sp.valid = (s.C == s.C) ? 1 : 0;
   if (C_out) *C_out = s.C;
   if (sp.valid) {
@@ -171,7 +184,8 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
     const T ez[3] = {T(0), T(0), T(1)};
     const T zero3[3] = {T(0), T(0), T(0)};
     T Cv;
-    cat_shape_span_setup<T, M>(conn, Li, c_lo, c_hi, hop, c.sp[0], &Cv);
+    const double conn_d[3] = {(double)b[0] - (double)a[0], (double)b[1] - (double)a[1], (double)b[2] - (double)a[2]};
+    cat_shape_span_setup<T, M>(conn, sizeof(T) == 4 ? conn_d : nullptr, Li, c_lo, c_hi, hop, c.sp[0], &Cv);
     if (C_out) C_out[i] = Cv;
     int vbits = c.sp[0].valid;
     if (c.sp[0].valid) {
@@ -193,7 +207,7 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
       cat_rodrigues<T, M>(conn, kt, ct, st, rb);
       const T bq[3] = {a[0] + rb[0], a[1] + rb[1], a[2] + rb[2]};
       const T rel1[3] = {bq[0] - a[0], bq[1] - a[1], bq[2] - a[2]};
-      cat_shape_span_setup<T, M>(rel1, Li, c_lo, c_hi, hop, c.sp[1], (T*)nullptr);
+      cat_shape_span_setup<T, M>(rel1, nullptr, Li, c_lo, c_hi, hop, c.sp[1], (T*)nullptr);
       vbits |= c.sp[1].valid << 1;
       // axes as rodrigues_rotation normalises them (main_fun.py:30)
       const T nt = M::sqrt_(kt[0] * kt[0] + kt[1] * kt[1] + kt[2] * kt[2]);

@@ -20,20 +20,30 @@
 #define CAT_MPC_BLOCK 128   // maximum; the host launches 64 when the batch is under ~1 wave (better SM balance)
 
 // Fused winner exchange over NVLink peer memory: every rank owns a slot buffer
-// [2 parities][n_ranks] x {cost bits, global idx, seq, pad} that its peers map through CUDA IPC.  The last
-// block of the rollout writes this rank's winner into slot [seq & 1][rank] of EVERY rank's buffer (payload,
-// system fence, then the sequence number), waits until its own buffer holds all n_ranks winners of this step and
-// folds them in rank order -- the job-wide (cost, idx) is in best_cost/best_idx when the kernel ends, with no
-// NCCL call and no second launch.  Two parities suffice: a rank cannot start step s+2 before every peer has
-// written step s+1, which a peer does only after it has finished reading step s.
+// [CAT_P2P_RING steps][n_ranks] x {cost bits, global idx, seq, pad} that its peers map through CUDA IPC.  The last
+// block of the rollout POSTS this rank's winner of step s into slot [s % RING][rank] of EVERY rank's buffer
+// (payload, system fence, then the sequence number) and then folds, in rank order, the G winners of
+//   * step s itself (CAT_P2P_LOCKSTEP): it waits until its own buffer holds all of them, so the job-wide
+//     (cost, idx) is in best_cost/best_idx when the kernel ends -- one kernel, no NCCL call, no second launch; the
+//     latency path.  Every kernel then ends when the slowest rank's winner has arrived.
+//   * step s - 1 (CAT_P2P_PIPELINED): those winners were posted one whole rollout ago, so nothing spins and
+//     back-to-back steps of G independent processes no longer pay each other's launch jitter; the job-wide winner
+//     of step s is delivered by step s + 1 (or by k_p2p_fold after the last step) -- the throughput path.
+// Ring of 4: a rank finishes step s+1 only after it has seen every peer's post of s (pipelined) or s+1
+// (lock-step), and a peer posts s only after its own fold of s-2 ended with its step-(s-1) kernel -- so nobody can
+// be more than two posts ahead of a reader, and slot s % 4 is never rewritten (by s + 4) while s is still unread.
 struct CatP2PDev {
   long long* const* peers;   // device array [n_ranks]: slot buffer of each rank (own included); null = off
   int rank, n_ranks;
   unsigned int seq;          // step number, >= 1, identical on every rank
+  int mode;                  // CAT_P2P_LOCKSTEP / CAT_P2P_PIPELINED
   int* err;                  // set to 1 if a peer's winner did not arrive in time
 };
 #define CAT_P2P_SLOT_W 4     // long longs per slot
+#define CAT_P2P_RING 4
 #define CAT_P2P_MAX_RANKS 64
+#define CAT_P2P_LOCKSTEP 0
+#define CAT_P2P_PIPELINED 1
 
 // Kernel-side parameters in the compute type.  Derived constants are formed on the host in
 // double exactly as the oracle forms them (dt/1000, dt/6, rho*L, z_floor+margin).
@@ -69,13 +79,21 @@ template <typename T> struct CatMpcVm {
   int n_t, n_g;
 };
 
+// shared-memory slot of the sampler table: the real thing in the sampling kernels, one byte elsewhere
+template <typename T, bool RNG> struct CatIcdfSlot { typedef CatIcdfSmem<T> type; };
+template <typename T> struct CatIcdfSlot<T, false> { typedef char type; };
+template <typename T, bool RNG>
+__device__ __forceinline__ const CatIcdfSmem<T>& cat_icdf_ref(const typename CatIcdfSlot<T, RNG>::type& s) {
+  return *reinterpret_cast<const CatIcdfSmem<T>*>(&s);   // never dereferenced when RNG is false
+}
+
 // candidate control of the receding-horizon controller: clamp(u_nom[h] + sigma*clip(N(0,1)), +-u_max);
 // global candidate 0 carries no noise (oracle ctrl_candidates)
 template <typename T, typename M>
 __device__ __forceinline__ void cat_nominal_control(const CatMpcDev<T>& q, unsigned long long seed_eff, int prob,
-                                                    long long kglob, int h, T out[3]) {
+                                                    long long kglob, int h, const CatIcdfSmem<T>& icdf, T out[3]) {
   cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)kglob, (uint32_t)h, q.sigma,
-                           q.clip, out);
+                           q.clip, icdf, out);
   const double* un = q.u_nom + ((long long)prob * q.H + h) * 3;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
@@ -137,7 +155,8 @@ __device__ __forceinline__ void cat_scale18(T (&x)[18]) {
   for (int j = 0; j < 18; ++j) x[j] = cat_scale1<T>(x[j], j);
 }
 
-// block-wide (cost, idx) argmin; result valid in thread 0
+// block-wide (cost, idx) argmin in the MPC winner order (cat_better_mpc: NaN ranks with +inf); result valid in
+// thread 0
 __device__ __forceinline__ CatBest cat_block_argmin(double cost, long long idx) {
   __shared__ double s_cost[CAT_MPC_BLOCK / 32];
   __shared__ long long s_idx[CAT_MPC_BLOCK / 32];
@@ -145,7 +164,7 @@ __device__ __forceinline__ CatBest cat_block_argmin(double cost, long long idx) 
   for (int off = 16; off > 0; off >>= 1) {
     const double oc = __shfl_xor_sync(0xffffffffu, cost, off);
     const long long oi = __shfl_xor_sync(0xffffffffu, idx, off);
-    if (cat_better(oc, oi, cost, idx)) {
+    if (cat_better_mpc(oc, oi, cost, idx)) {
       cost = oc;
       idx = oi;
     }
@@ -164,7 +183,7 @@ __device__ __forceinline__ CatBest cat_block_argmin(double cost, long long idx) 
     for (int off = 16; off > 0; off >>= 1) {
       const double oc = __shfl_xor_sync(0xffffffffu, cost, off);
       const long long oi = __shfl_xor_sync(0xffffffffu, idx, off);
-      if (cat_better(oc, oi, cost, idx)) {
+      if (cat_better_mpc(oc, oi, cost, idx)) {
         cost = oc;
         idx = oi;
       }
@@ -174,6 +193,71 @@ __device__ __forceinline__ CatBest cat_block_argmin(double cost, long long idx) 
   b.cost = cost;
   b.idx = idx;
   return b;
+}
+
+// Post this rank's winner of step p2p.seq to every rank, then fold the G winners of the step the mode names
+// (see CatP2PDev).  Called by every thread of ONE block (>= 64 threads).  A peer that does not show up within
+// ~2-4 s raises *p2p.err and the result is the sentinel (NaN, -1), never a fold over stale slots: every consumer
+// sees the failure in the value itself.
+__device__ __forceinline__ long long* cat_p2p_slot(long long* base, unsigned int seq, int n_ranks, int r) {
+  return base + ((long long)(seq % CAT_P2P_RING) * n_ranks + r) * CAT_P2P_SLOT_W;
+}
+
+__device__ __forceinline__ void cat_p2p_fold(const CatP2PDev& p2p, unsigned int want, double* __restrict__ best_cost,
+                                             long long* __restrict__ best_idx) {
+  __shared__ long long s_x[2 * CAT_P2P_MAX_RANKS];
+  __shared__ int s_bad;
+  const int t = threadIdx.x;
+  if (t == 0) s_bad = 0;
+  __syncthreads();
+  if (t < p2p.n_ranks && want >= 1u) {
+    volatile long long* src = cat_p2p_slot(p2p.peers[p2p.rank], want, p2p.n_ranks, t);
+    int spins = 0;
+    while (src[2] != (long long)want) {
+      __nanosleep(64);
+      if (++spins > (1 << 25)) {       // ~2-4 s: a peer is missing
+        *p2p.err = 1;
+        s_bad = 1;
+        break;
+      }
+    }
+    __threadfence_system();
+    s_x[2 * t] = src[0];
+    s_x[2 * t + 1] = src[1];
+  }
+  __syncthreads();
+  if (t == 0) {
+    if (want < 1u || s_bad) {          // no such step (first pipelined launch) or a missing peer
+      *best_cost = __longlong_as_double(0x7ff8000000000000LL);
+      *best_idx = -1;
+    } else {
+      double fc = __longlong_as_double(s_x[0]);
+      long long fi = s_x[1];
+      for (int g = 1; g < p2p.n_ranks; ++g) {
+        const double c = __longlong_as_double(s_x[2 * g]);
+        const long long i = s_x[2 * g + 1];
+        if (cat_better_mpc(c, i, fc, fi)) {
+          fc = c;
+          fi = i;
+        }
+      }
+      *best_cost = fc;
+      *best_idx = fi;
+    }
+  }
+}
+
+__device__ __forceinline__ void cat_p2p_finish(long long my_c, long long my_i, const CatP2PDev& p2p,
+                                               double* __restrict__ best_cost, long long* __restrict__ best_idx) {
+  const int t = threadIdx.x;
+  if (t < p2p.n_ranks) {
+    volatile long long* dst = cat_p2p_slot(p2p.peers[t], p2p.seq, p2p.n_ranks, p2p.rank);
+    dst[0] = my_c;
+    dst[1] = my_i;
+    __threadfence_system();            // payload visible system-wide before the sequence number
+    dst[2] = (long long)p2p.seq;
+  }
+  cat_p2p_fold(p2p, p2p.mode == CAT_P2P_PIPELINED ? p2p.seq - 1u : p2p.seq, best_cost, best_idx);
 }
 
 // grid-wide argmin of one problem: block fold -> one slot per block -> the last block (atomic ticket)
@@ -198,7 +282,7 @@ __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int pro
   for (unsigned int s = threadIdx.x; s < gridDim.x; s += blockDim.x) {
     const double oc = slots[s].cost;
     const long long oi = slots[s].idx;
-    if (cat_better(oc, oi, bc, bi)) {
+    if (cat_better_mpc(oc, oi, bc, bi)) {
       bc = oc;
       bi = oi;
     }
@@ -214,60 +298,29 @@ __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int pro
     return;
   }
   // ---- fused exchange of the rank winners through peer memory (one problem per launch) ----
-  __shared__ long long s_x[2 * CAT_P2P_MAX_RANKS];
+  __shared__ long long s_mine[2];
   if (threadIdx.x == 0) {
-    s_x[0] = __double_as_longlong(r.cost);
-    s_x[1] = r.idx;
+    s_mine[0] = __double_as_longlong(r.cost);
+    s_mine[1] = r.idx;
     tickets[prob] = 0u;
   }
   __syncthreads();
-  const long long my_c = s_x[0], my_i = s_x[1];
-  __syncthreads();
-  const int par = (int)(p2p.seq & 1u);
-  const int t = threadIdx.x;
-  if (t < p2p.n_ranks) {
-    volatile long long* dst = p2p.peers[t] + (long long)(par * p2p.n_ranks + p2p.rank) * CAT_P2P_SLOT_W;
-    dst[0] = my_c;
-    dst[1] = my_i;
-    __threadfence_system();            // payload visible system-wide before the sequence number
-    dst[2] = (long long)p2p.seq;
-    volatile long long* src = p2p.peers[p2p.rank] + (long long)(par * p2p.n_ranks + t) * CAT_P2P_SLOT_W;
-    int spins = 0;
-    while (src[2] != (long long)p2p.seq) {
-      __nanosleep(64);
-      if (++spins > (1 << 25)) {       // ~2-4 s: a peer is missing; report, fall back to what is there
-        *p2p.err = 1;
-        break;
-      }
-    }
-    __threadfence_system();
-    s_x[2 * t] = src[0];
-    s_x[2 * t + 1] = src[1];
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double fc = __longlong_as_double(s_x[0]);
-    long long fi = s_x[1];
-    for (int g = 1; g < p2p.n_ranks; ++g) {
-      const double c = __longlong_as_double(s_x[2 * g]);
-      const long long i = s_x[2 * g + 1];
-      if (cat_better(c, i, fc, fi)) {
-        fc = c;
-        fi = i;
-      }
-    }
-    best_cost[prob] = fc;
-    best_idx[prob] = fi;
-  }
+  cat_p2p_finish(s_mine[0], s_mine[1], p2p, best_cost + prob, best_idx + prob);
 }
 
-template <typename T, bool GENERIC, bool VM = false, bool RNG = false>
+// T = compute type, S = storage type of the explicit controls (S = float with T = double: the candidates cross
+// PCIe and HBM at 12 B per rollout-step instead of 24 and are widened on load -- the oracle is fed the same
+// rounded values, so parity is untouched).  RNG = true draws the controls on the device instead (S unused).
+template <typename T, typename S, bool GENERIC, bool VM = false, bool RNG = false>
 __global__ void __launch_bounds__(CAT_MPC_BLOCK, 4)   // <= 128 registers: config 3 needs 3.5 blocks per SM resident
-k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, const T* __restrict__ controls,
+k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, const S* __restrict__ controls,
               const double* __restrict__ p_ref, T* __restrict__ costs, CatBest* __restrict__ block_best,
               unsigned int* __restrict__ tickets, double* __restrict__ best_cost,
               long long* __restrict__ best_idx) {
   typedef CatMath<T> M;
+  // inverse-CDF table of the device sampler (hot octaves), staged once per block
+  __shared__ typename CatIcdfSlot<T, RNG>::type s_icdf;
+  if constexpr (RNG) cat_icdf_stage<T>(s_icdf);
   CatMpcVm<T> vm;
   if constexpr (VM) {   // stage both programs into shared memory once per block
     extern __shared__ __align__(16) unsigned char cat_mpc_smem[];
@@ -306,10 +359,10 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     warm = cat_warm_guess<T, M>(M::sqrt_(wx * wx + wy * wy), P[2] - P0[2], q.L);
   }
 
-  // control source fixed at compile time: the explicit-controls kernel carries no Philox / Box-Muller code
-  // (a third of the loop's SASS) and the sampling kernel no control loads
+  // control source fixed at compile time: the explicit-controls kernel carries no Philox / sampler code and the
+  // sampling kernel no control loads
   constexpr bool rng = RNG;
-  const T* uc = rng ? nullptr : controls + (long long)prob * q.sp + kk * q.sk;
+  const S* uc = rng ? nullptr : controls + (long long)prob * q.sp + kk * q.sk;
   // controller mode: the step counter lives in HBM so that one captured graph serves every control step
   int t0 = 0;
   if (q.step) t0 = min(*q.step, q.ref_len - 1);
@@ -335,15 +388,23 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     carry_g = (CAT_DGAMMA_LIVE_MASK & 0xC000u) == 0;
   }
 
-  // controls and the reference point of a step are fetched one step ahead, so the load latency hides
-  // behind the arithmetic of the current step (round-1 profile: 25% of the stall samples sat on the first
-  // use of the control loads)
-  T Vnext[3] = {T(0), T(0), T(0)};
+  // Controls are fetched PF steps ahead and the reference point one step ahead, so the load latency hides behind
+  // arithmetic.  One step of fp64 arithmetic (~3,000 cycles at 3.5 warps per scheduler) covers an HBM miss; one
+  // step of the fp32 kernel (~1,900 cycles, with the loads issued ~40% into the step) did NOT (~1,000 cycles of
+  // DRAM latency at the natural clock): round-1 ncu showed 3.2 long-scoreboard stall cycles per issued
+  // instruction there.  The fp32 kernel therefore keeps a ring of three steps in registers.
+  constexpr int PF = (!RNG && sizeof(T) == 4) ? 3 : 1;
+  S Vq[PF][3];
   T Rnext[3];
-  if (!rng) {
-    Vnext[0] = uc[0];
-    Vnext[1] = uc[q.sa];
-    Vnext[2] = uc[2 * q.sa];
+  if constexpr (!RNG) {
+#pragma unroll
+    for (int i = 0; i < PF; ++i) {
+      const S* u = uc + (long long)(i < q.H ? i : q.H - 1) * q.sh;
+      Vq[i][0] = u[0];
+      Vq[i][1] = u[q.sa];
+      Vq[i][2] = u[2 * q.sa];
+    }
+    uc += (long long)PF * q.sh;   // the row of step h + PF at the top of step h; dereferenced only below H
   }
   Rnext[0] = T(pr[0]);
   Rnext[1] = T(pr[1]);
@@ -351,16 +412,22 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
 
   for (int h = 0; h < q.H; ++h) {
     T Vn[3];
-    if (rng) {
+    if constexpr (RNG) {
       if (q.u_nom)
-        cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + kk, h, Vn);
+        cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + kk, h, cat_icdf_ref<T, RNG>(s_icdf), Vn);
       else
         cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
-                                 (uint32_t)h, q.sigma, q.clip, Vn);
+                                 (uint32_t)h, q.sigma, q.clip, cat_icdf_ref<T, RNG>(s_icdf), Vn);
     } else {
-      Vn[0] = Vnext[0];
-      Vn[1] = Vnext[1];
-      Vn[2] = Vnext[2];
+      Vn[0] = T(Vq[0][0]);
+      Vn[1] = T(Vq[0][1]);
+      Vn[2] = T(Vq[0][2]);
+#pragma unroll
+      for (int i = 0; i + 1 < PF; ++i) {
+        Vq[i][0] = Vq[i + 1][0];
+        Vq[i][1] = Vq[i + 1][1];
+        Vq[i][2] = Vq[i + 1][2];
+      }
     }
     const T Rh[3] = {Rnext[0], Rnext[1], Rnext[2]};
     if constexpr (RNG) {
@@ -371,15 +438,30 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       Rnext[0] = T(pr[0]);
       Rnext[1] = T(pr[1]);
       Rnext[2] = T(pr[2]);
-    } else if (h + 1 < q.H) {
-      uc += q.sh;
-      Vnext[0] = uc[0];
-      Vnext[1] = uc[q.sa];
-      Vnext[2] = uc[2 * q.sa];
-      if (h + 1 < ref_rem) pr += 3;
-      Rnext[0] = T(pr[0]);
-      Rnext[1] = T(pr[1]);
-      Rnext[2] = T(pr[2]);
+    } else if constexpr (PF == 1) {
+      if (h + 1 < q.H) {   // one branch for both fetches (the form the fp64 kernel was tuned with)
+        Vq[0][0] = uc[0];
+        Vq[0][1] = uc[q.sa];
+        Vq[0][2] = uc[2 * q.sa];
+        uc += q.sh;
+        if (h + 1 < ref_rem) pr += 3;
+        Rnext[0] = T(pr[0]);
+        Rnext[1] = T(pr[1]);
+        Rnext[2] = T(pr[2]);
+      }
+    } else {
+      if (h + PF < q.H) {
+        Vq[PF - 1][0] = uc[0];
+        Vq[PF - 1][1] = uc[q.sa];
+        Vq[PF - 1][2] = uc[2 * q.sa];
+        uc += q.sh;
+      }
+      if (h + 1 < q.H) {
+        if (h + 1 < ref_rem) pr += 3;
+        Rnext[0] = T(pr[0]);
+        Rnext[1] = T(pr[1]);
+        Rnext[2] = T(pr[2]);
+      }
     }
     T Pn[3], An[3];
 #pragma unroll
@@ -476,35 +558,61 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   cat_grid_argmin(jc, ji, prob, block_best, tickets, best_cost, best_idx, q.p2p);
 }
 
-// fold of the per-rank winners gathered from G ranks, on the device: in = G x [cost bits, global idx]
-// (the layout MpcDeviceStep.winner has and all_gather produces), out = [cost bits, idx].  Rank order,
-// np.argmin ordering -> identical on every rank.
-__global__ void k_reduce_winners(int n, const long long* __restrict__ in, long long* __restrict__ out) {
-  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+// fold of n winners, on the device: in = n x [cost bits, global idx] (the layout MpcDeviceStep.winner has and
+// all_gather produces; also the chunk winners of the host pipeline), out = [cost bits, idx].  Input order, MPC
+// winner order (cat_better_mpc) -> identical on every rank.
+__device__ __forceinline__ void cat_fold_pairs(int n, const long long* __restrict__ in, long long& bc_bits,
+                                               long long& bi) {
   double bc = __longlong_as_double(in[0]);
-  long long bi = in[1];
+  bi = in[1];
   for (int g = 1; g < n; ++g) {
     const double c = __longlong_as_double(in[2 * g]);
     const long long i = in[2 * g + 1];
-    if (cat_better(c, i, bc, bi)) {
+    if (cat_better_mpc(c, i, bc, bi)) {
       bc = c;
       bi = i;
     }
   }
-  out[0] = __double_as_longlong(bc);
-  out[1] = bi;
+  bc_bits = __double_as_longlong(bc);
+}
+
+static __global__ void k_reduce_winners(int n, const long long* __restrict__ in, long long* __restrict__ out) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  long long c, i;
+  cat_fold_pairs(n, in, c, i);
+  out[0] = c;
+  out[1] = i;
+}
+
+// The same fold followed by the fused exchange (the host-pointer multi-GPU step with chunked explicit controls:
+// the chunk launches carry no exchange, this one-block kernel does it).  <<<1, 64>>>
+static __global__ void __launch_bounds__(64) k_p2p_exchange(int n, const long long* __restrict__ in, const CatP2PDev p2p,
+                                                     double* __restrict__ best_cost,
+                                                     long long* __restrict__ best_idx) {
+  __shared__ long long s_mine[2];
+  if (threadIdx.x == 0) cat_fold_pairs(n, in, s_mine[0], s_mine[1]);
+  __syncthreads();
+  cat_p2p_finish(s_mine[0], s_mine[1], p2p, best_cost, best_idx);
+}
+
+// job-wide winner of step p2p.seq without posting anything: closes a run of pipelined steps.  <<<1, 64>>>
+static __global__ void __launch_bounds__(64) k_p2p_fold(const CatP2PDev p2p, double* __restrict__ best_cost,
+                                                 long long* __restrict__ best_idx) {
+  cat_p2p_fold(p2p, p2p.seq, best_cost, best_idx);
 }
 
 // materialise the on-device RNG controls: out[p][h][a][k] (SoA over candidates)
 template <typename T>
 __global__ void __launch_bounds__(256) k_sample_controls(const CatMpcDev<T> q, T* __restrict__ out) {
   typedef CatMath<T> M;
+  __shared__ CatIcdfSmem<T> s_icdf;
+  cat_icdf_stage<T>(s_icdf);
   const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= q.K) return;
   const int h = blockIdx.y, prob = blockIdx.z;
   T v[3];
   cat_sample_control<T, M>(q.seed, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + k), (uint32_t)h,
-                           q.sigma, q.clip, v);
+                           q.sigma, q.clip, s_icdf, v);
   T* o = out + (((long long)prob * q.H + h) * 3) * q.K + k;
   o[0] = v[0];
   o[q.K] = v[1];

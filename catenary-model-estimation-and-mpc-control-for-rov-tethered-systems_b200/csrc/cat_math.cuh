@@ -9,6 +9,22 @@
 #include <stdint.h>
 
 // ------------------------------------------------------------------------------------------
+// Cold-path counters (bench.py "sensitivity"): how many warp-level entries the data-dependent slow branches of
+// the rollout take -- [0] the catenary solve's iteration loop (a lane moved beyond the warm step's range or did
+// not converge), [1] the full-range sine (|x| >= 1e5, inf, NaN).  Counting is off unless cat_dbg_on is set
+// (cat_mpc_stats), and the test sits inside the cold branches, so the common path carries nothing.  One copy
+// per translation unit (no relocatable device code); the unit that instantiates the rollout reads its own.
+// ------------------------------------------------------------------------------------------
+__device__ unsigned long long cat_dbg_counters[4];
+__device__ int cat_dbg_on;
+__device__ __forceinline__ void cat_dbg_count(int which) {
+  if (cat_dbg_on) {
+    const unsigned m = __activemask();
+    if ((threadIdx.x & 31) == (unsigned)(__ffs(m) - 1)) atomicAdd(&cat_dbg_counters[which], 1ULL);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // fp64 elementary functions written for this path.  CUDA's sin()/exp() re-materialise their
 // 64-bit literals with UMOV pairs, fetch a coefficient table with LDG and carry inf/nan/huge-
 // argument select chains; in the rollout kernel those were 28% of the issue slots (profiles/r1_*).
@@ -78,6 +94,7 @@ __device__ __forceinline__ void cat_sin_vec_f64(double (&a)[N]) {
     r[n] = __hiloint2double(__double2hiint(v) ^ (q[n] << 31), __double2loint(v));
   }
   if (bad) {
+    cat_dbg_count(1);
 #pragma unroll
     for (int n = 0; n < N; ++n)
       if ((__double2hiint(a[n]) & 0x7fffffff) >= 0x40F86A00) r[n] = sin(a[n]);
@@ -403,6 +420,7 @@ __device__ __forceinline__ CatSolve<T> cat_solve_u(T N, T D, const CatWarm<T>& w
   if constexpr (FULL_WARP) again = __any_sync(0xffffffffu, more);   // every lane of the warp is here
   else again = more;
   if (again) {
+    if constexpr (FULL_WARP) cat_dbg_count(0);
     int it = 1;
     while (more && it < 60) {
       cat_hyp<T, M>(u, sm, cm, sh);
@@ -463,15 +481,45 @@ template <typename T> __device__ __forceinline__ CatWarm<T> cat_cold() {
   return w;
 }
 
-// NEED_C = false skips the division C = 2u/l: the domain test is done on 2u against c*l.
-template <typename T, typename M, bool NEED_C = true, bool FULL_WARP = false>
-__device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, const CatWarm<T>& warm) {
-  CatSpan<T> s;
+// What the solve needs from a span: s2 = L^2 - dH^2, N = s2 - l^2, D = l (sqrt(s2) + l).
+template <typename T> struct CatSpanPrep {
+  T N, D;
+  bool none;   // no root: taut, vertical or degenerate span
+};
+
+template <typename T, typename M>
+__device__ __forceinline__ CatSpanPrep<T> cat_span_prep(T l, T dH, T L) {
+  CatSpanPrep<T> p;
   const T s2 = (L - dH) * (L + dH);
   const T sq = M::sqrt_(M::pos_(s2));
-  const T N = s2 - l * l;
-  const T D = l * (sq + l);
-  const bool none = !(s2 > T(0)) || !(N > T(0)) || !(l > T(0));   // no root: taut, vertical or degenerate span
+  p.N = s2 - l * l;
+  p.D = l * (sq + l);
+  p.none = !(s2 > T(0)) || !(p.N > T(0)) || !(l > T(0));
+  return p;
+}
+
+// fp32 fast mode, stand-alone solves and shapes: N = L^2 - dH^2 - l^2 is formed in fp64 from the fp32 inputs
+// (l2 = l^2 or rel_x^2 + rel_y^2, exact in fp64) and rounded ONCE.  In fp32 the two subtractions lose
+// eps * L^2 / N relative -- 3e-4 in C for a span within 0.1% of taut -- while everything after N (the quotient-free
+// iteration, D, the outputs) is benign in 24 bits.  Four FP64 instructions per solve.
+template <typename M>
+__device__ __forceinline__ CatSpanPrep<float> cat_span_prep_exact(float l, double l2, double dH, double L) {
+  CatSpanPrep<float> p;
+  const double s2d = (L - dH) * (L + dH);
+  const float s2 = (float)s2d;
+  const float sq = M::sqrt_(M::pos_(s2));
+  p.N = (float)(s2d - l2);
+  p.D = l * (sq + l);
+  p.none = !(s2d > 0.0) || !(s2d - l2 > 0.0) || !(l > 0.0f);
+  return p;
+}
+
+// NEED_C = false skips the division C = 2u/l: the domain test is done on 2u against c*l.
+template <typename T, typename M, bool NEED_C = true, bool FULL_WARP = false>
+__device__ __forceinline__ CatSpan<T> cat_span_from(const CatSpanPrep<T>& p, T l, T dH, T L, T c_lo, T c_hi,
+                                                    const CatWarm<T>& warm) {
+  CatSpan<T> s;
+  const bool none = p.none;
   if constexpr (!FULL_WARP) {
     if (none) {
       s.C = M::nan_();
@@ -485,7 +533,8 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, c
   }
   // FULL_WARP (the rollout): no early exit -- a rootless lane solves a harmless stand-in (N = D = 1) and is
   // masked afterwards, so the warp stays converged and the common path is one basic block
-  const CatSolve<T> r = cat_solve_u<T, M, FULL_WARP>(FULL_WARP && none ? T(1) : N, FULL_WARP && none ? T(1) : D, warm);
+  const CatSolve<T> r =
+      cat_solve_u<T, M, FULL_WARP>(FULL_WARP && none ? T(1) : p.N, FULL_WARP && none ? T(1) : p.D, warm);
   s.u = r.u;
   s.sh = r.sh;
   s.ch = r.ch;
@@ -503,6 +552,36 @@ __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, c
   // triple from which the safeguarded iteration converges like from any other start.
   if constexpr (FULL_WARP) s.C = none ? M::nan_() : s.C;
   return s;
+}
+
+template <typename T, typename M, bool NEED_C = true, bool FULL_WARP = false>
+__device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, const CatWarm<T>& warm) {
+  return cat_span_from<T, M, NEED_C, FULL_WARP>(cat_span_prep<T, M>(l, dH, L), l, dH, L, c_lo, c_hi, warm);
+}
+
+// a span given by its components (rel = B - A): fp64 as cat_span; fp32 with the exact N (see cat_span_prep_exact)
+template <typename T, typename M>
+__device__ __forceinline__ CatSpan<T> cat_span_rel(T rx, T ry, T rz, T L, T c_lo, T c_hi, T& l_out) {
+  const T l = M::sqrt_(rx * rx + ry * ry);
+  l_out = l;
+  if constexpr (sizeof(T) == 4) {
+    const double l2 = (double)rx * (double)rx + (double)ry * (double)ry;
+    return cat_span_from<T, M>(cat_span_prep_exact<M>(l, l2, (double)rz, (double)L), l, rz, L, c_lo, c_hi,
+                               cat_cold<T>());
+  } else {
+    return cat_span<T, M>(l, rz, L, c_lo, c_hi, cat_cold<T>());
+  }
+}
+
+// a span given by (l, dH) as main_fun.solve_catenary takes it
+template <typename T, typename M>
+__device__ __forceinline__ CatSpan<T> cat_span_ldh(T l, T dH, T L, T c_lo, T c_hi) {
+  if constexpr (sizeof(T) == 4) {
+    return cat_span_from<T, M>(cat_span_prep_exact<M>(l, (double)l * (double)l, (double)dH, (double)L), l, dH, L,
+                               c_lo, c_hi, cat_cold<T>());
+  } else {
+    return cat_span<T, M>(l, dH, L, c_lo, c_hi, cat_cold<T>());
+  }
 }
 
 // Warm-start record at the cold-start guess of a span, without solving: (u, sinh u - u, cosh u - 1, sinh u)
@@ -616,6 +695,19 @@ __host__ __device__ __forceinline__ bool cat_better(double ca, long long ia, dou
   return ia < ib;
 }
 
+// Winner of a sampling-MPC step: lower cost, then lower index, and a NaN cost ranks with +inf -- a candidate
+// whose rollout produced a NaN must never become the applied control (a receding-horizon loop would feed it to
+// the plant).  With every cost NaN the lowest index wins, which in the controller is candidate 0, the noise-free
+// shifted previous solution.  Definition: oracle.argmin_mpc.  (np.argmin's NaN-first order above stays for
+// the curve's lowest sample, fully_augmented_catenary.py:21.)
+__host__ __device__ __forceinline__ bool cat_better_mpc(double ca, long long ia, double cb, long long ib) {
+  const double inf = __builtin_huge_val();
+  const double a = (ca != ca) ? inf : ca, b = (cb != cb) ? inf : cb;
+  if (a < b) return true;
+  if (a > b) return false;
+  return ia < ib;
+}
+
 // ------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al. 2011) -- counter-based RNG for on-device control sampling
 // ------------------------------------------------------------------------------------------
@@ -635,92 +727,89 @@ __device__ __forceinline__ void cat_philox4x32_10(uint32_t c0, uint32_t c1, uint
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
-// sin and cos of the Box-Muller angle 2 pi (r + 0.5) / 2^32 straight from the counter word r: the nearest quarter
-// turn comes off the top bits, so the argument reduction is exact integer arithmetic, and both functions share
-// one argument on [-pi/4, pi/4] with 6-coefficient interpolants (Chebyshev nodes, mpmath: |error| <= 1.4e-17 and
-// 9e-19).  16 flops + 2 for the argument, against ~35 + range logic for sincospi.
-__constant__ __align__(16) double CAT_SC_C[12] = {   // (sin, cos) coefficient pairs, highest degree first
-    1.5918129293821173e-10, -1.1382632424867702e-11,
-    -2.5051131844989112e-08, 2.087614626839412e-09,
-    2.755731610255237e-06, -2.755731727172975e-07,
-    -0.00019841269836758574, 2.480158729876569e-05,
-    0.008333333333330948, -0.0013888888888887398,
-    -0.16666666666666666, 0.041666666666666664};
-__device__ __forceinline__ void cat_sincos2pi_u32(uint32_t r, double& s, double& c) {
-  const uint32_t k = (r + 0x20000000u) >> 30;             // nearest quarter turn, 0..4
-  const int rem = (int)(r - (k << 30));                    // [-2^29, 2^29)
-  const double x = ((double)rem + 0.5) * 1.4629180792671596e-09;   // 2 pi / 2^32; |x| <= pi/4
-  const double z = x * x;
-  double ps = CAT_SC_C[0], pc = CAT_SC_C[1];
-#pragma unroll
-  for (int i = 1; i < 6; ++i) {
-    ps = fma(ps, z, CAT_SC_C[2 * i]);
-    pc = fma(pc, z, CAT_SC_C[2 * i + 1]);
+// ------------------------------------------------------------------------------------------
+// Standard normal from one Philox word by a tabulated inverse CDF (gen/icdf_table.cuh; the table is the
+// definition, shared with oracle.sample_controls -- tools/make_icdf_table.py):
+//   z(r) = sign * y(r'),  r' = r < 2^31 ? r : ~r (clamped to >= 32),  y(r') = -ndtri((r' + 0.5) / 2^32)
+// y is a cubic in the bits below the top six of r' -- octave e = floor(log2 r') and the next five bits select one
+// of 32 segments per octave, exactly the exponent and leading mantissa bits of (double)r'.  Per normal: one
+// conversion, five integer ops, two 16-byte shared loads, three FMAs -- a quarter of a Box-Muller lane with its
+// logarithm, square root and sine/cosine (the round-1 sampler: ~230 of the 642 instructions per warp-step).
+// Shared memory holds octaves >= 21 (|z| <= 3.297, 10 KB in fp64): candidates are clipped at +-clip (3 sigma
+// in every BASELINE config), so below that octave the lane is clamped and needs no coefficients; a caller that
+// asks for clip > 3.29 sends those lanes (2^-10 of them) to the full table in global memory.
+// ------------------------------------------------------------------------------------------
+#include "gen/icdf_table.cuh"
+#define CAT_ICDF_SMEM_E_LO 21
+#define CAT_ICDF_SMEM_SEGS ((CAT_ICDF_E_HI - CAT_ICDF_SMEM_E_LO + 1) * 32)
+#define CAT_ICDF_SMEM_ZMAX 3.29   // < y(2^21) = 3.2971...
+
+template <typename T> struct CatIcdfSmem {
+  alignas(16) T tab[CAT_ICDF_SMEM_SEGS * 4];
+};
+
+// block-cooperative copy of the hot octaves into shared memory; ends with a barrier
+template <typename T>
+__device__ __forceinline__ void cat_icdf_stage(CatIcdfSmem<T>& sm) {
+  const double2* src =
+      reinterpret_cast<const double2*>(CAT_ICDF_TAB + (CAT_ICDF_SMEM_E_LO - CAT_ICDF_E_LO) * 32 * 4);
+  for (int i = threadIdx.x; i < CAT_ICDF_SMEM_SEGS * 2; i += blockDim.x) {
+    const double2 v = __ldg(src + i);
+    sm.tab[2 * i] = T(v.x);
+    sm.tab[2 * i + 1] = T(v.y);
   }
-  const double sx = fma(x * z, ps, x);                     // sin x = x + x z S(z)
-  const double cx = fma(z * z, pc, fma(-0.5, z, 1.0));     // cos x = 1 - z/2 + z^2 C(z)
-  // angle = k pi/2 + x:  k&3 = 0: (sx, cx)  1: (cx, -sx)  2: (-sx, -cx)  3: (-cx, sx)
-  const bool swap = (k & 1u) != 0;
-  const double s0 = swap ? cx : sx, c0 = swap ? sx : cx;
-  s = __hiloint2double(__double2hiint(s0) ^ (int)((k & 2u) << 30), __double2loint(s0));
-  c = __hiloint2double(__double2hiint(c0) ^ (int)(((k + 1u) & 2u) << 30), __double2loint(c0));
+  __syncthreads();
 }
 
-// Box-Muller radius^2 = -2 ln((r + 0.5) / 2^32) straight from the counter word r (fp64).  x = r + 0.5 is exact and
-// normal, so the exponent and the mantissa on [sqrt(1/2), sqrt 2) come off the high word with integer arithmetic
-// and no special case exists (no zero, denormal, inf or NaN); ln m = 2s + 2s z Q(z), s = (m-1)/(m+1), z = s^2, with
-// a 7-coefficient interpolant of Q (Chebyshev nodes, mpmath: |error| <= 4.6e-18 relative in ln m).  ~32
-// instructions against ~80 for the library log; against np.log over 2e5 words: <= 2.6e-16 relative.
-__constant__ double CAT_LOG_Q[7] = {0.3333333333333335,  0.19999999999949444, 0.14285714313126918, 0.11111105544689748,
-                                    0.09091446216268435, 0.07665805861027504, 0.07308903576708663};
-__device__ __forceinline__ double cat_neg2log_u32(uint32_t r) {
-  const double x = (double)r + 0.5;
-  const int hx = __double2hiint(x) + (0x3ff00000 - 0x3fe6a09e);
-  const int k = (hx >> 20) - 0x3ff;                                   // x = m 2^k, m in [sqrt(1/2), sqrt 2)
-  const double m = __hiloint2double((hx & 0x000fffff) + 0x3fe6a09e, __double2loint(x));
-  const double f = m - 1.0;
-  double y;
-  const double d = 2.0 + f;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
-  double e = fma(-d, y, 1.0);
-  y = fma(y, e, y);
-  e = fma(-d, y, 1.0);
-  y = fma(y, e, y);
-  const double s2 = (f + f) * y;                                      // 2s
-  const double z = 0.25 * (s2 * s2);
-  double q = CAT_LOG_Q[6];
-#pragma unroll
-  for (int i = 5; i >= 0; --i) q = fma(q, z, CAT_LOG_Q[i]);
-  const double lg = fma(s2, z * q, s2);                               // ln m
-  return -2.0 * fma((double)(k - 32), 0.6931471805599453, lg);
+// deep: clip > CAT_ICDF_SMEM_ZMAX (warp-uniform)
+template <typename T, typename M>
+__device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& sm, bool deep) {
+  uint32_t rp = (r & 0x80000000u) ? ~r : r;
+  rp = rp < 32u ? 32u : rp;
+  int seg;
+  T t;
+  if constexpr (sizeof(T) == 8) {
+    const double x = (double)rp;   // exact (rp < 2^31)
+    const int hi = __double2hiint(x);
+    const unsigned lo = (unsigned)__double2loint(x);
+    seg = (hi >> 15) - ((1023 + CAT_ICDF_E_LO) << 5);
+    // mantissa bits below the top five, as 1.t - 1
+    t = __hiloint2double(0x3ff00000 | ((hi & 0x7fff) << 5) | (int)(lo >> 27), (int)(lo << 5)) - 1.0;
+  } else {
+    int b = __float_as_int((float)rp);   // 24-bit rounding moves the sample by < 1e-6 ...
+    b = b > 0x4effffff ? 0x4effffff : b;   // ... and must not round up to 2^31, one octave past the table
+    seg = (b >> 18) - ((127 + CAT_ICDF_E_LO) << 5);
+    t = __int_as_float(0x3f800000 | ((b & 0x3ffff) << 5)) - 1.0f;
+  }
+  const int sseg = seg - (CAT_ICDF_SMEM_E_LO - CAT_ICDF_E_LO) * 32;
+  const T* c = sm.tab + 4 * (sseg < 0 ? 0 : sseg);
+  T c0, c1, c2, c3;
+  if constexpr (sizeof(T) == 8) {
+    const double2 a = *reinterpret_cast<const double2*>(c), b2 = *reinterpret_cast<const double2*>(c + 2);
+    c0 = a.x; c1 = a.y; c2 = b2.x; c3 = b2.y;
+  } else {
+    const float4 a = *reinterpret_cast<const float4*>(c);
+    c0 = a.x; c1 = a.y; c2 = a.z; c3 = a.w;
+  }
+  T y = M::fma_(M::fma_(M::fma_(c3, t, c2), t, c1), t, c0);
+  if (sseg < 0) {
+    if (deep) {
+      const double* g = CAT_ICDF_TAB + 4 * seg;
+      y = M::fma_(M::fma_(M::fma_(T(g[3]), t, T(g[2])), t, T(g[1])), t, T(g[0]));
+    } else {
+      y = T(4);   // beyond every clip <= CAT_ICDF_SMEM_ZMAX: the caller's clamp decides
+    }
+  }
+  return (r & 0x80000000u) ? y : -y;
 }
 
-// three clipped normals scaled by sigma, keyed by (seed, problem, global k, h)
+// three clipped normals scaled by sigma, keyed by (seed, problem, global k, h): Philox words 0..2 -> axes x, y, z
 template <typename T, typename M>
 __device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t problem, uint64_t k, uint32_t h,
-                                                   const T sigma[3], T clip, T out[3]) {
+                                                   const T sigma[3], T clip, const CatIcdfSmem<T>& sm, T out[3]) {
   uint32_t r[4];
   cat_philox4x32_10((uint32_t)k, (uint32_t)(k >> 32), h, problem, (uint32_t)seed, (uint32_t)(seed >> 32), r);
-  T ra, rb, sa, ca, cb;
-  if constexpr (sizeof(T) == 8) {
-    double sb;
-    ra = M::sqrt_(cat_neg2log_u32(r[0]));
-    rb = M::sqrt_(cat_neg2log_u32(r[2]));
-    cat_sincos2pi_u32(r[1], sa, ca);
-    cat_sincos2pi_u32(r[3], sb, cb);
-  } else {
-    const T s = T(2.3283064365386963e-10);   // 2^-32
-    const T u0 = (T(r[0]) + T(0.5)) * s, u2 = (T(r[2]) + T(0.5)) * s;
-    ra = M::sqrt_(T(-2) * M::log_(u0));
-    rb = M::sqrt_(T(-2) * M::log_(u2));
-    const T u1 = (T(r[1]) + T(0.5)) * s, u3 = (T(r[3]) + T(0.5)) * s;
-    M::sincos2pi_(u1, &sa, &ca);
-    cb = M::cos2pi_(u3);
-  }
-  const T z0 = M::clamp_sym_(ra * ca, clip);
-  const T z1 = M::clamp_sym_(ra * sa, clip);
-  const T z2 = M::clamp_sym_(rb * cb, clip);
-  out[0] = z0 * sigma[0];
-  out[1] = z1 * sigma[1];
-  out[2] = z2 * sigma[2];
+  const bool deep = clip > T(CAT_ICDF_SMEM_ZMAX);
+#pragma unroll
+  for (int a = 0; a < 3; ++a) out[a] = M::clamp_sym_(cat_icdf_normal<T, M>(r[a], sm, deep), clip) * sigma[a];
 }

@@ -4,6 +4,7 @@
 // host-pointer entry points, kernel launches.  No CPU fallback anywhere: every compute entry point
 // launches a CUDA kernel or fails with CAT_ECUDA.
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <cstdio>
 #include <cstdlib>
@@ -12,39 +13,17 @@
 #include <string>
 #include <vector>
 
-#include "../../include/catenary_b200.h"
+#include "cat_host.cuh"
 #include "cat_kernels_dyn.cuh"
 #include "cat_kernels_geom.cuh"
-#include "cat_kernels_mpc.cuh"
+#include "cat_mpc_launch.cuh"
 #include "cat_kernels_ctrl.cuh"
 #include "cat_kernels_expr.cuh"
 
+void cat_nvtx_push(const CatCtx*, const char* name) { nvtxRangePushA(name); }
+void cat_nvtx_pop(const CatCtx*) { nvtxRangePop(); }
+
 namespace {
-
-enum { SLOT_A = 0, SLOT_B, SLOT_C, SLOT_D, SLOT_E, SLOT_F, SLOT_G, SLOT_H, SLOT_BEST, SLOT_TICKET, N_SLOTS };
-
-struct CatCtx;
-int fail(CatCtx* c, int code, const char* what, cudaError_t e = cudaSuccess);
-
-struct CatCtx {
-  int device;
-  cudaStream_t own_stream;
-  cudaStream_t aux_stream;    // second lane of the chunked shape pipeline
-  cudaStream_t stream;        // stream in use (own_stream or a caller-owned one)
-  cudaEvent_t ev0, ev1, ev_aux;
-  cudaEvent_t ev_chunk[8];    // H2D chunk k of the pipelined host MPC step is on the device
-  std::string err;
-  int64_t launches;
-  void* slot[N_SLOTS];
-  size_t cap[N_SLOTS];
-  int sm_count;
-  int mpc_block;   // 0 = heuristic; else forced block size (CAT_MPC_BLOCK_SIZE env, tuning only)
-  // device-mapped pinned staging of the host MPC step: [0, kStageWin) winners written by the kernel's last block
-  // (no D2H copy), [kStageWin, kStageBytes) problems + reference rows going up in ONE async copy
-  unsigned char* h_stage;
-  unsigned char* d_stage;   // device alias of h_stage
-};
-constexpr size_t kStageWin = 4096, kStageBytes = 65536;
 
 int stage(CatCtx* c) {
   if (c->h_stage) return CAT_OK;
@@ -62,76 +41,12 @@ int stage(CatCtx* c) {
   return CAT_OK;
 }
 
-int fail(CatCtx* c, int code, const char* what, cudaError_t e) {
-  if (c) {
-    c->err = what;
-    if (e != cudaSuccess) {
-      c->err += ": ";
-      c->err += cudaGetErrorString(e);
-    }
-  }
-  return code;
-}
-
-#define CU(call)                                              \
-  do {                                                        \
-    cudaError_t e__ = (call);                                 \
-    if (e__ != cudaSuccess) return fail(c, CAT_ECUDA, #call, e__); \
-  } while (0)
-
-#define NEED(cond)                                            \
-  do {                                                        \
-    if (!(cond)) return fail(c, CAT_EINVAL, "invalid argument: " #cond); \
-  } while (0)
-
-int bind(CatCtx* c) {
-  CU(cudaSetDevice(c->device));
-  return CAT_OK;
-}
-
-// grow-only device scratch; zero-filled when (re)allocated if zero == true
-int scratch(CatCtx* c, int s, size_t bytes, void** out, bool zero = false) {
-  if (bytes == 0) bytes = 16;
-  if (c->cap[s] < bytes) {
-    if (c->slot[s]) {
-      CU(cudaStreamSynchronize(c->stream));
-      CU(cudaFree(c->slot[s]));
-      c->slot[s] = nullptr;
-      c->cap[s] = 0;
-    }
-    size_t want = bytes + (bytes >> 2);
-    cudaError_t e = cudaMalloc(&c->slot[s], want);
-    if (e != cudaSuccess) {
-      want = bytes;
-      e = cudaMalloc(&c->slot[s], want);
-    }
-    if (e != cudaSuccess) {
-      c->slot[s] = nullptr;
-      return fail(c, CAT_ENOMEM, "cudaMalloc", e);
-    }
-    c->cap[s] = want;
-    if (zero) CU(cudaMemsetAsync(c->slot[s], 0, want, c->stream));
-  }
-  *out = c->slot[s];
-  return CAT_OK;
-}
-
-#define SCRATCH(slot_, bytes_, ptr_)                                   \
-  do {                                                                 \
-    void* p__ = nullptr;                                               \
-    int rc__ = scratch(c, slot_, (size_t)(bytes_), &p__);              \
-    if (rc__ != CAT_OK) return rc__;                                   \
-    ptr_ = reinterpret_cast<decltype(ptr_)>(p__);                      \
-  } while (0)
-
-#define LAUNCHED()                                                     \
-  do {                                                                 \
-    ++c->launches;                                                     \
-    cudaError_t e__ = cudaGetLastError();                              \
-    if (e__ != cudaSuccess) return fail(c, CAT_ECUDA, "kernel launch", e__); \
-  } while (0)
-
-inline unsigned int nblk(long long n, int b) { return (unsigned int)((n + b - 1) / b); }
+// private per-block winner slots + tickets of one in-flight MPC step (cat_mpc_workspace_create)
+struct CatMpcWs {
+  CatBest* bb;
+  unsigned int* tk;
+  size_t n_bb, n_tk;
+};
 
 const double kCLo = 1e-6, kCHi = 10.0;   // bracket of main_fun.py:425
 
@@ -369,6 +284,7 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.p2p.rank = 0;
   q.p2p.n_ranks = 1;
   q.p2p.seq = 0;
+  q.p2p.mode = CAT_P2P_LOCKSTEP;
   q.p2p.err = nullptr;
   q.u_nom = nullptr;
   q.step = nullptr;
@@ -377,19 +293,37 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   return CAT_OK;
 }
 
-// launch of k_mpc_rollout for a filled q; bb/tk = per-block winner slots and tickets (ctx scratch when null)
+// bytes per stored control value of a step with these flags
+template <typename T> inline size_t mpc_control_size(int flags) {
+  return (sizeof(T) == 4 || (flags & CAT_MPC_CONTROLS_F32)) ? 4 : 8;
+}
+
+// launch of k_mpc_rollout for a filled q; bb/tk = per-block winner slots and tickets (the selected workspace,
+// else the ctx scratch, when null)
 template <typename T>
-int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, const T* controls,
+int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, const void* controls,
                const double* p_ref, double* best_cost, long long* best_idx, T* costs, CatBest* bb,
                unsigned int* tk) {
   // Launch shape: one thread per candidate.  (A role-split variant -- dynamics and catenary chains of a
   // candidate in two threads -- was measured in round 1 and was 13% SLOWER at config 3: the kernel is bound by
   // issue slots, not by the dependency chain, and the split duplicates loads and kinematics.  DESIGN.md 9.)
-  const int block = mpc_block_size(c, q.K, q.n_problems);
-  const dim3 grid(nblk(q.K, block), (unsigned)q.n_problems, 1);
+  CatMpcLaunchArgs a;
+  a.block = mpc_block_size(c, q.K, q.n_problems);
+  a.grid = dim3(nblk(q.K, a.block), (unsigned)q.n_problems, 1);
+  a.stream = c->stream;
+  a.rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
+  a.controls_f32 = (q.flags & CAT_MPC_CONTROLS_F32) != 0;
+  NEED(q.p2p.peers == nullptr || q.p2p.n_ranks <= a.block);
+  const size_t n_bb = (size_t)a.grid.x * a.grid.y;
+  if (!bb && c->ws) {
+    CatMpcWs* w = (CatMpcWs*)c->ws;
+    NEED(n_bb <= w->n_bb && (size_t)q.n_problems <= w->n_tk);
+    bb = w->bb;
+    tk = w->tk;
+  }
   if (!bb) {
     void* pp = nullptr;
-    int rc = scratch(c, SLOT_BEST, (size_t)grid.x * grid.y * sizeof(CatBest), &pp);
+    int rc = scratch(c, SLOT_BEST, n_bb * sizeof(CatBest), &pp);
     if (rc) return rc;
     bb = (CatBest*)pp;
     rc = scratch(c, SLOT_TICKET, (size_t)65536 * sizeof(unsigned int), &pp, true);
@@ -397,32 +331,28 @@ int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, 
     tk = (unsigned int*)pp;
   }
   const bool shipped = (q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED);
-  const bool rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
-  const size_t smem =
-      q.prog ? (size_t)(q.n_ops_t + q.n_ops_g) * sizeof(int2) + (size_t)(q.n_c_t + q.n_c_g + 2) * sizeof(T) : 0;
-#define CAT_MPC_LAUNCH(GEN, VM, RNG) \
-  k_mpc_rollout<T, GEN, VM, RNG><<<grid, block, smem, c->stream>>>(q, problems, controls, p_ref, costs, bb, tk, \
-                                                                   best_cost, best_idx)
-  if (q.prog) {   // run-time equation programs
-    if (rng) CAT_MPC_LAUNCH(false, true, true); else CAT_MPC_LAUNCH(false, true, false);
-  } else if (shipped) {
-    if (rng) CAT_MPC_LAUNCH(false, false, true); else CAT_MPC_LAUNCH(false, false, false);
-  } else {
-    if (rng) CAT_MPC_LAUNCH(true, false, true); else CAT_MPC_LAUNCH(true, false, false);
-  }
-#undef CAT_MPC_LAUNCH
-  LAUNCHED();
+  a.smem = q.prog ? (size_t)(q.n_ops_t + q.n_ops_g) * sizeof(int2) + (size_t)(q.n_c_t + q.n_c_g + 2) * sizeof(T) : 0;
+  int e;
+  if (q.prog)   // run-time equation programs
+    e = cat_mpc_launch_inst<T, CAT_KIND_VM>(a, q, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
+  else if (shipped)
+    e = cat_mpc_launch_inst<T, CAT_KIND_SHIPPED>(a, q, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
+  else
+    e = cat_mpc_launch_inst<T, CAT_KIND_GENERIC>(a, q, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
+  ++c->launches;
+  if (e != (int)cudaSuccess) return fail(c, CAT_ECUDA, "kernel launch (k_mpc_rollout)", (cudaError_t)e);
   return CAT_OK;
 }
 
 template <typename T>
-int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
+int mpc_step_dev(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const void* controls,
                  const double* p_ref, double* best_cost, long long* best_idx, T* costs) {
   CatMpcDev<T> q;
   int rc = mpc_fill<T>(c, p, q);
   if (rc) return rc;
   const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
   NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
+  CatNvtxRange r(c, "cat_mpc_step_dev");
   return mpc_launch<T>(c, q, problems, controls, p_ref, best_cost, best_idx, costs, nullptr, nullptr);
 }
 
@@ -446,6 +376,10 @@ int mpc_attach_programs(CatCtx* c, const CatHostPrograms* hp, CatMpcDev<T>& q) {
   if (rc) return rc;
   const size_t b_ops = (size_t)(hp->n_ops_t + hp->n_ops_g) * sizeof(int2);
   const size_t b_c = (size_t)(hp->n_c_t + hp->n_c_g + 1) * sizeof(double);
+  // both programs are staged in the rollout's dynamic shared memory: keep the pair inside the 48 KB a kernel
+  // gets without opting in (a pair of PySR equations is a few hundred bytes; expr_validate alone would admit 64 KB)
+  if (b_ops + (size_t)(hp->n_c_t + hp->n_c_g + 2) * sizeof(T) > 48 * 1024)
+    return fail(c, CAT_EINVAL, "equation programs too large for the rollout kernel (ops + constants > 48 KB)");
   unsigned char* base;
   SCRATCH(SLOT_G, b_ops + b_c, base);
   int2* d_ops = (int2*)base;
@@ -474,19 +408,46 @@ int mpc_attach_programs(CatCtx* c, const CatHostPrograms* hp, CatMpcDev<T>& q) {
   return CAT_OK;
 }
 
+// fused winner exchange over NVLink peer memory (CUDA IPC between the ranks of one node)
+struct CatP2P {
+  CatCtx* c;
+  int rank, n_ranks;
+  unsigned int seq;          // steps launched so far
+  int mode;                  // CAT_P2P_MODE_*
+  long long* slots;          // this rank's buffer [CAT_P2P_RING][n_ranks][CAT_P2P_SLOT_W]
+  long long** d_peers;       // device array of n_ranks buffer addresses
+  void* opened[CAT_P2P_MAX_RANKS];   // peers' mappings (null for self)
+  int* d_err;
+  bool connected;
+};
+
+inline void p2p_arm(const CatP2P* x, CatP2PDev& d) {   // the NEXT step's exchange parameters
+  d.peers = x->d_peers;
+  d.rank = x->rank;
+  d.n_ranks = x->n_ranks;
+  d.seq = x->seq + 1;
+  d.mode = x->mode;
+  d.err = x->d_err;
+}
+
+// Host-pointer MPC step.  x != null: the winners of the ranks are exchanged inside the step (lock-step) and
+// best_cost / best_idx receive the JOB-WIDE winner (one problem).
 template <typename T>
-int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
+int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problems, const void* controls,
                   const double* p_ref, double* best_cost, int64_t* best_idx, T* costs,
-                  const CatHostPrograms* hp = nullptr) {
+                  const CatHostPrograms* hp = nullptr, CatP2P* x = nullptr) {
   NEED(p != nullptr && p->K >= 1 && p->H >= 1 && p->n_problems >= 1);
   const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
   NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
+  NEED(x == nullptr || (x->c == c && x->connected && p->n_problems == 1 && x->mode == CAT_P2P_MODE_LOCKSTEP));
   int rc = bind(c);
   if (rc) return rc;
+  CatNvtxRange range(c, x ? "cat_mpc_step_p2p (host)" : "cat_mpc_step (host)");
   const size_t np = (size_t)p->n_problems;
+  const size_t esz = mpc_control_size<T>(p->flags);
   const size_t n_ctl = rng ? 0 : np * (size_t)p->H * 3 * (size_t)p->K;
   CatMpcProblem* d_prob;
-  T* d_ctl = nullptr;
+  unsigned char* d_ctl = nullptr;
   double* d_ref;
   double* d_bc;
   long long* d_bi;
@@ -497,7 +458,7 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   const size_t b_prob = (np * sizeof(CatMpcProblem) + 15) & ~(size_t)15;
   const size_t b_ref = np * (size_t)p->H * 3 * sizeof(double);
   const bool staged = np * 16 <= kStageWin && b_prob + b_ref <= kStageBytes - kStageWin;
-  if (!rng) SCRATCH(SLOT_B, n_ctl * sizeof(T), d_ctl);
+  if (!rng) SCRATCH(SLOT_B, n_ctl * esz, d_ctl);
   if (costs) SCRATCH(SLOT_E, np * (size_t)p->K * sizeof(T), d_costs);
   if (staged) {
     rc = stage(c);
@@ -518,59 +479,83 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     CU(cudaMemcpyAsync(d_ref, p_ref, b_ref, cudaMemcpyHostToDevice, c->stream));
   }
   d_bi = (long long*)(d_bc + np);
-  if (!rng && np == 1 && p->K >= 32768) {
-    // One problem, explicit controls (config 3: 78.6 MB): the step is PCIe-bound, so the candidates go up in 8
-    // chunks on the aux stream and chunk i's rollout overlaps chunk i+1's copy; the chunk winners fold on the
-    // device in candidate order (same total order as one launch: lowest cost, then lowest global index).
-    const int NC = 8;
-    CatMpcDev<T> q;
-    rc = mpc_fill<T>(c, p, q);
+  CatMpcDev<T> q;
+  rc = mpc_fill<T>(c, p, q);
+  if (rc) return rc;
+  if (hp) {
+    rc = mpc_attach_programs<T>(c, hp, q);
     if (rc) return rc;
-    if (hp) {
-      rc = mpc_attach_programs<T>(c, hp, q);
-      if (rc) return rc;
-    }
+  }
+  // the shared scratch slots serve the host call (it synchronises before it returns); a workspace selected for
+  // *_dev launches on other streams is left alone
+  void* const ws_saved = c->ws;
+  c->ws = nullptr;
+  if (!rng && np == 1 && p->K >= 32768) {
+    // One problem, explicit controls (config 3: 78.6 MB in fp64, 39.3 MB as float): the step is PCIe-bound, so
+    // the candidates go up in 8 chunks on the aux stream and chunk i's rollout overlaps chunk i+1's copy; the chunk
+    // winners fold on the device in candidate order (same total order as one launch: lowest cost, then lowest
+    // global index).
+    const int NC = 8;
     long long* d_pairs;
     SCRATCH(SLOT_F, (size_t)NC * 16, d_pairs);
     const bool aos = (p->flags & CAT_MPC_CONTROLS_AOS) != 0;
     const long long K = p->K, H3 = 3LL * p->H;
+    const unsigned char* h_ctl = (const unsigned char*)controls;
     int used = 0;
-    for (int i = 0; i < NC; ++i) {
+    for (int i = 0; i < NC && rc == CAT_OK; ++i) {
       const long long k0 = ((K * i / NC) + 127) / 128 * 128;
       long long k1 = (i == NC - 1) ? K : ((K * (i + 1) / NC) + 127) / 128 * 128;
       if (k1 > K) k1 = K;
       if (k1 <= k0) continue;
+      cudaError_t e;
       if (aos)
-        CU(cudaMemcpyAsync(d_ctl + k0 * H3, controls + k0 * H3, (size_t)(k1 - k0) * H3 * sizeof(T),
-                           cudaMemcpyHostToDevice, c->aux_stream));
+        e = cudaMemcpyAsync(d_ctl + (size_t)(k0 * H3) * esz, h_ctl + (size_t)(k0 * H3) * esz,
+                            (size_t)(k1 - k0) * H3 * esz, cudaMemcpyHostToDevice, c->aux_stream);
       else
-        CU(cudaMemcpy2DAsync(d_ctl + k0, (size_t)K * sizeof(T), controls + k0, (size_t)K * sizeof(T),
-                             (size_t)(k1 - k0) * sizeof(T), (size_t)H3, cudaMemcpyHostToDevice, c->aux_stream));
-      CU(cudaEventRecord(c->ev_chunk[i], c->aux_stream));
-      CU(cudaStreamWaitEvent(c->stream, c->ev_chunk[i], 0));
+        e = cudaMemcpy2DAsync(d_ctl + (size_t)k0 * esz, (size_t)K * esz, h_ctl + (size_t)k0 * esz, (size_t)K * esz,
+                              (size_t)(k1 - k0) * esz, (size_t)H3, cudaMemcpyHostToDevice, c->aux_stream);
+      if (e == cudaSuccess) e = cudaEventRecord(c->ev_chunk[i], c->aux_stream);
+      if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, c->ev_chunk[i], 0);
+      if (e != cudaSuccess) {
+        rc = fail(c, CAT_ECUDA, "chunked control upload", e);
+        break;
+      }
       CatMpcDev<T> qi = q;
       qi.K = k1 - k0;
       qi.k_offset = p->k_offset + k0;
-      rc = mpc_launch<T>(c, qi, d_prob, d_ctl + k0 * q.sk, d_ref, (double*)(d_pairs + 2 * used),
+      rc = mpc_launch<T>(c, qi, d_prob, d_ctl + (size_t)(k0 * q.sk) * esz, d_ref, (double*)(d_pairs + 2 * used),
                          d_pairs + 2 * used + 1, d_costs ? d_costs + k0 : nullptr, nullptr, nullptr);
-      if (rc) return rc;
       ++used;
     }
-    k_reduce_winners<<<1, 32, 0, c->stream>>>(used, d_pairs, (long long*)d_bc);   // -> d_bc[0], d_bi[0]
-    LAUNCHED();
-  } else {
-    if (!rng) CU(cudaMemcpyAsync(d_ctl, controls, n_ctl * sizeof(T), cudaMemcpyHostToDevice, c->stream));
-    if (hp) {
-      CatMpcDev<T> q;
-      rc = mpc_fill<T>(c, p, q);
-      if (rc) return rc;
-      rc = mpc_attach_programs<T>(c, hp, q);
-      if (rc) return rc;
-      rc = mpc_launch<T>(c, q, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs, nullptr, nullptr);
-    } else {
-      rc = mpc_step_dev<T>(c, p, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs);
+    if (rc == CAT_OK) {
+      if (x) {
+        CatP2PDev d;
+        p2p_arm(x, d);
+        k_p2p_exchange<<<1, 64, 0, c->stream>>>(used, d_pairs, d, d_bc, d_bi);
+      } else {
+        k_reduce_winners<<<1, 32, 0, c->stream>>>(used, d_pairs, (long long*)d_bc);   // -> d_bc[0], d_bi[0]
+      }
+      ++c->launches;
+      const cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) rc = fail(c, CAT_ECUDA, "kernel launch (winner fold)", e);
+      else if (x) ++x->seq;
     }
-    if (rc) return rc;
+  } else {
+    if (!rng) {
+      const cudaError_t e = cudaMemcpyAsync(d_ctl, controls, n_ctl * esz, cudaMemcpyHostToDevice, c->stream);
+      if (e != cudaSuccess) rc = fail(c, CAT_ECUDA, "control upload", e);
+    }
+    if (rc == CAT_OK) {
+      if (x) p2p_arm(x, q.p2p);
+      rc = mpc_launch<T>(c, q, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs, nullptr, nullptr);
+      if (rc == CAT_OK && x) ++x->seq;
+    }
+  }
+  c->ws = ws_saved;
+  if (rc) {
+    cudaStreamSynchronize(c->aux_stream);
+    cudaStreamSynchronize(c->stream);
+    return rc;
   }
   if (!staged) {
     CU(cudaMemcpyAsync(best_cost, d_bc, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -925,18 +910,7 @@ int ctrl_run(CatCtrl* k, int32_t n_steps) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// fused winner exchange over NVLink peer memory (CUDA IPC between the ranks of one node)
-struct CatP2P {
-  CatCtx* c;
-  int rank, n_ranks;
-  unsigned int seq;
-  long long* slots;          // this rank's buffer [2][n_ranks][CAT_P2P_SLOT_W]
-  long long** d_peers;       // device array of n_ranks buffer addresses
-  void* opened[CAT_P2P_MAX_RANKS];   // peers' mappings (null for self)
-  int* d_err;
-  bool connected;
-};
-
+// fused winner exchange over NVLink peer memory: device-pointer step
 void p2p_free(CatP2P* x) {
   if (!x) return;
   cudaSetDevice(x->c->device);
@@ -950,20 +924,19 @@ void p2p_free(CatP2P* x) {
 }
 
 template <typename T>
-int mpc_step_p2p_dev(CatCtx* c, CatP2P* x, const CatMpcParams* p, const CatMpcProblem* problems, const T* controls,
-                     const double* p_ref, double* best_cost, long long* best_idx, T* costs) {
+int mpc_step_p2p_dev(CatCtx* c, CatP2P* x, const CatMpcParams* p, const CatMpcProblem* problems,
+                     const void* controls, const double* p_ref, double* best_cost, long long* best_idx, T* costs) {
   NEED(x != nullptr && x->c == c && x->connected);
   CatMpcDev<T> q;
   int rc = mpc_fill<T>(c, p, q);
   if (rc) return rc;
   const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
   NEED(p->n_problems == 1 && problems && p_ref && best_cost && best_idx && (rng || controls));
-  q.p2p.peers = x->d_peers;
-  q.p2p.rank = x->rank;
-  q.p2p.n_ranks = x->n_ranks;
-  q.p2p.seq = ++x->seq;
-  q.p2p.err = x->d_err;
-  return mpc_launch<T>(c, q, problems, controls, p_ref, best_cost, best_idx, costs, nullptr, nullptr);
+  CatNvtxRange r(c, x->mode == CAT_P2P_MODE_PIPELINED ? "cat_mpc_step_p2p_dev (pipelined)" : "cat_mpc_step_p2p_dev");
+  p2p_arm(x, q.p2p);
+  rc = mpc_launch<T>(c, q, problems, controls, p_ref, best_cost, best_idx, costs, nullptr, nullptr);
+  if (rc == CAT_OK) ++x->seq;   // a launch that failed posts nothing: the ranks stay in step
+  return rc;
 }
 
 }  // namespace
@@ -992,6 +965,10 @@ int cat_init(int device, void** ctx) {
   c->launches = 0;
   c->mpc_block = 0;
   c->h_stage = c->d_stage = nullptr;
+  c->ws = nullptr;
+  c->n_reg = 0;
+  c->nvtx = 0;
+  if (const char* e = std::getenv("CAT_NVTX")) c->nvtx = std::atoi(e) != 0;
   if (const char* e = std::getenv("CAT_MPC_BLOCK_SIZE")) {
     const int v = std::atoi(e);
     if (v == 32 || v == 64 || v == 128) c->mpc_block = v;
@@ -1023,6 +1000,7 @@ int cat_destroy(void* ctx) {
   for (int s = 0; s < N_SLOTS; ++s)
     if (c->slot[s]) cudaFree(c->slot[s]);
   if (c->h_stage) cudaFreeHost(c->h_stage);
+  for (int i = 0; i < c->n_reg; ++i) cudaHostUnregister(c->reg[i].p);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
   cudaEventDestroy(c->ev_aux);
@@ -1073,6 +1051,106 @@ int cat_host_alloc(void* ctx, size_t bytes, void** out) {
 int cat_host_free(void* ctx, void* p) {
   CTX();
   if (p) CU(cudaFreeHost(p));
+  return CAT_OK;
+}
+
+int cat_host_register(void* ctx, void* p, size_t bytes) {
+  CTX();
+  NEED(p != nullptr && bytes > 0);
+  for (int i = 0; i < c->n_reg; ++i)
+    if (c->reg[i].p == p) return c->reg[i].bytes >= bytes ? CAT_OK : fail(c, CAT_EINVAL, "range registered with a smaller size");
+  NEED(c->n_reg < 64);
+  int rc = bind(c);
+  if (rc) return rc;
+  cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(c, CAT_ECUDA, "cudaHostRegister", e);
+  }
+  c->reg[c->n_reg].p = p;
+  c->reg[c->n_reg].bytes = bytes;
+  ++c->n_reg;
+  return CAT_OK;
+}
+
+int cat_host_unregister(void* ctx, void* p) {
+  CTX();
+  for (int i = 0; i < c->n_reg; ++i)
+    if (c->reg[i].p == p) {
+      cudaStreamSynchronize(c->stream);
+      cudaStreamSynchronize(c->aux_stream);
+      cudaError_t e = cudaHostUnregister(p);
+      c->reg[i] = c->reg[--c->n_reg];
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(c, CAT_ECUDA, "cudaHostUnregister", e);
+      }
+      return CAT_OK;
+    }
+  return fail(c, CAT_EINVAL, "range was not registered on this context");
+}
+
+int cat_mpc_workspace_create(void* ctx, int64_t max_candidates, int32_t max_problems, void** ws) {
+  CTX();
+  NEED(ws != nullptr);
+  *ws = nullptr;
+  NEED(max_candidates >= 1 && max_problems >= 1 && max_problems <= 65535);
+  int rc = bind(c);
+  if (rc) return rc;
+  CatMpcWs* w = new (std::nothrow) CatMpcWs();
+  if (!w) return fail(c, CAT_ENOMEM, "workspace allocation");
+  w->n_bb = (size_t)((max_candidates + 31) / 32) * (size_t)max_problems;   // any block size >= 32
+  w->n_tk = (size_t)max_problems;
+  w->bb = nullptr;
+  w->tk = nullptr;
+  cudaError_t e = cudaMalloc((void**)&w->bb, w->n_bb * sizeof(CatBest));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&w->tk, w->n_tk * sizeof(unsigned int));
+  if (e == cudaSuccess) e = cudaMemset(w->tk, 0, w->n_tk * sizeof(unsigned int));   // synchronous: ready on any stream
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    if (w->bb) cudaFree(w->bb);
+    if (w->tk) cudaFree(w->tk);
+    delete w;
+    return fail(c, CAT_ENOMEM, "cudaMalloc (workspace)", e);
+  }
+  *ws = w;
+  return CAT_OK;
+}
+
+int cat_mpc_workspace_destroy(void* ctx, void* ws) {
+  CTX();
+  CatMpcWs* w = (CatMpcWs*)ws;
+  if (!w) return CAT_OK;
+  if (c->ws == ws) c->ws = nullptr;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  cudaFree(w->bb);
+  cudaFree(w->tk);
+  delete w;
+  return CAT_OK;
+}
+
+int cat_set_workspace(void* ctx, void* ws_or_null) {
+  CTX();
+  c->ws = ws_or_null;
+  return CAT_OK;
+}
+
+int cat_mpc_stats(void* ctx, int enable, int reset, uint64_t* out) {
+  CTX();
+  int rc = bind(c);
+  if (rc) return rc;
+  unsigned long long acc[4] = {0, 0, 0, 0};
+  unsigned long long* o = out ? acc : nullptr;
+  int e = cat_mpc_inst_stats<double, 0>(enable, reset, o);
+  if (!e) e = cat_mpc_inst_stats<double, 1>(enable, reset, o);
+  if (!e) e = cat_mpc_inst_stats<double, 2>(enable, reset, o);
+  if (!e) e = cat_mpc_inst_stats<float, 0>(enable, reset, o);
+  if (!e) e = cat_mpc_inst_stats<float, 1>(enable, reset, o);
+  if (!e) e = cat_mpc_inst_stats<float, 2>(enable, reset, o);
+  if (e) return fail(c, CAT_ECUDA, "cat_mpc_stats", (cudaError_t)e);
+  if (out)
+    for (int i = 0; i < 4; ++i) out[i] = acc[i];
   return CAT_OK;
 }
 
@@ -1331,7 +1409,7 @@ int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx, double
   double bc = cost[0];
   long long bi = idx[0];
   for (int g = 1; g < n; ++g)
-    if (cat_better(cost[g], idx[g], bc, bi)) {
+    if (cat_better_mpc(cost[g], idx[g], bc, bi)) {
       bc = cost[g];
       bi = idx[g];
     }
@@ -1501,7 +1579,8 @@ int cat_p2p_create(void* ctx, int rank, int n_ranks, void** p2p, void* handle_ou
   x->c = c;
   x->rank = rank;
   x->n_ranks = n_ranks;
-  const size_t bytes = (size_t)2 * n_ranks * CAT_P2P_SLOT_W * sizeof(long long);
+  x->mode = CAT_P2P_MODE_LOCKSTEP;
+  const size_t bytes = (size_t)CAT_P2P_RING * n_ranks * CAT_P2P_SLOT_W * sizeof(long long);
   cudaError_t e = cudaMalloc((void**)&x->slots, bytes);
   if (e == cudaSuccess) e = cudaMemset(x->slots, 0, bytes);
   if (e == cudaSuccess) e = cudaMalloc((void**)&x->d_peers, (size_t)n_ranks * sizeof(long long*));
@@ -1559,6 +1638,41 @@ int cat_mpc_step_p2p_dev_f32(void* ctx, void* p2p, const CatMpcParams* p, const 
   if (rc) return rc;
   return mpc_step_p2p_dev<float>(c, (CatP2P*)p2p, p, problems, controls, p_ref, best_cost, (long long*)best_idx, costs);
 }
+int cat_mpc_step_p2p_f64(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
+                         const double* controls, const double* p_ref, double* best_cost, int64_t* best_idx,
+                         double* costs) {
+  CTX();
+  NEED(p2p != nullptr);
+  return mpc_step_host<double>(c, p, problems, controls, p_ref, best_cost, best_idx, costs, nullptr, (CatP2P*)p2p);
+}
+int cat_mpc_step_p2p_f32(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
+                         const float* controls, const double* p_ref, double* best_cost, int64_t* best_idx,
+                         float* costs) {
+  CTX();
+  NEED(p2p != nullptr);
+  return mpc_step_host<float>(c, p, problems, controls, p_ref, best_cost, best_idx, costs, nullptr, (CatP2P*)p2p);
+}
+int cat_p2p_set_mode(void* p2p, int mode) {
+  CatP2P* x = (CatP2P*)p2p;
+  if (!x) return CAT_EINVAL;
+  CatCtx* c = x->c;
+  NEED(mode == CAT_P2P_MODE_LOCKSTEP || mode == CAT_P2P_MODE_PIPELINED);
+  x->mode = mode;
+  return CAT_OK;
+}
+int cat_p2p_flush_dev(void* ctx, void* p2p, double* best_cost, int64_t* best_idx) {
+  CTX();
+  CatP2P* x = (CatP2P*)p2p;
+  NEED(x != nullptr && x->c == c && x->connected && best_cost && best_idx);
+  int rc = bind(c);
+  if (rc) return rc;
+  CatP2PDev d;
+  p2p_arm(x, d);
+  d.seq = x->seq;   // the step already launched, not the next one
+  k_p2p_fold<<<1, 64, 0, c->stream>>>(d, best_cost, (long long*)best_idx);
+  LAUNCHED();
+  return CAT_OK;
+}
 int cat_p2p_status(void* p2p, int* timed_out) {
   CatP2P* x = (CatP2P*)p2p;
   if (!x || !timed_out) return CAT_EINVAL;
@@ -1567,6 +1681,7 @@ int cat_p2p_status(void* p2p, int* timed_out) {
   if (rc) return rc;
   CU(cudaStreamSynchronize(c->stream));
   CU(cudaMemcpy(timed_out, x->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+  if (*timed_out) CU(cudaMemset(x->d_err, 0, sizeof(int)));
   return CAT_OK;
 }
 int cat_p2p_destroy(void* p2p) {

@@ -1,0 +1,51 @@
+// mpc_inst.cu -- instantiations of k_mpc_rollout for ONE (compute type, equation source) pair, selected by
+//   -DCAT_INST_T=double|float  -DCAT_INST_KIND=0 (shipped pair, generated code) | 1 (any hall-of-fame row) |
+//   2 (run-time equation programs).  build.py compiles this file six times, in parallel.
+#include <cuda_runtime.h>
+
+#include "cat_mpc_launch.cuh"
+
+#if !defined(CAT_INST_T) || !defined(CAT_INST_KIND)
+#error "compile with -DCAT_INST_T=<double|float> -DCAT_INST_KIND=<0|1|2>"
+#endif
+
+typedef CAT_INST_T InstT;
+constexpr bool kGen = CAT_INST_KIND == CAT_KIND_GENERIC;
+constexpr bool kVm = CAT_INST_KIND == CAT_KIND_VM;
+
+template <>
+int cat_mpc_launch_inst<InstT, CAT_INST_KIND>(const CatMpcLaunchArgs& a, const CatMpcDev<InstT>& q,
+                                              const CatMpcProblem* problems, const void* controls,
+                                              const double* p_ref, InstT* costs, CatBest* bb, unsigned int* tk,
+                                              double* best_cost, long long* best_idx) {
+  if (a.rng) {
+    k_mpc_rollout<InstT, InstT, kGen, kVm, true><<<a.grid, a.block, a.smem, a.stream>>>(
+        q, problems, (const InstT*)nullptr, p_ref, costs, bb, tk, best_cost, best_idx);
+  } else if (sizeof(InstT) == 8 && a.controls_f32) {
+    k_mpc_rollout<InstT, float, kGen, kVm, false><<<a.grid, a.block, a.smem, a.stream>>>(
+        q, problems, (const float*)controls, p_ref, costs, bb, tk, best_cost, best_idx);
+  } else {
+    k_mpc_rollout<InstT, InstT, kGen, kVm, false><<<a.grid, a.block, a.smem, a.stream>>>(
+        q, problems, (const InstT*)controls, p_ref, costs, bb, tk, best_cost, best_idx);
+  }
+  return (int)cudaGetLastError();
+}
+
+template <> int cat_mpc_inst_stats<InstT, CAT_INST_KIND>(int enable, int reset, unsigned long long* out) {
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return (int)e;
+  if (out) {
+    unsigned long long v[4];
+    e = cudaMemcpyFromSymbol(v, cat_dbg_counters, sizeof(v));
+    if (e != cudaSuccess) return (int)e;
+    for (int i = 0; i < 4; ++i) out[i] += v[i];
+  }
+  if (reset) {
+    const unsigned long long z[4] = {0, 0, 0, 0};
+    e = cudaMemcpyToSymbol(cat_dbg_counters, z, sizeof(z));
+    if (e != cudaSuccess) return (int)e;
+  }
+  const int on = enable ? 1 : 0;
+  e = cudaMemcpyToSymbol(cat_dbg_on, &on, sizeof(on));
+  return (int)e;
+}

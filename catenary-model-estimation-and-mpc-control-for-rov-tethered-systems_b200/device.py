@@ -9,12 +9,13 @@ import numpy as np
 
 from . import _lib
 from .context import Context
-from .mpc import make_params, make_problems
+from .mpc import _wire_controls, make_params, make_problems
 
 
 class MpcDeviceStep:
     def __init__(self, params, p_ref, K, *, controls=None, layout="H3K", sigma=None, seed=0, clip=3.0, k_offset=0,
-                 problems=None, problem_offset=0, keep_costs=False, dtype=np.float64, device=0, ctx=None):
+                 problems=None, problem_offset=0, keep_costs=False, dtype=np.float64, device=0, ctx=None,
+                 controls_dtype=None, private_workspace=False):
         import torch
         self.torch = torch
         self.dev = torch.device("cuda", device)
@@ -35,7 +36,9 @@ class MpcDeviceStep:
         else:
             if layout == "KH3":
                 flags |= _lib.MPC_CONTROLS_AOS
-            self.controls = torch.as_tensor(np.ascontiguousarray(controls, self.dtype)).to(self.dev)
+            U, wire = _wire_controls(controls, self.dtype, controls_dtype)   # float32 storage under fp64 arithmetic
+            flags |= wire
+            self.controls = torch.as_tensor(U).to(self.dev)
         self.params = make_params(params, K, H, n_problems=n, k_offset=k_offset, problem_offset=problem_offset,
                                   flags=flags, seed=seed, sigma=(0, 0, 0) if sigma is None else sigma, clip=clip)
         self.K, self.H, self.n = int(K), int(H), int(n)
@@ -49,6 +52,13 @@ class MpcDeviceStep:
         self.costs = torch.empty((n, K), dtype=tdt, device=self.dev) if keep_costs else None
         self._host_winner = None
         self._fn = self.ctx.lib.cat_mpc_step_dev_f64 if self.dtype == np.float64 else self.ctx.lib.cat_mpc_step_dev_f32
+        # per-block winner slots + tickets of THIS step object: steps that share a Context may then be in flight on
+        # different streams at once (the context's own scratch is shared by every launch on it)
+        self._ws = None
+        if private_workspace:
+            h = C.c_void_p()
+            self.ctx.check(self.ctx.lib.cat_mpc_workspace_create(self.ctx.handle, self.K, self.n, C.byref(h)))
+            self._ws = h
 
     def set_controls(self, controls_dev):
         """Swap in another device tensor of candidate controls (same layout and dtype)."""
@@ -72,6 +82,7 @@ class MpcDeviceStep:
         else:
             wp = (self.winner if winner is None else winner).data_ptr()
         self.ctx.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
+        self.ctx.lib.cat_set_workspace(self.ctx.handle, self._ws)
         self.ctx.check(self._fn(self.ctx.handle, C.byref(self.params), self.problems.data_ptr(),
                                 None if self.controls is None else self.controls.data_ptr(), self.p_ref.data_ptr(),
                                 wp, wp + 8 * self.n,
@@ -87,6 +98,18 @@ class MpcDeviceStep:
         """(best_idx (n,), best_cost (n,)) on the host (one small D2H + sync)."""
         w = self.winner.cpu().numpy()
         return w[self.n:].copy(), w[:self.n].view(np.float64).copy()
+
+    def close(self):
+        if self._ws is not None and self.ctx.handle:
+            self.ctx.lib.cat_set_workspace(self.ctx.handle, None)
+            self.ctx.lib.cat_mpc_workspace_destroy(self.ctx.handle, self._ws)
+        self._ws = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def sample_controls(params, K, H, sigma, *, seed=0, clip=3.0, k_offset=0, problem_offset=0, n_problems=1, device=0,

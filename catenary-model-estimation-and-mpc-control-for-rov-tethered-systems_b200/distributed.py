@@ -3,14 +3,17 @@ contiguous shards, ONE (cost, index) exchange per step.
 
 NCCL has no MINLOC and an fp64 cost + int64 index do not pack into one 64-bit min, so every rank all-gathers
 the 16-byte winners and folds them in rank order with the lowest-global-index tie-break
-(cat_reduce_winners_f64) -- identical on every rank and identical to np.argmin over the concatenated costs.
+(cat_reduce_winners_f64; a NaN cost ranks with +inf) -- identical on every rank and identical to np.argmin over the concatenated costs.
 The fleet configuration (independent problems) shards problems and needs no communication.
 """
 from __future__ import annotations
 
 import numpy as np
 
+from . import _lib
 from .mpc import reduce_winners
+
+_P2P_LOCKSTEP, _P2P_PIPELINED = _lib.P2P_LOCKSTEP, _lib.P2P_PIPELINED
 
 
 def shard_range(total, rank, world):
@@ -130,28 +133,42 @@ class PipelinedExchange:
 
 
 class P2PWinnerExchange:
-    """Fused multi-GPU step: ONE kernel per step per rank.  The rollout's last block writes this
-    rank's (cost, global idx) into every peer's slot buffer over NVLink (CUDA IPC mappings), waits for the peers'
-    winners of the same step and folds them in rank order -- when the kernel ends, ``step.winner`` holds the
-    JOB-WIDE winner on every rank (same value as ``exchange_winner``), with no NCCL call and no second launch.
-    The process group is used once, at construction, to swap the 64-byte IPC handles."""
+    """Fused multi-GPU step: ONE kernel per step per rank.  The rollout's last block posts this
+    rank's (cost, global idx) into every peer's slot buffer over NVLink (CUDA IPC mappings) and folds the G
+    winners in rank order, with no NCCL call and no second launch:
 
-    def __init__(self, step, group=None):
+    * ``launch()`` (lock-step): the kernel waits for the peers' winners of the SAME step -- when it ends,
+      ``step.winner`` holds the JOB-WIDE winner on every rank (same value as ``exchange_winner``).  The latency path.
+    * ``launch(pipelined=True)``: the kernel folds the winners of the PREVIOUS step (posted a whole rollout ago, so
+      nothing spins and back-to-back steps of G processes do not pay each other's launch jitter); the winner of
+      step s arrives with step s+1, or with ``flush()`` after the last one.  The throughput path.
+    * ``mpc.mpc_sample_step(..., p2p=self)``: NumPy in, job-wide winner out (cat_mpc_step_p2p_*, lock-step).
+
+    A peer that does not show up within a few seconds makes the step return the sentinel (NaN, -1); ``result`` /
+    ``result_host`` raise on it.  The process group is used once, at construction, to swap the 64-byte IPC handles.
+    Every rank must launch the same sequence of steps and modes.  Not capturable into a CUDA graph."""
+
+    def __init__(self, step=None, group=None, ctx=None, device=None):
+        """``step``: the MpcDeviceStep whose launches carry the exchange (``launch``); for the host-pointer step (``mpc_sample_step(p2p=...)``) alone,
+        a ``ctx`` (and ``device``) is enough."""
         import ctypes as C
 
         import torch
         import torch.distributed as dist
         self.step, self.torch = step, torch
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
-        if step.n != 1:
+        if step is not None and step.n != 1:
             raise ValueError("the fused exchange handles one problem per launch")
-        ctx = step.ctx
+        ctx = step.ctx if step is not None else ctx
+        if ctx is None:
+            raise ValueError("P2PWinnerExchange needs a step or a ctx")
+        self.dev = step.dev if step is not None else torch.device("cuda", ctx.device if device is None else device)
         self.ctx = ctx
         h = C.c_void_p()
         handle = (C.c_ubyte * 64)()
         ctx.check(ctx.lib.cat_p2p_create(ctx.handle, self.rank, self.world, C.byref(h), handle))
         self.handle = h
-        hdev = step.dev if dist.get_backend(group) == "nccl" else torch.device("cpu")   # gloo: host tensors
+        hdev = self.dev if dist.get_backend(group) == "nccl" else torch.device("cpu")   # gloo: host tensors
         mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=hdev)
         parts = [torch.empty(64, dtype=torch.uint8, device=hdev) for _ in range(self.world)]
         dist.all_gather(parts, mine, group=group)
@@ -159,29 +176,55 @@ class P2PWinnerExchange:
         rc = ctx.lib.cat_p2p_connect(self.handle, buf)
         dist.barrier(group)                                 # every rank has mapped every buffer before step 1
         ctx.check(rc)
-        self._fn = ctx.lib.cat_mpc_step_p2p_dev_f64 if step.dtype == np.float64 else ctx.lib.cat_mpc_step_p2p_dev_f32
+        self._mode = _P2P_LOCKSTEP
 
-    def launch(self, winner=None, to_host=False):
+    def _set_mode(self, mode):
+        if mode != self._mode:
+            self.ctx.check(self.ctx.lib.cat_p2p_set_mode(self.handle, mode))
+            self._mode = mode
+
+    def launch(self, winner=None, to_host=False, pipelined=False):
         """Enqueue one step on torch's current stream; ``winner`` (int64[2] device) receives [cost bits, idx];
-        ``to_host`` writes it into the step's device-mapped host buffer instead (``step.result_host()``)."""
+        ``to_host`` writes it into the step's device-mapped host buffer instead (``step.result_host()``).
+        ``pipelined``: the buffer receives the job-wide winner of the PREVIOUS step (see the class docstring)."""
         import ctypes as C
         st = self.step
         wp = st.host_winner().ctypes.data if to_host else (st.winner if winner is None else winner).data_ptr()
+        self._set_mode(_P2P_PIPELINED if pipelined else _P2P_LOCKSTEP)
         self.ctx.set_stream(self.torch.cuda.current_stream(st.dev).cuda_stream)
-        self.ctx.check(self._fn(self.ctx.handle, self.handle, C.byref(st.params), st.problems.data_ptr(),
+        self.ctx.lib.cat_set_workspace(self.ctx.handle, st._ws)
+        fn = self.ctx.lib.cat_mpc_step_p2p_dev_f64 if st.dtype == np.float64 else self.ctx.lib.cat_mpc_step_p2p_dev_f32
+        self.ctx.check(fn(self.ctx.handle, self.handle, C.byref(st.params), st.problems.data_ptr(),
                                 None if st.controls is None else st.controls.data_ptr(), st.p_ref.data_ptr(),
                                 wp, wp + 8, None if st.costs is None else st.costs.data_ptr()))
 
+    def flush(self, winner=None):
+        """Enqueue the fold of the most recent step's winners (closes a run of pipelined steps)."""
+        st = self.step
+        wp = (st.winner if winner is None else winner).data_ptr()
+        self.ctx.set_stream(self.torch.cuda.current_stream(st.dev).cuda_stream)
+        self.ctx.check(self.ctx.lib.cat_p2p_flush_dev(self.ctx.handle, self.handle, wp, wp + 8))
+
+    def check_winner(self, idx):
+        """The in-kernel exchange reports a missing peer through the value itself: (NaN, -1)."""
+        if idx < 0:
+            self.timed_out()                                # synchronises and clears the device flag
+            raise RuntimeError("fused winner exchange: a peer's winner did not arrive (rank stalled or gone); "
+                               "the ranks are no longer in step")
+
     def result_host(self):
         i, c = self.step.result_host()
+        self.check_winner(int(i[0]))
         return int(i[0]), float(c[0])
 
     def result(self, winner=None):
         """(best_idx, best_cost) of the whole job (blocks on the stream)."""
         w = (self.step.winner if winner is None else winner).cpu().numpy()
+        self.check_winner(int(w[1]))
         return int(w[1]), float(w[:1].view(np.float64)[0])
 
     def timed_out(self):
+        """True if any step since the last call gave up waiting for a peer (clears the flag)."""
         import ctypes as C
         v = C.c_int()
         self.ctx.check(self.ctx.lib.cat_p2p_status(self.handle, C.byref(v)))

@@ -88,13 +88,33 @@ def _programs(params):
     return prog(te), prog(ge)
 
 
+def _wire_controls(controls, dtype, controls_dtype):
+    """(array handed to the library, extra flags).  The rollout arithmetic is ``dtype``; the candidates may be stored
+    -- and cross PCIe -- as float32 while the arithmetic stays fp64 (``controls_dtype=np.float32``, or simply a
+    float32 array): half the bytes of the PCIe-bound host step, and exact parity as long as the oracle is given the
+    same rounded values."""
+    dtype = np.dtype(dtype)
+    if controls_dtype is None:
+        controls_dtype = np.float32 if (dtype == np.float64 and getattr(controls, "dtype", None) == np.float32) else dtype
+    controls_dtype = np.dtype(controls_dtype)
+    if dtype == np.float32:
+        controls_dtype = dtype
+    if controls_dtype not in (np.dtype(np.float32), np.dtype(np.float64)):
+        raise ValueError("controls_dtype must be float32 or float64")
+    U = np.ascontiguousarray(controls, controls_dtype)
+    return U, (_lib.MPC_CONTROLS_F32 if (dtype == np.float64 and controls_dtype == np.float32) else 0)
+
+
 def mpc_sample_step(params, controls, p_ref, *, layout="KH3", return_costs=True, dtype=np.float64, seed=0,
-                    sigma=None, clip=3.0, K=None, k_offset=0, ctx=None):
+                    sigma=None, clip=3.0, K=None, k_offset=0, ctx=None, controls_dtype=None, p2p=None):
     """One sampling-MPC step -> (best_idx, best_cost, costs | None).
 
     controls: (K,H,3) [layout 'KH3', the oracle's] or (H,3,K) [layout 'H3K', the kernel's coalesced SoA]
-    commanded V1 in mm/s; or None with ``sigma`` (3,) and ``K`` to sample on the device (Philox4x32-10
-    keyed by (seed, problem, k, h)).  p_ref (H,3) in m.  best_idx is the first minimum (np.argmin order)."""
+    commanded V1 in mm/s; or None with ``sigma`` (3,) and ``K`` to sample on the device (Philox4x32-10 and the
+    tabulated inverse normal CDF, keyed by (seed, problem, k, h)).  p_ref (H,3) in m.  best_idx: lowest cost, ties
+    -> lowest index, NaN costs rank last.  ``controls_dtype=np.float32`` (or a float32 array) stores the candidates
+    as float under fp64 arithmetic.  ``p2p``: a distributed.P2PWinnerExchange -- this rank's shard goes in, the
+    JOB-WIDE winner comes out on every rank (exchanged inside the kernel over NVLink)."""
     ctx = ctx or default_context()
     dtype = np.dtype(dtype)
     p_ref = np.ascontiguousarray(p_ref, np.float64)
@@ -106,7 +126,10 @@ def mpc_sample_step(params, controls, p_ref, *, layout="KH3", return_costs=True,
         flags |= _lib.MPC_RNG_CONTROLS
         U = None
     else:
-        U = np.ascontiguousarray(controls, dtype)
+        U, wire = _wire_controls(controls, dtype, controls_dtype)
+        flags |= wire
+        if U is controls:                                # the caller's own array (no conversion copy): page-lock it once
+            ctx.maybe_register(U)
         if layout == "KH3":
             if U.ndim != 3 or U.shape[1:] != (H, 3):
                 raise ValueError(f"controls must be (K,{H},3)")
@@ -124,6 +147,8 @@ def mpc_sample_step(params, controls, p_ref, *, layout="KH3", return_costs=True,
     best_idx = np.empty(1, np.int64)
     costs = np.empty(K, dtype) if return_costs else None
     progs = _programs(params)
+    if progs is not None and p2p is not None:
+        raise ValueError("run-time equation programs and the fused exchange are not combined in one call")
     if progs is not None:
         # run-time equation programs (a retrained model's equation strings) instead of the generated code
         pt, pg = progs
@@ -132,6 +157,12 @@ def mpc_sample_step(params, controls, p_ref, *, layout="KH3", return_costs=True,
                      len(pt.ops), _lib.ptr(pt.ops), len(pt.consts), _lib.ptr(pt.consts) if len(pt.consts) else None,
                      len(pg.ops), _lib.ptr(pg.ops), len(pg.consts), _lib.ptr(pg.consts) if len(pg.consts) else None,
                      _lib.ptr(best_cost), _lib.ptr(best_idx), _lib.ptr(costs)))
+        return int(best_idx[0]), float(best_cost[0]), costs
+    if p2p is not None:
+        fn = ctx.lib.cat_mpc_step_p2p_f64 if dtype == np.float64 else ctx.lib.cat_mpc_step_p2p_f32
+        ctx.check(fn(ctx.handle, p2p.handle, C.byref(s), _lib.ptr(pr), _lib.ptr(U), _lib.ptr(p_ref),
+                     _lib.ptr(best_cost), _lib.ptr(best_idx), _lib.ptr(costs)))
+        p2p.check_winner(int(best_idx[0]))
         return int(best_idx[0]), float(best_cost[0]), costs
     fn = ctx.lib.cat_mpc_step_f64 if dtype == np.float64 else ctx.lib.cat_mpc_step_f32
     ctx.check(fn(ctx.handle, C.byref(s), _lib.ptr(pr), _lib.ptr(U), _lib.ptr(p_ref), _lib.ptr(best_cost),
@@ -163,7 +194,7 @@ def mpc_fleet_step(params, problems, p_ref, K, sigma, *, seed=0, clip=3.0, probl
 
 
 def reduce_winners(costs, idxs):
-    """Deterministic fold of per-shard winners (lowest cost, ties -> lowest global index, NaN wins)."""
+    """Deterministic fold of per-shard winners (lowest cost, ties -> lowest global index, NaN ranks last)."""
     lib = _lib.load()
     c = np.ascontiguousarray(costs, np.float64)
     i = np.ascontiguousarray(idxs, np.int64)

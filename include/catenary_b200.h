@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define CAT_ABI_VERSION 2
+#define CAT_ABI_VERSION 3
 
 #if defined(CAT_BUILD_SHARED) && defined(__GNUC__)
 #define CAT_API __attribute__((visibility("default")))
@@ -55,8 +55,20 @@ enum {
 
 /* flags of CatMpcParams */
 enum {
-  CAT_MPC_RNG_CONTROLS = 1,  /* controls == NULL: sample on device (Philox4x32-10) */
-  CAT_MPC_CONTROLS_AOS = 2   /* controls are [n_problems][K][H][3] (the oracle's (K,H,3)) instead of SoA */
+  CAT_MPC_RNG_CONTROLS = 1,  /* controls == NULL: sample on device (Philox4x32-10 + tabulated inverse normal CDF) */
+  CAT_MPC_CONTROLS_AOS = 2,  /* controls are [n_problems][K][H][3] (the oracle's (K,H,3)) instead of SoA */
+  CAT_MPC_CONTROLS_F32 = 4   /* *_f64 entry points only: the controls buffer holds float, not double (the pointer
+                                argument is reinterpreted).  Arithmetic stays fp64; the candidates cross PCIe and HBM
+                                at half the bytes.  A float rollout (*_f32) always reads float controls. */
+};
+
+/* modes of the fused multi-GPU winner exchange (cat_p2p_set_mode) */
+enum {
+  CAT_P2P_MODE_LOCKSTEP = 0, /* a step returns the job-wide winner of ITSELF: its kernel ends when every rank's
+                                winner has arrived (the latency path) */
+  CAT_P2P_MODE_PIPELINED = 1 /* a step returns the job-wide winner of the PREVIOUS step and never waits for a peer
+                                that is less than a whole step behind (the throughput path); cat_p2p_flush_dev
+                                delivers the winner of the last step */
 };
 
 /* receding-horizon controller: how the next nominal sequence is formed */
@@ -113,6 +125,25 @@ CAT_API int cat_set_stream(void* ctx, void* cuda_stream, int own);
 /* pinned host memory for the un-suffixed (host-pointer) entry points */
 CAT_API int cat_host_alloc(void* ctx, size_t bytes, void** out);
 CAT_API int cat_host_free(void* ctx, void* p);
+/* page-lock a CALLER-owned host range (an ordinary NumPy array) so that the host-pointer entry points copy it at
+ * PCIe speed instead of through the driver's pageable staging path; the caller unregisters before freeing the
+ * memory (the Python layer ties it to the array's lifetime).  At most 64 ranges per ctx. */
+CAT_API int cat_host_register(void* ctx, void* p, size_t bytes);
+CAT_API int cat_host_unregister(void* ctx, void* p);
+/* Private per-block winner slots + tickets for the *_dev MPC entry points.  The default (ws == NULL) is scratch
+ * shared by every call on the ctx, which is only safe when launches of one ctx never overlap; a caller that
+ * pipelines steps over several streams, or captures a step into a CUDA graph, creates one workspace per in-flight
+ * step and selects it with cat_set_workspace before the launch (like cat_set_stream).  Sized for max_candidates x
+ * max_problems of one launch. */
+CAT_API int cat_mpc_workspace_create(void* ctx, int64_t max_candidates, int32_t max_problems, void** ws);
+CAT_API int cat_mpc_workspace_destroy(void* ctx, void* ws);
+CAT_API int cat_set_workspace(void* ctx, void* ws_or_null);
+/* cold-path counters of the rollout kernel (bench.py "sensitivity"): enable != 0 switches counting on, 0 off;
+ * out (may be NULL) receives, summed over every rollout launched by this process since the last reset:
+ * [0] warp-level entries into the catenary solve's iteration loop (the warm Halley step did not suffice),
+ * [1] warp-level entries into the full-range sine (|x| >= 1e5, inf, NaN), [2], [3] reserved.  reset != 0 zeroes
+ * them after reading.  Synchronises the device. */
+CAT_API int cat_mpc_stats(void* ctx, int enable, int reset, uint64_t* out);
 /* device event timing on the ctx stream (bench.py; torch.cuda.Event only sees torch's stream) */
 CAT_API int cat_timer_start(void* ctx);
 CAT_API int cat_timer_stop_ms(void* ctx, float* ms);   /* records, synchronises, returns elapsed */
@@ -191,8 +222,8 @@ CAT_API int cat_features_f64(void* ctx, int64_t T, const double* P0, const doubl
 /* ---- fused closed-loop sampling-MPC step (new composition) --------
  * problems: n_problems structs.  controls: [n_problems][H][3][K] (SoA over candidates, mm/s) or
  * NULL with CAT_MPC_RNG_CONTROLS.  p_ref: [n_problems][H][3] (m).
- * best_cost / best_idx: n_problems values (best_idx is GLOBAL: k_offset + local index, first
- * minimum, NaN wins like np.argmin).  costs: [n_problems][K] or NULL. */
+ * best_cost / best_idx: n_problems values (best_idx is GLOBAL: k_offset + local index; lowest cost, ties -> lowest
+ * index, a NaN cost ranks with +inf so that a failed rollout is never selected).  costs: [n_problems][K] or NULL. */
 CAT_API int cat_mpc_step_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
                      const double* controls, const double* p_ref,
                      double* best_cost, int64_t* best_idx, double* costs);
@@ -209,7 +240,7 @@ CAT_API int cat_mpc_step_dev_f32(void* ctx, const CatMpcParams* p, const CatMpcP
 /* materialise the on-device RNG controls ([n_problems][H][3][K], device pointer) */
 CAT_API int cat_sample_controls_dev_f64(void* ctx, const CatMpcParams* p, double* controls);
 /* deterministic reduce of per-shard winners gathered from G ranks (cost[g], idx[g]):
- * lowest cost, ties -> lowest global index, NaN wins.  Host arrays. */
+ * lowest cost, ties -> lowest global index, NaN ranks with +inf.  Host arrays. */
 CAT_API int cat_reduce_winners_f64(int n, const double* cost, const int64_t* idx,
                            double* best_cost, int64_t* best_idx);
 
@@ -295,8 +326,8 @@ CAT_API int cat_mpc_step_expr_f32(void* ctx, const CatMpcParams* p, const CatMpc
  * rollout's last block writes this rank's (cost, global idx) into every peer's buffer, waits for the peers'
  * winners of the same step and folds them in rank order, so best_cost / best_idx (device pointers, one value
  * each) hold the JOB-WIDE winner on every rank when the kernel ends -- no NCCL call, no second launch.  Every
- * rank must launch the same sequence of steps; n_problems must be 1.  cat_p2p_status synchronises and reports
- * whether any step gave up waiting for a peer (~seconds). */
+ * rank must launch the same sequence of steps; n_problems must be 1.  A peer that does not show up within a few
+ * seconds makes the step return the sentinel best_cost = NaN, best_idx = -1 (never a fold over stale slots). */
 CAT_API int cat_p2p_create(void* ctx, int rank, int n_ranks, void** p2p, void* handle_out /* 64 bytes */);
 CAT_API int cat_p2p_connect(void* p2p, const void* all_handles /* n_ranks x 64 bytes, rank order */);
 CAT_API int cat_mpc_step_p2p_dev_f64(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
@@ -305,6 +336,23 @@ CAT_API int cat_mpc_step_p2p_dev_f64(void* ctx, void* p2p, const CatMpcParams* p
 CAT_API int cat_mpc_step_p2p_dev_f32(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
                                      const float* controls, const double* p_ref, double* best_cost,
                                      int64_t* best_idx, float* costs);
+/* host-pointer form of the same step (SURVEY.md 8b "cat_mpc_step_multi"): every rank passes its shard as host
+ * arrays exactly as to cat_mpc_step_*, the library copies, rolls out, exchanges inside the kernel (lock-step) and
+ * returns the JOB-WIDE winner in best_cost / best_idx on every rank.  n_problems must be 1. */
+CAT_API int cat_mpc_step_p2p_f64(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
+                                 const double* controls, const double* p_ref, double* best_cost,
+                                 int64_t* best_idx, double* costs);
+CAT_API int cat_mpc_step_p2p_f32(void* ctx, void* p2p, const CatMpcParams* p, const CatMpcProblem* problems,
+                                 const float* controls, const double* p_ref, double* best_cost,
+                                 int64_t* best_idx, float* costs);
+/* CAT_P2P_MODE_*; every rank must switch at the same step.  Not capturable into a CUDA graph (the step number is
+ * a kernel argument). */
+CAT_API int cat_p2p_set_mode(void* p2p, int mode);
+/* job-wide winner of the most recent step (device pointers, one value each), without launching a rollout: the
+ * closing call of a run of pipelined steps */
+CAT_API int cat_p2p_flush_dev(void* ctx, void* p2p, double* best_cost, int64_t* best_idx);
+/* synchronises, reports whether any step since the last call gave up waiting for a peer (such a step returns the
+ * sentinel best_cost = NaN, best_idx = -1), and clears the flag */
 CAT_API int cat_p2p_status(void* p2p, int* timed_out);
 CAT_API int cat_p2p_destroy(void* p2p);
 

@@ -105,6 +105,29 @@ def transform_catenary(point_A, point_B, catenary_fn, theta_rad, gamma_rad):
     return original, theta_rotated, theta_aligned, final
 
 
+def transform_catenary_batch(A, B, L, theta, gamma, n_pts=None):
+    """transform_catenary (main_fun.py:38-111) with the stand-in Catenary, vectorised over n configurations:
+    A, B (n,3); L, theta, gamma (n,) -> (original, theta_rotated, theta_aligned, final) each (n, n_pts, 3),
+    C (n,) of the span A->B, valid (n,) bit 0: span A->B in the solve domain, bit 1: span A->B'.
+    Same operations as the per-configuration function; a span outside the domain holds the straight chord
+    sampled at n_pts points (its first and last samples are the [start, end] of main_fun.py:67-69)."""
+    n_pts = N_PTS if n_pts is None else n_pts
+    A = np.asarray(A, np.float64)
+    B = np.asarray(B, np.float64)
+    L = np.broadcast_to(np.asarray(L, np.float64), A.shape[:1])
+    th = np.asarray(theta, np.float64)
+    ga = np.asarray(gamma, np.float64)
+    C0, v0, original = catenary_points(A, B, L, n_pts)
+    conn = B - A
+    k_theta = theta_axis_of(conn)
+    rotated_B = A + rodrigues_rotation(conn, k_theta, th)
+    _, v1, theta_rotated = catenary_points(A, rotated_B, L, n_pts)
+    aligned = A[:, None] + rodrigues_rotation(theta_rotated - A[:, None], k_theta[:, None], -th[:, None])
+    k_gamma = conn / np.linalg.norm(conn, axis=-1, keepdims=True)
+    final = A[:, None] + rodrigues_rotation(aligned - A[:, None], k_gamma[:, None], ga[:, None])
+    return (original, theta_rotated, aligned, final), C0, v0.astype(np.uint8) | (v1.astype(np.uint8) << 1)
+
+
 # --------------------------------------------------------------------------
 # catenary parameter: main_fun.py:418-431
 # --------------------------------------------------------------------------
@@ -586,15 +609,25 @@ def mpc_rollout_costs(params, controls, p_ref, return_traj=False):
 
 
 def argmin_first(costs):
-    """np.argmin semantics (fully_augmented_catenary.py:21): first minimum; first nan wins."""
+    """np.argmin semantics (fully_augmented_catenary.py:21, the curve's lowest sample): first minimum; first nan
+    wins.  The MPC winner uses argmin_mpc."""
     costs = np.asarray(costs)
     i = int(np.argmin(costs))
     return i, float(costs[i])
 
 
+def argmin_mpc(costs):
+    """Winner of a sampling-MPC step (builder-defined): lowest cost, ties -> lowest index, and a NaN cost ranks
+    with +inf -- a candidate whose rollout failed must never be applied to the plant.  With every cost NaN the
+    lowest index wins (candidate 0 = the noise-free nominal sequence in the controller).  Returns (idx, cost)."""
+    costs = np.asarray(costs, np.float64)
+    i = int(np.argmin(np.where(np.isnan(costs), np.inf, costs)))
+    return i, float(costs[i])
+
+
 def mpc_sample_step(params, controls, p_ref):
     J = mpc_rollout_costs(params, controls, p_ref)
-    i, c = argmin_first(J)
+    i, c = argmin_mpc(J)
     return i, c, J
 
 
@@ -626,24 +659,51 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
     return c0, c1, c2, c3
 
 
+_ICDF = None
+
+
+def icdf_table():
+    """artifacts/icdf_table.json (tools/make_icdf_table.py): the piecewise-cubic inverse normal CDF that DEFINES the
+    sampler -- the CUDA kernels compile the same numbers (csrc/gen/icdf_table.cuh)."""
+    global _ICDF
+    if _ICDF is None:
+        with open(os.path.join(os.path.dirname(_MODEL_JSON), "icdf_table.json")) as fh:
+            t = json.load(fh)
+        _ICDF = (int(t["e_lo"]), int(t["sub_bits"]), np.array(t["coef"], np.float64))
+    return _ICDF
+
+
+def icdf_normal(r):
+    """Standard normal from uint32 words: z = sign * y(r'), r' = r if r < 2^31 else ~r (clamped to >= 32),
+    sign = -1 for r < 2^31; y = cubic of the segment (octave e = floor(log2 r'), next five bits) in
+    t = (bits below) / 2^(e-5)."""
+    e_lo, m, coef = icdf_table()
+    r = np.asarray(r, np.uint32)
+    hi = r >= np.uint32(0x80000000)
+    rp = np.where(hi, ~r, r).astype(np.int64)
+    rp = np.maximum(rp, 32)
+    e = np.floor(np.log2(rp.astype(np.float64))).astype(np.int64)      # exact for integers < 2^53
+    w = np.left_shift(np.int64(1), e - m)
+    sub = (rp >> (e - m)) & ((1 << m) - 1)
+    t = (rp & (w - 1)).astype(np.float64) / w.astype(np.float64)
+    c = coef[((e - e_lo) << m) + sub]
+    y = ((c[..., 3] * t + c[..., 2]) * t + c[..., 1]) * t + c[..., 0]
+    return np.where(hi, y, -y)
+
+
 def sample_controls(seed, k_index, H, sigma, clip=3.0, problem=0):
     """controls[k,h,:] = sigma * clip(N(0,1), +-clip) keyed by (seed, problem, global k, h).
 
-    counter = (k_lo, k_hi, h, problem), key = (seed_lo, seed_hi); r0..r3 -> u=(r+0.5)*2^-32;
-    z0,z1 = sqrt(-2 ln u0) * (cos, sin)(2 pi u1); z2 = sqrt(-2 ln u2) * cos(2 pi u3).
+    counter = (k_lo, k_hi, h, problem), key = (seed_lo, seed_hi); Philox words r0, r1, r2 -> axes x, y, z through
+    the tabulated inverse normal CDF (icdf_normal).
     """
     k_index = np.asarray(k_index, np.uint64)
-    K = k_index.shape[0]
     klo = (k_index & np.uint64(0xFFFFFFFF)).astype(np.uint32)[:, None]
     khi = (k_index >> np.uint64(32)).astype(np.uint32)[:, None]
     hh = np.arange(H, dtype=np.uint32)[None, :]
-    r0, r1, r2, r3 = philox4x32_10(klo, khi, hh, np.uint32(problem),
-                                   seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
-    u = [(r.astype(np.float64) + 0.5) * 2.0 ** -32 for r in (r0, r1, r2, r3)]
-    ra = np.sqrt(-2.0 * np.log(u[0]))
-    rb = np.sqrt(-2.0 * np.log(u[2]))
-    z = np.stack([ra * np.cos(2 * np.pi * u[1]), ra * np.sin(2 * np.pi * u[1]),
-                  rb * np.cos(2 * np.pi * u[3])], axis=-1)
+    r0, r1, r2, _ = philox4x32_10(klo, khi, hh, np.uint32(problem),
+                                  seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+    z = np.stack([icdf_normal(r0), icdf_normal(r1), icdf_normal(r2)], axis=-1)
     z = np.clip(z, -clip, clip)
     return z * np.asarray(sigma, np.float64)
 
@@ -686,7 +746,7 @@ def mpc_receding_horizon(params, p_ref_traj, n_steps, K, H, sigma, u_max, seed=0
         U = ctrl_candidates(u_nom, seed, t, K, sigma, u_max, clip, problem)
         win = traj[np.minimum(t + np.arange(H), ref_len - 1)]
         J = mpc_rollout_costs(p, U, win)
-        i, Jb = argmin_first(J)
+        i, Jb = argmin_mpc(J)
         if mode == "mppi" and not np.isnan(Jb):
             w = np.exp(-(J - Jb) / lam)
             w = np.where(np.isnan(J), 0.0, w)

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol(cb):
         assert hasattr(lib, n), f"{n} declared in include/catenary_b200.h but not exported"
     bound = importlib.import_module(PKG + "._lib").SIGNATURES
     assert sorted(bound) == names, "ctypes SIGNATURES and the header disagree"
-    assert lib.cat_abi_version() == 2
+    assert lib.cat_abi_version() == 3
 
 
 def test_struct_layouts_match_header(cb):
@@ -69,8 +69,11 @@ def test_no_cpu_fallback_without_device(cb):
 def test_reduce_winners_order(cb):
     inf, nan = float("inf"), float("nan")
     assert cb.reduce_winners([3.0, 1.0, 1.0, 2.0], [10, 30, 20, 5]) == (20, 1.0)       # tie -> lowest index
-    i, c = cb.reduce_winners([3.0, nan, 1.0], [0, 7, 9])
-    assert i == 7 and math.isnan(c)                                                     # NaN wins (np.argmin)
+    assert cb.reduce_winners([3.0, nan, 1.0], [0, 7, 9]) == (9, 1.0)                   # a NaN cost never wins ...
+    i, c = cb.reduce_winners([nan, inf, nan], [8, 6, 3])
+    assert i == 3 and math.isnan(c)                                                     # ... it ranks with +inf
+    i, c = cb.reduce_winners([nan, nan], [5, 4])
+    assert i == 4 and math.isnan(c)                                                     # all NaN: lowest index
     assert cb.reduce_winners([inf, inf], [4, 2]) == (2, inf)
     rng = np.random.default_rng(0)
     c = rng.integers(0, 5, 64).astype(float)

@@ -1,6 +1,8 @@
 """Fused peer-memory winner exchange on ONE GPU: two ranks (gloo for the handle swap) share
-cuda:0, map each other's slot buffers through CUDA IPC and run the one-kernel step.  The two processes' kernels are
-time-sliced, so this checks the protocol (sequence numbers, parities, rank-order fold), not the latency."""
+cuda:0, map each other's slot buffers through CUDA IPC and run the one-kernel step -- lock-step, pipelined (winner one
+step late + flush), the two interleaved, and the host-pointer entry with device-sampled and with explicit controls.
+The two processes' kernels are time-sliced, so this checks the protocol (sequence numbers, ring slots, rank-order fold),
+not the latency."""
 import json
 import os
 import subprocess
@@ -29,19 +31,47 @@ p = cb.default_mpc_params()
 K_total, H = 6000, 12
 pref = cb.circle_reference(H, p["dt"])
 lo, hi = dmod.shard_range(K_total, rank, world)
-out = {"rank": rank, "winners": []}
+SEEDS = (3, 4, 5, 6, 7, 8, 9)
+out = {"rank": rank, "winners": [], "pipelined": [], "host": [], "host_explicit": None}
 try:
-    for seed in (3, 4, 5, 6, 7):          # five steps: both parities reused, a fresh job each time
-        st = devmod.MpcDeviceStep(p, pref, hi - lo, sigma=sigma, seed=seed, k_offset=lo, device=0)
-        if seed == 3:
-            ex = dmod.P2PWinnerExchange(st)
-        else:
-            ex.step = st
+    steps = [devmod.MpcDeviceStep(p, pref, hi - lo, sigma=sigma, seed=s, k_offset=lo, device=0) for s in SEEDS]
+    ex = dmod.P2PWinnerExchange(steps[0])
+    for st in steps:                      # lock-step: seven steps, every ring slot reused, a fresh job each time
+        ex.step = st
         ex.launch()
         out["winners"].append(list(ex.result()))
+    # pipelined: step s returns the job-wide winner of step s-1; flush() closes the run
+    wbuf = [torch.zeros(2, dtype=torch.int64, device="cuda:0") for _ in SEEDS]
+    for j, st in enumerate(steps):
+        ex.step = st
+        ex.launch(winner=wbuf[j], pipelined=True)
+    last = torch.zeros(2, dtype=torch.int64, device="cuda:0")
+    ex.flush(winner=last)
+    torch.cuda.synchronize()
+    first = wbuf[0].cpu().numpy()
+    out["pipelined_first_is_sentinel"] = bool(first[1] == -1)
+    for j in range(1, len(SEEDS)):
+        out["pipelined"].append(list(ex.result(winner=wbuf[j])))
+    out["pipelined"].append(list(ex.result(winner=last)))
+    # modes interleaved, then the host-pointer entry (NumPy in, job-wide winner out)
+    ex.step = steps[0]
+    ex.launch()
+    out["after_mix"] = list(ex.result())
+    for s in SEEDS[:3]:
+        bi, bc, _ = cb.mpc_sample_step(p, None, pref, K=hi - lo, sigma=sigma, seed=s, k_offset=lo,
+                                       return_costs=False, ctx=steps[0].ctx, p2p=ex)
+        out["host"].append([bi, bc])
+    # explicit controls through the chunked host pipeline + the one-block exchange kernel
+    Kx = 80_000
+    xlo, xhi = dmod.shard_range(Kx, rank, world)
+    Ux = (np.clip(np.random.default_rng(99).normal(size=(Kx, H, 3)), -3, 3) * np.asarray(sigma))[xlo:xhi]
+    bi, bc, _ = cb.mpc_sample_step(p, Ux.astype(np.float32), pref, k_offset=xlo, return_costs=False,
+                                   ctx=steps[0].ctx, p2p=ex)
+    out["host_explicit"] = [bi, bc]
     out["timed_out"] = ex.timed_out()
 except Exception as e:                    # IPC refused in this environment, ...
-    out["error"] = repr(e)
+    import traceback
+    out["error"] = repr(e) + traceback.format_exc()[-600:]
 print("RESULT " + json.dumps(out), flush=True)
 dist.barrier()
 """
@@ -72,6 +102,19 @@ def test_fused_exchange_two_ranks_one_gpu(cb, tmp_path):
     sigma = np.array(orc.load_model()["scaler_scale"][3:6])
     p = orc.default_mpc_params()
     pref = orc.circle_reference(12, p["dt"])
-    for seed, (bi, bc) in zip((3, 4, 5, 6, 7), outs[0]["winners"]):
+    seeds = (3, 4, 5, 6, 7, 8, 9)
+    for seed, (bi, bc) in zip(seeds, outs[0]["winners"]):
         J = orc.mpc_rollout_costs(p, orc.sample_controls(seed, np.arange(6000), 12, sigma), pref)
         assert bi == int(np.argmin(J)) and abs(bc - J.min()) <= 1e-9 * J.min()
+    for o in outs:
+        # pipelined steps deliver the same winners one step late; the first one has no predecessor
+        assert o["pipelined_first_is_sentinel"]
+        assert o["pipelined"] == outs[0]["winners"]
+        assert o["after_mix"] == outs[0]["winners"][0]
+        assert o["host"] == outs[0]["winners"][:3]
+    # explicit float32-stored controls through the host entry: job-wide winner of the 80,000-candidate job
+    Ux = np.clip(np.random.default_rng(99).normal(size=(80_000, 12, 3)), -3, 3) * sigma
+    Jx = orc.mpc_rollout_costs(p, Ux.astype(np.float32).astype(np.float64), pref)
+    for o in outs:
+        assert o["host_explicit"][0] == int(np.argmin(Jx))
+        assert abs(o["host_explicit"][1] - Jx.min()) <= 1e-9 * Jx.min()
