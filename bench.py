@@ -762,6 +762,11 @@ def single_gpu_legs(torch, cb, devmod, ctx, step, p, pref, sigma, host_sets, hos
     t0 = time.perf_counter()
     (fin,), Ch, vh = cb.catenary_shapes(A2, B2, 3.0, th2, ga2, ctx=ctx)
     e2e2 = time.perf_counter() - t0
+    pin_out = ctx.pinned_empty((1, n2, 100, 3))
+    cb.catenary_shapes(A2, B2, 3.0, th2, ga2, ctx=ctx, out=pin_out)
+    t0 = time.perf_counter()
+    cb.catenary_shapes(A2, B2, 3.0, th2, ga2, ctx=ctx, out=pin_out)
+    e2e2p = time.perf_counter() - t0
     tr2 = _load_json("profiles", "traffic.json").get("k_shape_f64_config2", {}).get("dram_bytes_per_launch")
     ach2 = n2 * BYTES_PER_SHAPE_CONFIG / (s_ms * 1e-3) / 1e9
     out["configs_single_gpu"] = {"config2": {
@@ -775,8 +780,10 @@ def single_gpu_legs(torch, cb, devmod, ctx, step, p, pref, sigma, host_sets, hos
                 "d2h_bytes": int(fin.nbytes + Ch.nbytes + vh.nbytes),
                 "d2h_gbs": (fin.nbytes + Ch.nbytes + vh.nbytes) / e2e2 / 1e9,
                 "what": "catenary_shapes(A, B, 3.0, theta, gamma) on NumPy arrays: chunked two-lane H2D / kernel / D2H "
-                        "pipeline into a freshly allocated (n, 100, 3) result"}}}
-    del fin, Ch, vh, out_h
+                        "pipeline into a freshly allocated (n, 100, 3) result (page faults + pageable D2H)",
+                "into_pinned_out": {"ms": e2e2p * 1e3, "configs_per_s": n2 / e2e2p, "d2h_gbs": fin.nbytes / e2e2p / 1e9,
+                                    "what": "the same call writing into a reused page-locked buffer (out=ctx.pinned_empty)"}}}}
+    del fin, Ch, vh, out_h, pin_out
 
     # ---- closed loop: the receding-horizon controller (device-resident, one CUDA graph per control step) ----
     closed = {}

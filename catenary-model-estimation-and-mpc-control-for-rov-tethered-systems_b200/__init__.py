@@ -15,7 +15,9 @@ from .mpc import (circle_reference, default_mpc_params, make_params, make_proble
 from .controller import RecedingHorizonController, mpc_receding_horizon
 from .expr import (ExpressionError, ExpressionModel, compile_expression, integrate_second_order, load_equation_table,
                    load_run)
-from .features import (build_clean_features, build_gamma_features, build_theta_features, extract_features16,
-                       feature_bank, load_and_resample_all, load_trajectory_csv, resample_linear, uniform_resample)
+from .features import (build_clean_features, build_gamma_features, build_gamma_features_valid,
+                       build_theta_features, build_theta_features_valid, compute_derivatives, extract_features16,
+                       feature_bank, features_dd, gaussian_filter1d, gradient, load_and_resample_all,
+                       load_trajectory_csv, preprocess_signals, resample_linear, savgol_filter, uniform_resample)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

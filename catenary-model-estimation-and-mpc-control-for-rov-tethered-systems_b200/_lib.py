@@ -99,6 +99,11 @@ SIGNATURES = {
     "cat_catenary_equation_f64": (_int, [_vp, _i64, _vp, _vp, _i64, _vp]),
     "cat_resample_linear_f64": (_int, [_vp, _i64, _vp, _i32, _vp, _i64, _vp, _vp]),
     "cat_feature_bank_f64": (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, C.c_double, C.c_double, _vp]),
+    "cat_fir_reflect_f64": (_int, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),
+    "cat_savgol_f64": (_int, [_vp, _i64, _i64, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "cat_gradient_f64": (_int, [_vp, _i64, _i64, _vp, _vp, _i32, _vp]),
+    "cat_features_valid_f64": (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _i32, _i32, _vp]),
+    "cat_features_dd_f64": (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp]),
     "cat_expr_eval_f64": (_int, [_vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "cat_expr_eval_f32": (_int, [_vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "cat_expr_integrate_f64": (_int, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp]),

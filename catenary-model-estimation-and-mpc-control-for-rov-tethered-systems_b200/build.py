@@ -43,40 +43,46 @@ def _newest_dep(src):
     return max(os.path.getmtime(d) for d in deps if os.path.exists(d))
 
 
-def _compile(unit, force, verbose):
+def _compile(unit, force, verbose, objdir=OBJ, extra=()):
     obj, src, defs = unit
-    out = os.path.join(OBJ, obj)
+    out = os.path.join(objdir, obj)
     if not force and os.path.exists(out) and os.path.getmtime(out) >= _newest_dep(src):
         return obj, 0, ""
-    cmd = [_nvcc()] + FLAGS + defs + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", out]
+    cmd = ([_nvcc()] + FLAGS + defs + list(extra) + (["-Xptxas", "-v"] if verbose else []) +
+           ["-c", os.path.join(CSRC, src), "-o", out])
     res = subprocess.run(cmd, capture_output=True, text=True)
     return obj, res.returncode, res.stdout + res.stderr
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, extra=(), lib=LIB, objdir=OBJ):
+    """``extra`` / ``lib`` / ``objdir``: a variant build for A/B timing (tools/ab.sh), e.g.
+    build(extra=["-DCAT_MPC_ASYNC_F64=1"], lib="ab/1_async64.so", objdir="/tmp/obj_async64")."""
     sys.path.insert(0, _HERE)
     try:
         import codegen
     finally:
         sys.path.pop(0)
     codegen.generate()
-    os.makedirs(OBJ, exist_ok=True)
+    os.makedirs(objdir, exist_ok=True)
     from concurrent.futures import ThreadPoolExecutor
     with ThreadPoolExecutor(max_workers=min(len(UNITS), os.cpu_count() or 2)) as pool:
-        results = list(pool.map(lambda u: _compile(u, force, verbose), UNITS))
+        results = list(pool.map(lambda u: _compile(u, force, verbose, objdir, extra), UNITS))
     for obj, rc, log in results:
         if verbose or rc != 0:
             sys.stderr.write(f"--- {obj}\n{log}")
         if rc != 0:
             raise RuntimeError(f"nvcc failed on {obj}:\n" + log[-4000:])
-    objs = [os.path.join(OBJ, u[0]) for u in UNITS]
-    if force or not os.path.exists(LIB) or any(os.path.getmtime(o) > os.path.getmtime(LIB) for o in objs):
-        cmd = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static", "-o", LIB] + objs
+    objs = [os.path.join(objdir, u[0]) for u in UNITS]
+    if force or not os.path.exists(lib) or any(os.path.getmtime(o) > os.path.getmtime(lib) for o in objs):
+        cmd = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static", "-o", lib] + objs
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError("link failed:\n" + (res.stdout + res.stderr)[-4000:])
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    _extra = [a for a in sys.argv[1:] if a.startswith("-D")]
+    _lib = next((a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--lib=")), LIB)
+    _obj = next((a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--objdir=")), OBJ)
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, extra=_extra, lib=_lib, objdir=_obj))

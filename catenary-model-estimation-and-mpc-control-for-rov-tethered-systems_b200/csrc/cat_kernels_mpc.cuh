@@ -87,6 +87,33 @@ __device__ __forceinline__ const CatIcdfSmem<T>& cat_icdf_ref(const typename Cat
   return *reinterpret_cast<const CatIcdfSmem<T>*>(&s);   // never dereferenced when RNG is false
 }
 
+// Asynchronous control prefetch (cp.async, global -> shared, no register in between): thread t owns column t of a
+// ring s[slot][axis][t] and keeps CAT_MPC_PF horizon steps in flight.  A ring held in REGISTERS does not work: the
+// moves that rotate it need the loaded data, so the warp waits on step h+3's load at step h+1 (round-2 ncu of the
+// fp32 kernel: 72% of the long-scoreboard samples on exactly that move, 1.2 stall cycles per issued instruction).
+#ifndef CAT_MPC_ASYNC_F64
+#define CAT_MPC_ASYNC_F64 0   // 1: the fp64 kernels prefetch this way too (A/B switch; fp32 always does)
+#endif
+#define CAT_MPC_PF 4
+template <typename S, bool ON> struct CatRing {
+  S v[(CAT_MPC_PF + 1) * 3 * CAT_MPC_BLOCK];
+};
+template <typename S> struct CatRing<S, false> {
+  char v[1];
+};
+template <typename S>
+__device__ __forceinline__ void cat_cp_async(S* smem_dst, const S* gsrc) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+  if constexpr (sizeof(S) == 4)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gsrc) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cat_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cat_cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // candidate control of the receding-horizon controller: clamp(u_nom[h] + sigma*clip(N(0,1)), +-u_max);
 // global candidate 0 carries no noise (oracle ctrl_candidates)
 template <typename T, typename M>
@@ -321,6 +348,8 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   // inverse-CDF table of the device sampler (hot octaves), staged once per block
   __shared__ typename CatIcdfSlot<T, RNG>::type s_icdf;
   if constexpr (RNG) cat_icdf_stage<T>(s_icdf);
+  constexpr bool ASYNC = !RNG && (sizeof(T) == 4 || CAT_MPC_ASYNC_F64 != 0);
+  __shared__ __align__(16) CatRing<S, ASYNC> s_ring;
   CatMpcVm<T> vm;
   if constexpr (VM) {   // stage both programs into shared memory once per block
     extern __shared__ __align__(16) unsigned char cat_mpc_smem[];
@@ -388,23 +417,34 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     carry_g = (CAT_DGAMMA_LIVE_MASK & 0xC000u) == 0;
   }
 
-  // Controls are fetched PF steps ahead and the reference point one step ahead, so the load latency hides behind
-  // arithmetic.  One step of fp64 arithmetic (~3,000 cycles at 3.5 warps per scheduler) covers an HBM miss; one
-  // step of the fp32 kernel (~1,900 cycles, with the loads issued ~40% into the step) did NOT (~1,000 cycles of
-  // DRAM latency at the natural clock): round-1 ncu showed 3.2 long-scoreboard stall cycles per issued
-  // instruction there.  The fp32 kernel therefore keeps a ring of three steps in registers.
-  constexpr int PF = (!RNG && sizeof(T) == 4) ? 3 : 1;
-  S Vq[PF][3];
+  // Controls are fetched ahead of their use and the reference point one step ahead, so the load latency hides behind
+  // arithmetic.  One step of fp64 arithmetic (~3,000 cycles at 3.5 warps per scheduler) covers an HBM miss, so the
+  // fp64 kernels load the next step's controls into registers.  One step of the fp32 kernel (~1,900 cycles, loads
+  // issued ~40% into the step) does NOT (~1,000 cycles of DRAM latency at the natural clock; round-1 ncu: 3.2
+  // long-scoreboard stall cycles per issued instruction): it keeps CAT_MPC_PF steps in flight through cp.async.
+  S Vq[3] = {S(0), S(0), S(0)};
   T Rnext[3];
-  if constexpr (!RNG) {
+  int slot = 0;          // ASYNC: ring slot of step h
+  int slot_in = 0;       // ASYNC: ring slot the next prefetch lands in
+  if constexpr (ASYNC) {
+    S* const mine = reinterpret_cast<S*>(s_ring.v) + threadIdx.x;
 #pragma unroll
-    for (int i = 0; i < PF; ++i) {
-      const S* u = uc + (long long)(i < q.H ? i : q.H - 1) * q.sh;
-      Vq[i][0] = u[0];
-      Vq[i][1] = u[q.sa];
-      Vq[i][2] = u[2 * q.sa];
+    for (int i = 0; i < CAT_MPC_PF; ++i) {
+      if (i < q.H) {
+        S* d = mine + (i * 3) * CAT_MPC_BLOCK;
+        cat_cp_async<S>(d, uc);
+        cat_cp_async<S>(d + CAT_MPC_BLOCK, uc + q.sa);
+        cat_cp_async<S>(d + 2 * CAT_MPC_BLOCK, uc + 2 * q.sa);
+        uc += q.sh;
+      }
+      cat_cp_async_commit();   // one group per step, empty or not: the wait below counts groups
     }
-    uc += (long long)PF * q.sh;   // the row of step h + PF at the top of step h; dereferenced only below H
+    slot_in = CAT_MPC_PF;
+  } else if constexpr (!RNG) {
+    Vq[0] = uc[0];
+    Vq[1] = uc[q.sa];
+    Vq[2] = uc[2 * q.sa];
+    uc += q.sh;
   }
   Rnext[0] = T(pr[0]);
   Rnext[1] = T(pr[1]);
@@ -418,16 +458,18 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       else
         cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
                                  (uint32_t)h, q.sigma, q.clip, cat_icdf_ref<T, RNG>(s_icdf), Vn);
+    } else if constexpr (ASYNC) {
+      // the group of step h is the oldest of the CAT_MPC_PF in flight
+      cat_cp_async_wait<CAT_MPC_PF - 1>();
+      const S* mine = reinterpret_cast<const S*>(s_ring.v) + threadIdx.x + (slot * 3) * CAT_MPC_BLOCK;
+      Vn[0] = T(mine[0]);
+      Vn[1] = T(mine[CAT_MPC_BLOCK]);
+      Vn[2] = T(mine[2 * CAT_MPC_BLOCK]);
+      slot = slot == CAT_MPC_PF ? 0 : slot + 1;
     } else {
-      Vn[0] = T(Vq[0][0]);
-      Vn[1] = T(Vq[0][1]);
-      Vn[2] = T(Vq[0][2]);
-#pragma unroll
-      for (int i = 0; i + 1 < PF; ++i) {
-        Vq[i][0] = Vq[i + 1][0];
-        Vq[i][1] = Vq[i + 1][1];
-        Vq[i][2] = Vq[i + 1][2];
-      }
+      Vn[0] = T(Vq[0]);
+      Vn[1] = T(Vq[1]);
+      Vn[2] = T(Vq[2]);
     }
     const T Rh[3] = {Rnext[0], Rnext[1], Rnext[2]};
     if constexpr (RNG) {
@@ -438,25 +480,28 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       Rnext[0] = T(pr[0]);
       Rnext[1] = T(pr[1]);
       Rnext[2] = T(pr[2]);
-    } else if constexpr (PF == 1) {
-      if (h + 1 < q.H) {   // one branch for both fetches (the form the fp64 kernel was tuned with)
-        Vq[0][0] = uc[0];
-        Vq[0][1] = uc[q.sa];
-        Vq[0][2] = uc[2 * q.sa];
+    } else if constexpr (ASYNC) {
+      if (h + CAT_MPC_PF < q.H) {   // step h + PF into the slot that was read PF + 1 steps ago
+        S* d = reinterpret_cast<S*>(s_ring.v) + threadIdx.x + (slot_in * 3) * CAT_MPC_BLOCK;
+        cat_cp_async<S>(d, uc);
+        cat_cp_async<S>(d + CAT_MPC_BLOCK, uc + q.sa);
+        cat_cp_async<S>(d + 2 * CAT_MPC_BLOCK, uc + 2 * q.sa);
         uc += q.sh;
+      }
+      cat_cp_async_commit();
+      slot_in = slot_in == CAT_MPC_PF ? 0 : slot_in + 1;
+      if (h + 1 < q.H) {
         if (h + 1 < ref_rem) pr += 3;
         Rnext[0] = T(pr[0]);
         Rnext[1] = T(pr[1]);
         Rnext[2] = T(pr[2]);
       }
     } else {
-      if (h + PF < q.H) {
-        Vq[PF - 1][0] = uc[0];
-        Vq[PF - 1][1] = uc[q.sa];
-        Vq[PF - 1][2] = uc[2 * q.sa];
+      if (h + 1 < q.H) {   // one branch for both fetches (the form the fp64 kernel was tuned with)
+        Vq[0] = uc[0];
+        Vq[1] = uc[q.sa];
+        Vq[2] = uc[2 * q.sa];
         uc += q.sh;
-      }
-      if (h + 1 < q.H) {
         if (h + 1 < ref_rem) pr += 3;
         Rnext[0] = T(pr[0]);
         Rnext[1] = T(pr[1]);

@@ -761,10 +761,20 @@ __device__ __forceinline__ void cat_icdf_stage(CatIcdfSmem<T>& sm) {
   __syncthreads();
 }
 
+// lanes below the shared-memory octaves when the caller's clip reaches past them: the full table in global memory.
+// Kept out of line so that the common path carries one predicated call, not the predicated-off loads and FMAs
+// (round-2 ncu: ~32 of the sampler's instructions per warp-step were this never-taken block, if-converted).
+template <typename T, typename M>
+__device__ __noinline__ T cat_icdf_deep(int seg, T t) {
+  const double* g = CAT_ICDF_TAB + 4 * seg;
+  return M::fma_(M::fma_(M::fma_(T(__ldg(g + 3)), t, T(__ldg(g + 2))), t, T(__ldg(g + 1))), t, T(__ldg(g)));
+}
+
 // deep: clip > CAT_ICDF_SMEM_ZMAX (warp-uniform)
 template <typename T, typename M>
 __device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& sm, bool deep) {
-  uint32_t rp = (r & 0x80000000u) ? ~r : r;
+  const uint32_t flip = (uint32_t)((int)r >> 31);          // 0xffffffff for r >= 2^31
+  uint32_t rp = r ^ flip;                                   // r' = r < 2^31 ? r : ~r
   rp = rp < 32u ? 32u : rp;
   int seg;
   T t;
@@ -774,7 +784,8 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& s
     const unsigned lo = (unsigned)__double2loint(x);
     seg = (hi >> 15) - ((1023 + CAT_ICDF_E_LO) << 5);
     // mantissa bits below the top five, as 1.t - 1
-    t = __hiloint2double(0x3ff00000 | ((hi & 0x7fff) << 5) | (int)(lo >> 27), (int)(lo << 5)) - 1.0;
+    const unsigned mh = (__funnelshift_l(lo, (unsigned)hi, 5) & 0x000fffffu) | 0x3ff00000u;
+    t = __hiloint2double((int)mh, (int)(lo << 5)) - 1.0;
   } else {
     int b = __float_as_int((float)rp);   // 24-bit rounding moves the sample by < 1e-6 ...
     b = b > 0x4effffff ? 0x4effffff : b;   // ... and must not round up to 2^31, one octave past the table
@@ -792,15 +803,15 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& s
     c0 = a.x; c1 = a.y; c2 = a.z; c3 = a.w;
   }
   T y = M::fma_(M::fma_(M::fma_(c3, t, c2), t, c1), t, c0);
-  if (sseg < 0) {
-    if (deep) {
-      const double* g = CAT_ICDF_TAB + 4 * seg;
-      y = M::fma_(M::fma_(M::fma_(T(g[3]), t, T(g[2])), t, T(g[1])), t, T(g[0]));
-    } else {
-      y = T(4);   // beyond every clip <= CAT_ICDF_SMEM_ZMAX: the caller's clamp decides
-    }
+  if (sseg < 0) y = T(4);   // beyond every clip <= CAT_ICDF_SMEM_ZMAX: the caller's clamp decides
+  if (deep) {               // warp-uniform; false in every BASELINE config
+    if (sseg < 0) y = cat_icdf_deep<T, M>(seg, t);
   }
-  return (r & 0x80000000u) ? y : -y;
+  // z = r >= 2^31 ? y : -y, on the sign bit
+  if constexpr (sizeof(T) == 8)
+    return __hiloint2double(__double2hiint(y) ^ (int)(~flip & 0x80000000u), __double2loint(y));
+  else
+    return __int_as_float(__float_as_int(y) ^ (int)(~flip & 0x80000000u));
 }
 
 // three clipped normals scaled by sigma, keyed by (seed, problem, global k, h): Philox words 0..2 -> axes x, y, z

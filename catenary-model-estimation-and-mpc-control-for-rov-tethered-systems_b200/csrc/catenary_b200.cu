@@ -19,6 +19,7 @@
 #include "cat_mpc_launch.cuh"
 #include "cat_kernels_ctrl.cuh"
 #include "cat_kernels_expr.cuh"
+#include "cat_kernels_feat.cuh"
 
 void cat_nvtx_push(const CatCtx*, const char* name) { nvtxRangePushA(name); }
 void cat_nvtx_pop(const CatCtx*) { nvtxRangePop(); }
@@ -1522,6 +1523,171 @@ int cat_feature_bank_f64(void* ctx, int64_t T, const double* P0, const double* P
                                                                w, kCLo, kCHi, dB);
   LAUNCHED();
   CU(cudaMemcpyAsync(bank, dB, (size_t)T * CAT_BANK_W * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+// ---- smoothed / second-order feature layouts (cat_kernels_feat.cuh) ----------------------------------------
+int cat_fir_reflect_f64(void* ctx, int64_t n_sig, int64_t len, const double* x, int32_t n_taps, const double* taps,
+                        double* out) {
+  CTX();
+  NEED(n_sig >= 0 && len >= 0 && n_taps >= 1 && (n_taps & 1) && n_taps <= 4097 && taps);
+  if (n_sig == 0 || len == 0) return CAT_OK;
+  NEED(x && out);
+  int rc = bind(c);
+  if (rc) return rc;
+  const size_t nb = (size_t)n_sig * len * sizeof(double);
+  double *dx, *dt, *dout;
+  SCRATCH(SLOT_A, nb, dx);
+  SCRATCH(SLOT_B, (size_t)n_taps * sizeof(double), dt);
+  SCRATCH(SLOT_C, nb, dout);
+  CU(cudaMemcpyAsync(dx, x, nb, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dt, taps, (size_t)n_taps * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_fir_reflect<double><<<nblk(n_sig * len, 256), 256, 0, c->stream>>>(n_sig, len, dx, n_taps, dt, dout);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dout, nb, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+int cat_savgol_f64(void* ctx, int64_t n_sig, int64_t len, const double* x, int32_t window, const double* taps,
+                   const double* edge_l, const double* edge_r, double* out) {
+  CTX();
+  NEED(n_sig >= 0 && window >= 3 && (window & 1) && window <= 4097 && len >= window && taps && edge_l && edge_r);
+  if (n_sig == 0) return CAT_OK;
+  NEED(x && out);
+  int rc = bind(c);
+  if (rc) return rc;
+  const size_t nb = (size_t)n_sig * len * sizeof(double);
+  const size_t nw = (size_t)window, ne = (size_t)(window / 2) * window;
+  double *dx, *dw, *dout;
+  SCRATCH(SLOT_A, nb, dx);
+  SCRATCH(SLOT_B, (nw + 2 * ne) * sizeof(double), dw);
+  SCRATCH(SLOT_C, nb, dout);
+  CU(cudaMemcpyAsync(dx, x, nb, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dw, taps, nw * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dw + nw, edge_l, ne * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dw + nw + ne, edge_r, ne * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_savgol<double><<<nblk(n_sig * len, 256), 256, 0, c->stream>>>(n_sig, len, dx, window, dw, dw + nw, dw + nw + ne, dout);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dout, nb, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+int cat_gradient_f64(void* ctx, int64_t n_sig, int64_t len, const double* y, const double* time, int32_t uniform,
+                     double* out) {
+  CTX();
+  NEED(n_sig >= 0 && len >= 2 && time);
+  if (n_sig == 0) return CAT_OK;
+  NEED(y && out);
+  int rc = bind(c);
+  if (rc) return rc;
+  const size_t nb = (size_t)n_sig * len * sizeof(double);
+  double *dy, *dt, *dout;
+  SCRATCH(SLOT_A, nb, dy);
+  SCRATCH(SLOT_B, (size_t)len * sizeof(double), dt);
+  SCRATCH(SLOT_C, nb, dout);
+  CU(cudaMemcpyAsync(dy, y, nb, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dt, time, (size_t)len * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_gradient<double><<<nblk(n_sig * len, 256), 256, 0, c->stream>>>(n_sig, len, dy, dt, uniform, dout);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dout, nb, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+namespace {
+// upload of an experiment's columns into one arena: [P0 (3T) | P1 (3T) | V1 (3T) | time (T) | theta (T) | gamma (T)]
+int feat_upload(CatCtx* c, int64_t T, const double* P0, const double* P1, const double* V1, const double* time,
+                const double* theta, const double* gamma, double** arena) {
+  double* in;
+  SCRATCH(SLOT_A, (size_t)T * 12 * sizeof(double), in);
+  CU(cudaMemcpyAsync(in, P0, (size_t)T * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(in + 3 * T, P1, (size_t)T * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(in + 6 * T, V1, (size_t)T * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(in + 9 * T, time, (size_t)T * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(in + 10 * T, theta, (size_t)T * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(in + 11 * T, gamma, (size_t)T * 8, cudaMemcpyHostToDevice, c->stream));
+  *arena = in;
+  return CAT_OK;
+}
+}  // namespace
+
+int cat_features_valid_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
+                           const double* time, const double* theta, const double* gamma, int32_t n_taps,
+                           const double* taps, int32_t uniform, int32_t for_gamma, double* out) {
+  CTX();
+  NEED(T >= 0 && n_taps >= 1 && (n_taps & 1) && n_taps <= 4097 && taps);
+  if (T == 0) return CAT_OK;
+  NEED(T >= 2 && P0 && P1 && V1 && time && theta && gamma && out);
+  int rc = bind(c);
+  if (rc) return rc;
+  CatNvtxRange range(c, "cat_features_valid");
+  double *in, *w, *dt, *dout;
+  rc = feat_upload(c, T, P0, P1, V1, time, theta, gamma, &in);
+  if (rc) return rc;
+  // work signals: sig (6T) | th1, ga1 (2T: the (T,1)-filtered angles) | sm (2T: smoothed) | d (2T: their gradient)
+  SCRATCH(SLOT_B, (size_t)T * 12 * sizeof(double), w);
+  SCRATCH(SLOT_C, (size_t)n_taps * sizeof(double), dt);
+  SCRATCH(SLOT_D, (size_t)T * 13 * sizeof(double), dout);
+  CU(cudaMemcpyAsync(dt, taps, (size_t)n_taps * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  double *sig = w, *a1 = w + 6 * T, *sm = w + 8 * T, *d = w + 10 * T;
+  const double* ang = in + 10 * T;   // [theta | gamma]
+  k_cable_terms<double><<<nblk(T, 256), 256, 0, c->stream>>>(T, in, in + 3 * T, in + 6 * T, 1.0, sig);
+  LAUNCHED();
+  // gaussian_filter1d(x.reshape(-1, 1)): the filtered axis has length 1 (main_fun.py:510-511)
+  k_fir_reflect<double><<<nblk(2 * T, 256), 256, 0, c->stream>>>(2 * T, 1, ang, n_taps, dt, a1);
+  LAUNCHED();
+  k_fir_reflect<double><<<nblk(2 * T, 256), 256, 0, c->stream>>>(2, T, ang, n_taps, dt, sm);
+  LAUNCHED();
+  k_gradient<double><<<nblk(2 * T, 256), 256, 0, c->stream>>>(2, T, sm, in + 9 * T, uniform, d);
+  LAUNCHED();
+  k_valid_rows<double><<<nblk(T, 256), 256, 0, c->stream>>>(T, sig, a1, a1 + T, d, d + T, for_gamma, dout);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(out, dout, (size_t)T * 13 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return CAT_OK;
+}
+
+int cat_features_dd_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
+                        const double* time, const double* theta, const double* gamma, int32_t window,
+                        const double* taps, const double* edge_l, const double* edge_r, int32_t uniform,
+                        double* feats, double* targets) {
+  CTX();
+  NEED(T >= 0 && window >= 3 && (window & 1) && window <= 4097 && taps && edge_l && edge_r);
+  if (T == 0) return CAT_OK;
+  NEED(T >= window && P0 && P1 && V1 && time && theta && gamma && feats && targets);
+  int rc = bind(c);
+  if (rc) return rc;
+  CatNvtxRange range(c, "cat_features_dd");
+  double *in, *w, *dw, *dout;
+  rc = feat_upload(c, T, P0, P1, V1, time, theta, gamma, &in);
+  if (rc) return rc;
+  // work signals: sig (6T) | sm (2T) | dsm (2T) | d2 (2T) | dsig (5T)
+  SCRATCH(SLOT_B, (size_t)T * 17 * sizeof(double), w);
+  const size_t nw = (size_t)window, ne = (size_t)(window / 2) * window;
+  SCRATCH(SLOT_C, (nw + 2 * ne) * sizeof(double), dw);
+  SCRATCH(SLOT_D, (size_t)T * 16 * sizeof(double), dout);
+  CU(cudaMemcpyAsync(dw, taps, nw * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dw + nw, edge_l, ne * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(dw + nw + ne, edge_r, ne * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  double *sig = w, *sm = w + 6 * T, *dsm = w + 8 * T, *d2 = w + 10 * T, *dsig = w + 12 * T;
+  const double* tm = in + 9 * T;
+  k_cable_terms<double><<<nblk(T, 256), 256, 0, c->stream>>>(T, in, in + 3 * T, in + 6 * T, 1e-3, sig);   // V1 in m/s
+  LAUNCHED();
+  k_savgol<double><<<nblk(2 * T, 256), 256, 0, c->stream>>>(2, T, in + 10 * T, window, dw, dw + nw, dw + nw + ne, sm);
+  LAUNCHED();
+  k_gradient<double><<<nblk(2 * T, 256), 256, 0, c->stream>>>(2, T, sm, tm, uniform, dsm);
+  LAUNCHED();
+  k_gradient<double><<<nblk(2 * T, 256), 256, 0, c->stream>>>(2, T, dsm, tm, uniform, d2);
+  LAUNCHED();
+  k_gradient<double><<<nblk(5 * T, 256), 256, 0, c->stream>>>(5, T, sig + T, tm, uniform, dsig);
+  LAUNCHED();
+  k_dd_rows<double><<<nblk(T, 256), 256, 0, c->stream>>>(T, sig, sm, dsm, dsig, d2, dout, dout + 14 * T);
+  LAUNCHED();
+  CU(cudaMemcpyAsync(feats, dout, (size_t)T * 14 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(targets, dout + 14 * T, (size_t)T * 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return CAT_OK;
 }

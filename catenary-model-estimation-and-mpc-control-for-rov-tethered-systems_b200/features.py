@@ -4,7 +4,9 @@
 cable-relative surge/sway, the per-row catenary solve + tension the reference runs through
 ``np.vectorize(brentq)`` at ~89 us/row); the builders below keep the reference's names, arguments and column
 orders and are column selections of that bank.  ``uniform_resample`` / ``load_and_resample_all`` keep
-main_fun.py:128-160's surface with the interpolation on the device.
+main_fun.py:128-160's surface with the interpolation on the device.  The smoothed / second-order layouts
+(``build_*_features_valid``, ``compute_derivatives``, ``preprocess_signals``, ``features_dd``) run SciPy's
+gaussian_filter1d / savgol_filter and np.gradient as device kernels (csrc/cat_kernels_feat.cuh).
 """
 from __future__ import annotations
 
@@ -105,31 +107,168 @@ UNIFORM_DT = 0.05      # main_fun.py:127
 
 
 def uniform_resample(df, dt=UNIFORM_DT, ctx=None):
-    """main_fun.py:128-145: every column linearly interpolated onto np.arange(t0, t_end, dt); returns a
-    DataFrame with 'Time' first, as the reference does."""
+    """Drop-in for main_fun.uniform_resample (main_fun.py:128-145): a DataFrame whose 'Time' column is the grid
+    np.arange(t[0], t[-1], dt) and whose other columns, in their original order, are linearly interpolated
+    (and extrapolated) onto it -- all columns in ONE device pass (k_resample_linear)."""
     import pandas as pd
     if "Time" not in df.columns:
-        raise ValueError("Missing 'Time' column in dataset.")
-    time_orig = df["Time"].values
-    time_uniform = np.arange(time_orig[0], time_orig[-1], dt)
-    others = [c for c in df.columns if c != "Time"]
-    out = resample_linear(time_orig, df[others].values, time_uniform, ctx)
-    data = {"Time": time_uniform}
-    data.update({c: out[:, j] for j, c in enumerate(others)})
-    return pd.DataFrame(data)
+        raise ValueError("Missing 'Time' column in dataset.")            # the reference's message
+    value_cols = df.columns.drop("Time")
+    knots = df["Time"].to_numpy(dtype=np.float64)
+    grid = np.arange(knots[0], knots[-1], dt)
+    table = resample_linear(knots, df[value_cols].to_numpy(dtype=np.float64), grid, ctx)
+    resampled = pd.DataFrame(table, columns=value_cols)
+    resampled.insert(0, "Time", grid)
+    return resampled
 
 
 def load_and_resample_all(file_list, dt=UNIFORM_DT, ctx=None):
-    """main_fun.py:148-159: read each CSV, drop rows without Theta/Gamma/Time, resample independently, concat."""
+    """Drop-in for main_fun.load_and_resample_all (main_fun.py:148-159): every CSV that carries Theta, Gamma and Time
+    is cleaned of rows missing any of them, resampled on its own grid and appended; others are skipped with a warning."""
+    import warnings
+
     import pandas as pd
-    dfs = []
-    for f in file_list:
-        df = pd.read_csv(f)
-        if {"Theta", "Gamma", "Time"}.issubset(df.columns):
-            dfs.append(uniform_resample(df.dropna(subset=["Theta", "Gamma", "Time"]), dt, ctx))
-        else:
-            print(f"[WARNING] Missing columns in {f}, skipping.")
-    return pd.concat(dfs, ignore_index=True)
+    needed = ["Theta", "Gamma", "Time"]
+    frames = []
+    for path in file_list:
+        raw = pd.read_csv(path)
+        if not set(needed) <= set(raw.columns):
+            warnings.warn(f"{path}: no {'/'.join(c for c in needed if c not in raw.columns)} column, skipped",
+                          stacklevel=2)
+            continue
+        frames.append(uniform_resample(raw.dropna(subset=needed), dt, ctx))
+    return pd.concat(frames, ignore_index=True)
+
+
+# ---- smoothed / second-order layouts (main_fun.py:504-655, 768-776, 811-871) -------------------------------------
+def _gaussian_taps(sigma, truncate=4.0):
+    """The weights scipy.ndimage.gaussian_filter1d(x, sigma) correlates with (order 0, truncate 4)."""
+    radius = int(truncate * float(sigma) + 0.5)
+    x = np.arange(-radius, radius + 1)
+    phi = np.exp(-0.5 / (float(sigma) * float(sigma)) * x ** 2)
+    return np.ascontiguousarray(phi / phi.sum())
+
+
+def _savgol_tables(window, order):
+    """Interior taps and the two edge-fit matrices of scipy.signal.savgol_filter(x, window, order), mode='interp'."""
+    if window % 2 != 1 or order >= window:
+        raise ValueError("window_length must be odd and larger than polyorder")
+    h = window // 2
+    centred = np.vander(np.arange(-h, h + 1, dtype=np.float64), order + 1, increasing=True)
+    taps = np.linalg.pinv(centred)[0]
+    pos = np.arange(window, dtype=np.float64)
+    fit = np.linalg.pinv(np.vander(pos, order + 1, increasing=True))
+    left = np.vander(pos[:h], order + 1, increasing=True) @ fit
+    right = np.vander(pos[window - h:], order + 1, increasing=True) @ fit
+    return (np.ascontiguousarray(taps), np.ascontiguousarray(left), np.ascontiguousarray(right))
+
+
+def _is_uniform(t):
+    """NumPy's own test for the uniform branch of np.gradient: every spacing bitwise equal."""
+    d = np.diff(t)
+    return int(d.size > 0 and bool((d == d[0]).all()))
+
+
+def _signals(x):
+    a = np.ascontiguousarray(x, np.float64)
+    if a.ndim == 1:
+        return a[None], True
+    if a.ndim != 2:
+        raise ValueError("a signal (len,) or a stack of signals (n, len) expected")
+    return a, False
+
+
+def gaussian_filter1d(x, sigma, ctx=None):
+    """scipy.ndimage.gaussian_filter1d(x, sigma) along the last axis (mode 'reflect') on the GPU; x (len,) or (n, len)."""
+    ctx = ctx or default_context()
+    a, one = _signals(x)
+    taps = _gaussian_taps(sigma)
+    out = np.empty_like(a)
+    ctx.check(ctx.lib.cat_fir_reflect_f64(ctx.handle, a.shape[0], a.shape[1], _lib.ptr(a), taps.size, _lib.ptr(taps),
+                                          _lib.ptr(out)))
+    return out[0] if one else out
+
+
+def savgol_filter(x, window_length, polyorder, ctx=None):
+    """scipy.signal.savgol_filter(x, window_length, polyorder) (mode 'interp') on the GPU; x (len,) or (n, len)."""
+    ctx = ctx or default_context()
+    a, one = _signals(x)
+    if a.shape[1] < window_length:
+        raise ValueError("If mode is 'interp', window_length must be less than or equal to the size of x.")
+    taps, left, right = _savgol_tables(int(window_length), int(polyorder))
+    out = np.empty_like(a)
+    ctx.check(ctx.lib.cat_savgol_f64(ctx.handle, a.shape[0], a.shape[1], _lib.ptr(a), int(window_length), _lib.ptr(taps),
+                                     _lib.ptr(left), _lib.ptr(right), _lib.ptr(out)))
+    return out[0] if one else out
+
+
+def gradient(y, t, ctx=None):
+    """np.gradient(y, t) (edge_order 1; uniform and non-uniform branches) on the GPU; y (len,) or (n, len)."""
+    ctx = ctx or default_context()
+    a, one = _signals(y)
+    tt = np.ascontiguousarray(t, np.float64)
+    if tt.shape != (a.shape[1],) or tt.size < 2:
+        raise ValueError("t must have the signal's length (>= 2)")
+    out = np.empty_like(a)
+    ctx.check(ctx.lib.cat_gradient_f64(ctx.handle, a.shape[0], a.shape[1], _lib.ptr(a), _lib.ptr(tt), _is_uniform(tt),
+                                       _lib.ptr(out)))
+    return out[0] if one else out
+
+
+def preprocess_signals(df, sigma=2, ctx=None):
+    """main_fun.preprocess_signals (main_fun.py:768-776): (time, Gaussian-smoothed Theta, Gaussian-smoothed Gamma)."""
+    t = np.ascontiguousarray(np.asarray(df["Time"], np.float64))
+    sm = gaussian_filter1d(np.stack([np.asarray(df["Theta"], np.float64), np.asarray(df["Gamma"], np.float64)]),
+                           sigma, ctx)
+    return t, sm[0], sm[1]
+
+
+def compute_derivatives(df, ctx=None):
+    """main_fun.compute_derivatives (main_fun.py:645-655): second time derivatives of the Savitzky-Golay (11, 3)
+    smoothed Theta and Gamma -> (ddtheta, ddgamma)."""
+    t = np.asarray(df["Time"], np.float64)
+    sm = savgol_filter(np.stack([np.asarray(df["Theta"], np.float64), np.asarray(df["Gamma"], np.float64)]), 11, 3, ctx)
+    dd = gradient(gradient(sm, t, ctx), t, ctx)
+    return dd[0], dd[1]
+
+
+def _valid(df, for_gamma, ctx):
+    ctx = ctx or default_context()
+    P0, P1, V1, t, th, ga = experiment_columns(df)
+    taps = _gaussian_taps(2)                                             # sigma = 2, main_fun.py:510-518
+    out = np.empty((t.shape[0], 13))
+    ctx.check(ctx.lib.cat_features_valid_f64(ctx.handle, t.shape[0], _lib.ptr(P0), _lib.ptr(P1), _lib.ptr(V1),
+                                             _lib.ptr(t), _lib.ptr(th), _lib.ptr(ga), taps.size, _lib.ptr(taps),
+                                             _is_uniform(t), int(for_gamma), _lib.ptr(out)))
+    return out
+
+
+def build_theta_features_valid(df, L=3.0, cable_wet_weight=1.521, ctx=None):
+    """main_fun.build_theta_features_valid (main_fun.py:504-571), 13 columns: theta v_surge / l, v_surge / l,
+    theta v_surge, v_surge, v_surge^2 / l, theta, gamma, gamma v_sway / l, v_sway / l, gamma v_sway, v_sway, dtheta,
+    dgamma.  (L and cable_wet_weight are accepted as in the reference, whose tension term is computed but not stacked.)"""
+    return _valid(df, 0, ctx)
+
+
+def build_gamma_features_valid(df, L=3.0, cable_wet_weight=1.521, ctx=None):
+    """main_fun.build_gamma_features_valid (main_fun.py:574-642): the sway / gamma terms first."""
+    return _valid(df, 1, ctx)
+
+
+def features_dd(df, ctx=None):
+    """main_fun.features_dd (main_fun.py:811-871) -> (features (T,14), targets (T,2)): the layout the second-order
+    (theta_ddot, gamma_ddot) models of dd_test_cluster.py / test_cluster.py:110-129 are trained on."""
+    ctx = ctx or default_context()
+    P0, P1, V1, t, th, ga = experiment_columns(df)
+    if t.shape[0] < 11:
+        raise ValueError("If mode is 'interp', window_length must be less than or equal to the size of x.")
+    taps, left, right = _savgol_tables(11, 3)                            # main_fun.py:829-830
+    feats = np.empty((t.shape[0], 14))
+    targets = np.empty((t.shape[0], 2))
+    ctx.check(ctx.lib.cat_features_dd_f64(ctx.handle, t.shape[0], _lib.ptr(P0), _lib.ptr(P1), _lib.ptr(V1), _lib.ptr(t),
+                                          _lib.ptr(th), _lib.ptr(ga), 11, _lib.ptr(taps), _lib.ptr(left),
+                                          _lib.ptr(right), _is_uniform(t), _lib.ptr(feats), _lib.ptr(targets)))
+    return feats, targets
 
 
 def load_trajectory_csv(path):

@@ -88,12 +88,14 @@ def rodrigues_rotation(vector, axis, angle_rad, *, ctx=None):
 
 
 def catenary_shapes(A, B, L, theta=None, gamma=None, *, n_pts=N_PTS, which=_lib.OUT_FINAL, dtype=np.float64,
-                    ctx=None):
+                    ctx=None, out=None):
     """Batched Catenary.__call__ + transform_catenary: A, B (n,3); L scalar or (n,); theta, gamma (n,) or None.
 
     Returns (curves, C, valid): curves is a list with one (n, n_pts, 3) array per bit of ``which``
     (order original, theta_rotated, theta_aligned, final), C (n,), valid (n,) uint8 (bit 0: span A->B in the
-    solve domain, bit 1: rotated span)."""
+    solve domain, bit 1: rotated span).  ``out``: a caller-owned (n_outputs, n, n_pts, 3) array to fill instead of a
+    fresh one -- for a million curves the 2.4 GB result is the cost of the call, and a reused page-locked buffer
+    (``ctx.pinned_empty``) takes it at PCIe speed where a fresh NumPy array pays page faults and the pageable path."""
     ctx = ctx or default_context()
     dtype = np.dtype(dtype)
     A_c = np.ascontiguousarray(A, dtype).reshape(-1, 3)
@@ -111,7 +113,10 @@ def catenary_shapes(A, B, L, theta=None, gamma=None, *, n_pts=N_PTS, which=_lib.
     nout = bin(which & 15).count("1")
     if nout == 0 or which != (which & 15):
         raise ValueError("which must be a non-empty mask of OUT_* bits")
-    out = np.empty((nout, n, n_pts, 3), dtype)
+    if out is None:
+        out = np.empty((nout, n, n_pts, 3), dtype)
+    elif out.shape != (nout, n, n_pts, 3) or out.dtype != dtype or not out.flags["C_CONTIGUOUS"]:
+        raise ValueError(f"out must be a C-contiguous {dtype} array of shape {(nout, n, n_pts, 3)}")
     C_out = np.empty(n, dtype)
     valid = np.empty(n, np.uint8)
     fn = ctx.lib.cat_shape_f64 if dtype == np.float64 else ctx.lib.cat_shape_f32

@@ -278,6 +278,36 @@ CAT_API int cat_feature_bank_f64(void* ctx, int64_t T, const double* P0, const d
                                  const double* time, const double* theta, const double* gamma, double L, double w,
                                  double* bank);
 
+/* ---- smoothed / second-order feature layouts (second half) -------------------
+ * Signals are stored one after the other: x, y, out are [n_sig][len].  The filter constants come from the caller
+ * (features.py computes them like SciPy does), so sigma, window length and polynomial order are free.
+ * cat_fir_reflect: replaces scipy.ndimage.gaussian_filter1d as the reference calls it (main_fun.py:510-519, 772-773):
+ *   correlation with n_taps (odd) symmetric taps, boundary mode 'reflect' (d c b a | a b c d | d c b a), any len >= 1.
+ * cat_savgol: replaces scipy.signal.savgol_filter(x, window, order), mode='interp' (main_fun.py:649-650, 829-830):
+ *   interior = taps (window) . x[i-h..i+h]; first / last h = window/2 samples = edge_l / edge_r (h x window, row-major)
+ *   applied to the first / last `window` samples (the window's least-squares polynomial evaluated in place).
+ * cat_gradient: replaces np.gradient(y, time) (edge_order 1): uniform != 0 selects NumPy's uniform branch
+ *   ((f[i+1] - f[i-1]) / 2h, taken when every spacing of `time` is bitwise equal), else the second-order
+ *   non-uniform formula; len >= 2. */
+CAT_API int cat_fir_reflect_f64(void* ctx, int64_t n_sig, int64_t len, const double* x, int32_t n_taps,
+                                const double* taps, double* out);
+CAT_API int cat_savgol_f64(void* ctx, int64_t n_sig, int64_t len, const double* x, int32_t window, const double* taps,
+                           const double* edge_l, const double* edge_r, double* out);
+CAT_API int cat_gradient_f64(void* ctx, int64_t n_sig, int64_t len, const double* y, const double* time,
+                             int32_t uniform, double* out);
+/* replaces build_theta_features_valid (for_gamma == 0, main_fun.py:504-571) / build_gamma_features_valid
+ * (for_gamma != 0, main_fun.py:574-642): inputs as cat_features_f64, taps = the Gaussian (sigma = 2 in the reference)
+ * -> out (T,13) row-major.  One upload, five kernels, one download. */
+CAT_API int cat_features_valid_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
+                                   const double* time, const double* theta, const double* gamma, int32_t n_taps,
+                                   const double* taps, int32_t uniform, int32_t for_gamma, double* out);
+/* replaces features_dd (main_fun.py:811-871): Savitzky-Golay smoothed angles, their first and second np.gradient,
+ * cable-relative surge / sway velocities (V1 / 1000: m/s) and their gradients -> feats (T,14), targets (T,2). */
+CAT_API int cat_features_dd_f64(void* ctx, int64_t T, const double* P0, const double* P1, const double* V1,
+                                const double* time, const double* theta, const double* gamma, int32_t window,
+                                const double* taps, const double* edge_l, const double* edge_r, int32_t uniform,
+                                double* feats, double* targets);
+
 /* ---- run-time equation programs ----------------------------------
  * Any PySR hall-of-fame row -- the ~3,900 equations under the reference's cluster_run/outputs and outputs
  * directories, or a model the user retrains (simple.py:60-75) -- evaluated without rebuilding the library:

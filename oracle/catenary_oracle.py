@@ -889,3 +889,131 @@ def resample_linear(time_in, values, time_out):
     idx = np.clip(np.searchsorted(x, xn), 1, len(x) - 1)
     lo, hi = idx - 1, idx
     return ((xn - x[lo]) / (x[hi] - x[lo]))[:, None] * y[hi] + ((x[hi] - xn) / (x[hi] - x[lo]))[:, None] * y[lo]
+
+
+# --------------------------------------------------------------------------
+# smoothed / second-order feature layouts (second half): main_fun.py:504-655, 768-776, 811-871.
+# The SciPy filters the reference calls are restated in NumPy (the GPU path follows these restatements); the golden
+# vectors in tests/golden/feature_layouts2.npz come from the reference's own functions with the real SciPy.
+# --------------------------------------------------------------------------
+def gaussian_taps(sigma, truncate=4.0):
+    """scipy.ndimage._gaussian_kernel1d(sigma, 0, radius) with radius = int(truncate * sigma + 0.5)."""
+    radius = int(truncate * float(sigma) + 0.5)
+    x = np.arange(-radius, radius + 1)
+    phi = np.exp(-0.5 / (float(sigma) * float(sigma)) * x ** 2)
+    return phi / phi.sum()
+
+
+def fir_reflect(x, taps):
+    """Correlation of the LAST axis with symmetric ``taps``, scipy.ndimage mode='reflect' (d c b a | a b c d | d c b a):
+    what gaussian_filter1d(x, sigma) does (main_fun.py:512-519, 772-773)."""
+    x = np.asarray(x, np.float64)
+    n = x.shape[-1]
+    r = (len(taps) - 1) // 2
+    idx = np.arange(-r, n + r)
+    idx = np.mod(idx, 2 * n)
+    idx = np.where(idx >= n, 2 * n - 1 - idx, idx)
+    ext = x[..., idx]
+    out = np.zeros_like(x)
+    for j, w in enumerate(taps):
+        out = out + w * ext[..., j:j + n]
+    return out
+
+
+def gaussian_filter1d(x, sigma):
+    return fir_reflect(x, gaussian_taps(sigma))
+
+
+def savgol_tables(window=11, order=3):
+    """(taps (window,), edge_left (h, window), edge_right (h, window)) of scipy.signal.savgol_filter(x, window, order)
+    with its default mode='interp': interior = least-squares polynomial value at the window centre; the first / last
+    h = window // 2 samples = the polynomial fitted to the first / last `window` samples, evaluated in place."""
+    h = window // 2
+    xs = np.arange(-h, h + 1, dtype=np.float64)
+    taps = np.linalg.pinv(np.vander(xs, order + 1, increasing=True))[0]
+    pos = np.arange(window, dtype=np.float64)
+    P = np.linalg.pinv(np.vander(pos, order + 1, increasing=True))            # (order+1, window)
+    edge_l = np.vander(pos[:h], order + 1, increasing=True) @ P
+    edge_r = np.vander(pos[window - h:], order + 1, increasing=True) @ P
+    return taps, edge_l, edge_r
+
+
+def savgol_filter(x, window=11, order=3):
+    x = np.asarray(x, np.float64)
+    n = x.shape[-1]
+    if n < window:
+        raise ValueError("savgol_filter: mode='interp' needs window_length <= size of x")
+    taps, el, er = savgol_tables(window, order)
+    h = window // 2
+    out = np.empty_like(x)
+    for i in range(h, n - h):
+        out[..., i] = x[..., i - h:i + h + 1] @ taps
+    out[..., :h] = x[..., :window] @ el.T
+    out[..., n - h:] = x[..., n - window:] @ er.T
+    return out
+
+
+def _valid_terms(df):
+    P0, P1, V1, _, t, th, ga = _experiment_arrays(df)
+    rel = P1 - P0
+    l = np.linalg.norm(rel[:, :2], axis=1, keepdims=True)
+    unit = rel / (np.linalg.norm(rel, axis=1, keepdims=True) + 1e-8)
+    v_surge = np.sum(V1 * unit, axis=1, keepdims=True)
+    v_sway = np.linalg.norm(np.cross(V1, unit), axis=1, keepdims=True)
+    # gaussian_filter1d of a (T,1) column filters along the LAST axis -- length 1 -- so the reference's `theta` and
+    # `gamma` feature columns are the raw signals times the weight sum (main_fun.py:510-511, 578-579) ...
+    theta = gaussian_filter1d(th.reshape(-1, 1), 2)
+    gamma = gaussian_filter1d(ga.reshape(-1, 1), 2)
+    # ... while the derivatives are taken of the properly smoothed 1-D signals (main_fun.py:517-521)
+    dtheta = np.gradient(gaussian_filter1d(th, 2), t).reshape(-1, 1)
+    dgamma = np.gradient(gaussian_filter1d(ga, 2), t).reshape(-1, 1)
+    return l, v_surge, v_sway, theta, gamma, dtheta, dgamma
+
+
+def build_theta_features_valid(df, L=3.0, cable_wet_weight=1.521):
+    """main_fun.py:504-571 (13 columns; the tension it also computes is not stacked)."""
+    l, vs, vw, th, ga, dth, dga = _valid_terms(df)
+    return np.hstack([th * vs / (l + 1e-8), vs / (l + 1e-8), th * vs, vs, vs ** 2 / (l + 1e-8), th, ga,
+                      ga * vw / (l + 1e-8), vw / (l + 1e-8), ga * vw, vw, dth, dga])
+
+
+def build_gamma_features_valid(df, L=3.0, cable_wet_weight=1.521):
+    """main_fun.py:574-642."""
+    l, vs, vw, th, ga, dth, dga = _valid_terms(df)
+    return np.hstack([ga * vw / (l + 1e-8), vw / (l + 1e-8), ga * vw, vw, vw ** 2 / (l + 1e-8), th, ga,
+                      th * vs / (l + 1e-8), vs / (l + 1e-8), th * vs, vs, dth, dga])
+
+
+def compute_derivatives(df):
+    """main_fun.py:645-655: second derivatives of the Savitzky-Golay (11, 3) smoothed angles."""
+    t = np.asarray(df["Time"], np.float64)
+    out = []
+    for k in ("Theta", "Gamma"):
+        s = savgol_filter(np.asarray(df[k], np.float64), 11, 3)
+        out.append(np.gradient(np.gradient(s, t), t))
+    return out[0], out[1]
+
+
+def preprocess_signals(df, sigma=2):
+    """main_fun.py:768-776."""
+    return (np.asarray(df["Time"], np.float64), gaussian_filter1d(np.asarray(df["Theta"], np.float64), sigma),
+            gaussian_filter1d(np.asarray(df["Gamma"], np.float64), sigma))
+
+
+def features_dd(df):
+    """main_fun.py:811-871: (features (T,14), targets (T,2)); V1 in m/s here."""
+    P0, P1, V1mm, _, t, th, ga = _experiment_arrays(df)
+    V1 = V1mm / 1000
+    a = np.stack([np.gradient(V1[:, j], t) for j in range(3)], 1)
+    th_s, ga_s = savgol_filter(th, 11, 3), savgol_filter(ga, 11, 3)
+    th_d, ga_d = np.gradient(th_s, t), np.gradient(ga_s, t)
+    th_dd, ga_dd = np.gradient(th_d, t), np.gradient(ga_d, t)
+    rel = P1 - P0
+    unit = rel / (np.linalg.norm(rel, axis=1, keepdims=True) + 1e-8)
+    v_surge = np.sum(V1 * unit, axis=1)
+    v_sway = np.linalg.norm(np.cross(V1, unit), axis=1)
+    a_surge, a_sway = np.gradient(v_surge, t), np.gradient(v_sway, t)
+    col = lambda v: np.asarray(v).reshape(-1, 1)
+    feats = np.hstack([col(th_s), col(ga_s), col(th_d), col(ga_d), col(v_sway), col(v_surge), col(a_sway), col(a_surge),
+                       V1, a])
+    return feats, np.hstack([col(th_dd), col(ga_dd)])

@@ -4,7 +4,10 @@
 Imports the reference's main_fun UNMODIFIED (oracle/reference_loader.py) and runs its own functions on a seeded
 synthetic experiment DataFrame: build_theta_features / build_gamma_features (main_fun.py:267-415, incl. the
 np.vectorize(brentq) solve_catenary per row), build_clean_features (main_fun.py:197-265), extract_features
-(main_fun.py:167-193), uniform_resample (main_fun.py:128-145).  Writes tests/golden/feature_layouts.npz."""
+(main_fun.py:167-193), uniform_resample (main_fun.py:128-145).  Writes tests/golden/feature_layouts.npz, and -- for the
+smoothed / second-order layouts build_theta_features_valid, build_gamma_features_valid (main_fun.py:504-642),
+compute_derivatives (:645-655), preprocess_signals (:768-776), features_dd (:811-871), on the jittered and on an exactly
+uniform time grid -- tests/golden/feature_layouts2.npz (inputs are those of feature_layouts.npz)."""
 import os
 import sys
 
@@ -41,6 +44,14 @@ def synthetic_experiment(T=600, seed=7):
     return cols
 
 
+def uniform_time(cols, dt=0.0625):
+    """The same experiment on an EXACTLY uniform time grid (dt a power of two): np.gradient then takes its uniform
+    branch ((f[i+1] - f[i-1]) / 2h) instead of the non-uniform second-order formula."""
+    c = dict(cols)
+    c["Time"] = np.arange(len(cols["Time"])) * dt
+    return c
+
+
 def main():
     import pandas as pd
     mf = ref.main_fun()
@@ -74,6 +85,23 @@ def main():
     np.savez_compressed(os.path.join(OUT, "catenary_model.npz"), cases=cases, ref_C=np.array(Cs), ref_x=np.array(xs),
                         ref_y=np.array(ys), eq_x=xe, eq_C=np.array([0.05, 0.7, 3.0]),
                         ref_eq=np.array([cm["catenary_equation"](xe, c) for c in (0.05, 0.7, 3.0)]))
+    # ---- second-order / smoothed layouts (second half): main_fun.py:504-655, 768-776, 811-871 ----
+    out2 = {}
+    for tag, cols_t in (("", cols), ("u_", uniform_time(cols))):
+        dft = pd.DataFrame(cols_t)
+        out2[tag + "Time"] = np.asarray(cols_t["Time"])
+        out2[tag + "ref_theta_features_valid"] = mf.build_theta_features_valid(dft, L, w)
+        out2[tag + "ref_gamma_features_valid"] = mf.build_gamma_features_valid(dft, L, w)
+        dd_t, dd_g = mf.compute_derivatives(dft)
+        out2[tag + "ref_ddtheta"], out2[tag + "ref_ddgamma"] = dd_t, dd_g
+        tt, th_s, ga_s = mf.preprocess_signals(dft, sigma=2)
+        out2[tag + "ref_pre_theta"], out2[tag + "ref_pre_gamma"] = th_s, ga_s
+        _, th_s3, ga_s3 = mf.preprocess_signals(dft, sigma=3.5)
+        out2[tag + "ref_pre_theta_s35"], out2[tag + "ref_pre_gamma_s35"] = th_s3, ga_s3
+        f_dd, t_dd = mf.features_dd(dft)
+        out2[tag + "ref_dd_features"], out2[tag + "ref_dd_targets"] = f_dd, t_dd
+    np.savez_compressed(os.path.join(OUT, "feature_layouts2.npz"), **out2)
+    print({k: v.shape for k, v in out2.items() if "ref_" in k})
     print({k: v.shape for k, v in out.items() if k.startswith("ref_")},
           "nan tension rows:", int(np.isnan(mf.solve_catenary(out["ref_theta_features"][:, 3],
                                                               out["ref_theta_features"][:, 4], L)).sum()))

@@ -41,3 +41,29 @@ def test_resample_matches_reference():
         assert np.array_equal(want[:, 0], t_new)
         got = orc.resample_linear(g["Time"], vals, t_new)
         assert np.array_equal(got, want[:, 1:]), key             # same formula as scipy: bit-exact
+
+
+def test_smoothed_and_second_order_layouts_match_reference():
+    """build_*_features_valid, compute_derivatives, preprocess_signals, features_dd (main_fun.py:504-655, 768-776,
+    811-871) restated in NumPy -- gaussian_filter1d's weights and 'reflect' boundary, savgol_filter's interior taps and
+    polynomial edge fit, np.gradient's uniform and non-uniform branches -- against the reference's own outputs with
+    the real SciPy, on a jittered and on an exactly uniform time grid."""
+    g, g2 = golden("feature_layouts.npz"), golden("feature_layouts2.npz")
+    for tag in ("", "u_"):
+        df = frame(g)
+        df["Time"] = g2[tag + "Time"]
+        assert_close(orc.build_theta_features_valid(df), g2[tag + "ref_theta_features_valid"], 1e-10, 1e-12, tag + "theta valid")
+        assert_close(orc.build_gamma_features_valid(df), g2[tag + "ref_gamma_features_valid"], 1e-10, 1e-12, tag + "gamma valid")
+        ddt, ddg = orc.compute_derivatives(df)
+        assert_close(ddt, g2[tag + "ref_ddtheta"], 1e-9, 1e-9, tag + "ddtheta")   # second differences of 4e-3 noise: |dd| ~ 10
+        assert_close(ddg, g2[tag + "ref_ddgamma"], 1e-9, 1e-9, tag + "ddgamma")
+        _, ths, gas = orc.preprocess_signals(df)
+        assert_close(ths, g2[tag + "ref_pre_theta"], 1e-12, 1e-14, tag + "gaussian theta")
+        assert_close(gas, g2[tag + "ref_pre_gamma"], 1e-12, 1e-14, tag + "gaussian gamma")
+        _, ths, gas = orc.preprocess_signals(df, sigma=3.5)
+        assert_close(ths, g2[tag + "ref_pre_theta_s35"], 1e-12, 1e-14, tag + "gaussian theta sigma 3.5")
+        f, tg = orc.features_dd(df)
+        assert_close(f, g2[tag + "ref_dd_features"], 1e-9, 1e-10, tag + "features_dd")
+        assert_close(tg, g2[tag + "ref_dd_targets"], 1e-9, 1e-9, tag + "features_dd targets")
+    taps, el, er = orc.savgol_tables(11, 3)
+    assert abs(taps.sum() - 1) < 1e-14 and np.allclose(taps, taps[::-1]) and np.allclose(el.sum(1), 1) and np.allclose(er.sum(1), 1)

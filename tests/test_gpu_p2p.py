@@ -48,8 +48,7 @@ try:
     last = torch.zeros(2, dtype=torch.int64, device="cuda:0")
     ex.flush(winner=last)
     torch.cuda.synchronize()
-    first = wbuf[0].cpu().numpy()
-    out["pipelined_first_is_sentinel"] = bool(first[1] == -1)
+    out["pipelined_first"] = list(ex.result(winner=wbuf[0]))   # = the winner of the step before the run
     for j in range(1, len(SEEDS)):
         out["pipelined"].append(list(ex.result(winner=wbuf[j])))
     out["pipelined"].append(list(ex.result(winner=last)))
@@ -107,8 +106,9 @@ def test_fused_exchange_two_ranks_one_gpu(cb, tmp_path):
         J = orc.mpc_rollout_costs(p, orc.sample_controls(seed, np.arange(6000), 12, sigma), pref)
         assert bi == int(np.argmin(J)) and abs(bc - J.min()) <= 1e-9 * J.min()
     for o in outs:
-        # pipelined steps deliver the same winners one step late; the first one has no predecessor
-        assert o["pipelined_first_is_sentinel"]
+        # pipelined steps deliver the same winners one step late: the first returns the winner of the step launched
+        # before the run (the last lock-step one), flush() the winner of the last
+        assert o["pipelined_first"] == outs[0]["winners"][-1]
         assert o["pipelined"] == outs[0]["winners"]
         assert o["after_mix"] == outs[0]["winners"][0]
         assert o["host"] == outs[0]["winners"][:3]

@@ -8,7 +8,7 @@ stamp() { echo "[$(( $(date +%s) - T0 )) s] $*" | tee -a gpurun_out/timeline.log
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.log 2>&1
 if [[ $PARTS == *tests* ]]; then
   stamp "pytest -m gpu"
-  timeout 1200 python -m pytest tests -m gpu -x -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+  timeout 1200 python -m pytest tests -m gpu -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
   tail -n 5 gpurun_out/pytest_gpu.log
   stamp "smoke"
   timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
@@ -22,6 +22,11 @@ fi
 if [[ $PARTS == *ref* ]]; then
   stamp "reference arm"
   timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
+fi
+if [[ $PARTS == *ab* ]]; then
+  stamp "A/B of the library variants in ab/"
+  bash tools/ab.sh 2 > gpurun_out/ab.log 2>&1
+  cat gpurun_out/ab.log
 fi
 if [[ $PARTS == *prof* || $PARTS == *ncu* ]]; then
   stamp "prof scripts"
