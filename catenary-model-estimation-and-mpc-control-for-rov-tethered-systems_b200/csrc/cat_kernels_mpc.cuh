@@ -423,7 +423,8 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   // issued ~40% into the step) does NOT (~1,000 cycles of DRAM latency at the natural clock; round-1 ncu: 3.2
   // long-scoreboard stall cycles per issued instruction): it keeps CAT_MPC_PF steps in flight through cp.async.
   S Vq[3] = {S(0), S(0), S(0)};
-  T Rnext[3];
+  double Rnext[3];   // as loaded: the fp32 kernel converts at USE, one step later (a conversion next to the load
+                     // waits for it: round-2 ncu, 55% of that kernel's remaining long-scoreboard samples)
   int slot = 0;          // ASYNC: ring slot of step h
   int slot_in = 0;       // ASYNC: ring slot the next prefetch lands in
   if constexpr (ASYNC) {
@@ -446,9 +447,9 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     Vq[2] = uc[2 * q.sa];
     uc += q.sh;
   }
-  Rnext[0] = T(pr[0]);
-  Rnext[1] = T(pr[1]);
-  Rnext[2] = T(pr[2]);
+  Rnext[0] = pr[0];
+  Rnext[1] = pr[1];
+  Rnext[2] = pr[2];
 
   for (int h = 0; h < q.H; ++h) {
     T Vn[3];
@@ -471,15 +472,15 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       Vn[1] = T(Vq[1]);
       Vn[2] = T(Vq[2]);
     }
-    const T Rh[3] = {Rnext[0], Rnext[1], Rnext[2]};
+    const T Rh[3] = {T(Rnext[0]), T(Rnext[1]), T(Rnext[2])};
     if constexpr (RNG) {
       // unconditional (the last step re-reads its own row): no branch at the top of the loop body.  Measured
       // on one box (tools/ab.sh): 0.1693 -> 0.1677 ms here, but 0.1054 -> 0.1088 ms with the control loads
       // of the explicit form below, which therefore keeps its branch.
       pr += (h + 1 < q.H && h + 1 < ref_rem) ? 3 : 0;
-      Rnext[0] = T(pr[0]);
-      Rnext[1] = T(pr[1]);
-      Rnext[2] = T(pr[2]);
+      Rnext[0] = pr[0];
+      Rnext[1] = pr[1];
+      Rnext[2] = pr[2];
     } else if constexpr (ASYNC) {
       if (h + CAT_MPC_PF < q.H) {   // step h + PF into the slot that was read PF + 1 steps ago
         S* d = reinterpret_cast<S*>(s_ring.v) + threadIdx.x + (slot_in * 3) * CAT_MPC_BLOCK;
@@ -492,9 +493,9 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       slot_in = slot_in == CAT_MPC_PF ? 0 : slot_in + 1;
       if (h + 1 < q.H) {
         if (h + 1 < ref_rem) pr += 3;
-        Rnext[0] = T(pr[0]);
-        Rnext[1] = T(pr[1]);
-        Rnext[2] = T(pr[2]);
+        Rnext[0] = pr[0];
+        Rnext[1] = pr[1];
+        Rnext[2] = pr[2];
       }
     } else {
       if (h + 1 < q.H) {   // one branch for both fetches (the form the fp64 kernel was tuned with)
@@ -503,9 +504,9 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
         Vq[2] = uc[2 * q.sa];
         uc += q.sh;
         if (h + 1 < ref_rem) pr += 3;
-        Rnext[0] = T(pr[0]);
-        Rnext[1] = T(pr[1]);
-        Rnext[2] = T(pr[2]);
+        Rnext[0] = pr[0];
+        Rnext[1] = pr[1];
+        Rnext[2] = pr[2];
       }
     }
     T Pn[3], An[3];

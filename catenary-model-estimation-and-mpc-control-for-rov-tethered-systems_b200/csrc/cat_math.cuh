@@ -745,7 +745,7 @@ __device__ __forceinline__ void cat_philox4x32_10(uint32_t c0, uint32_t c1, uint
 #define CAT_ICDF_SMEM_ZMAX 3.29   // < y(2^21) = 3.2971...
 
 template <typename T> struct CatIcdfSmem {
-  alignas(16) T tab[CAT_ICDF_SMEM_SEGS * 4];
+  alignas(16) T tab[(CAT_ICDF_SMEM_SEGS + 1) * 4];   // row 0 = (4, 0, 0, 0): every octave below the hot ones
 };
 
 // block-cooperative copy of the hot octaves into shared memory; ends with a barrier
@@ -755,9 +755,10 @@ __device__ __forceinline__ void cat_icdf_stage(CatIcdfSmem<T>& sm) {
       reinterpret_cast<const double2*>(CAT_ICDF_TAB + (CAT_ICDF_SMEM_E_LO - CAT_ICDF_E_LO) * 32 * 4);
   for (int i = threadIdx.x; i < CAT_ICDF_SMEM_SEGS * 2; i += blockDim.x) {
     const double2 v = __ldg(src + i);
-    sm.tab[2 * i] = T(v.x);
-    sm.tab[2 * i + 1] = T(v.y);
+    sm.tab[4 + 2 * i] = T(v.x);
+    sm.tab[4 + 2 * i + 1] = T(v.y);
   }
+  if (threadIdx.x < 4) sm.tab[threadIdx.x] = threadIdx.x == 0 ? T(4) : T(0);   // > every clip <= CAT_ICDF_SMEM_ZMAX
   __syncthreads();
 }
 
@@ -770,9 +771,9 @@ __device__ __noinline__ T cat_icdf_deep(int seg, T t) {
   return M::fma_(M::fma_(M::fma_(T(__ldg(g + 3)), t, T(__ldg(g + 2))), t, T(__ldg(g + 1))), t, T(__ldg(g)));
 }
 
-// deep: clip > CAT_ICDF_SMEM_ZMAX (warp-uniform)
+// clip(z(r), +-clip);  deep: clip > CAT_ICDF_SMEM_ZMAX (warp-uniform)
 template <typename T, typename M>
-__device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& sm, bool deep) {
+__device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& sm, T clip, bool deep) {
   const uint32_t flip = (uint32_t)((int)r >> 31);          // 0xffffffff for r >= 2^31
   uint32_t rp = r ^ flip;                                   // r' = r < 2^31 ? r : ~r
   rp = rp < 32u ? 32u : rp;
@@ -792,8 +793,10 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& s
     seg = (b >> 18) - ((127 + CAT_ICDF_E_LO) << 5);
     t = __int_as_float(0x3f800000 | ((b & 0x3ffff) << 5)) - 1.0f;
   }
-  const int sseg = seg - (CAT_ICDF_SMEM_E_LO - CAT_ICDF_E_LO) * 32;
-  const T* c = sm.tab + 4 * (sseg < 0 ? 0 : sseg);
+  // row of the shared table: 1 + segment above the first hot octave; everything below lands on row 0, whose constant
+  // 4 exceeds every clip the shared table serves, so the clamp below turns it into +-clip without a select here
+  const int row = seg - ((CAT_ICDF_SMEM_E_LO - CAT_ICDF_E_LO) * 32 - 1);
+  const T* c = sm.tab + 4 * (row < 0 ? 0 : row);
   T c0, c1, c2, c3;
   if constexpr (sizeof(T) == 8) {
     const double2 a = *reinterpret_cast<const double2*>(c), b2 = *reinterpret_cast<const double2*>(c + 2);
@@ -803,11 +806,12 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& s
     c0 = a.x; c1 = a.y; c2 = a.z; c3 = a.w;
   }
   T y = M::fma_(M::fma_(M::fma_(c3, t, c2), t, c1), t, c0);
-  if (sseg < 0) y = T(4);   // beyond every clip <= CAT_ICDF_SMEM_ZMAX: the caller's clamp decides
   if (deep) {               // warp-uniform; false in every BASELINE config
-    if (sseg < 0) y = cat_icdf_deep<T, M>(seg, t);
+    if (row <= 0) y = cat_icdf_deep<T, M>(seg, t);
   }
-  // z = r >= 2^31 ? y : -y, on the sign bit
+  // |z| clipped BEFORE the sign goes on (y >= 0, never NaN: one compare and two selects), then z = r >= 2^31 ? y : -y
+  // on the sign bit
+  y = y > clip ? clip : y;
   if constexpr (sizeof(T) == 8)
     return __hiloint2double(__double2hiint(y) ^ (int)(~flip & 0x80000000u), __double2loint(y));
   else
@@ -822,5 +826,5 @@ __device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t probl
   cat_philox4x32_10((uint32_t)k, (uint32_t)(k >> 32), h, problem, (uint32_t)seed, (uint32_t)(seed >> 32), r);
   const bool deep = clip > T(CAT_ICDF_SMEM_ZMAX);
 #pragma unroll
-  for (int a = 0; a < 3; ++a) out[a] = M::clamp_sym_(cat_icdf_normal<T, M>(r[a], sm, deep), clip) * sigma[a];
+  for (int a = 0; a < 3; ++a) out[a] = cat_icdf_normal<T, M>(r[a], sm, clip, deep) * sigma[a];
 }

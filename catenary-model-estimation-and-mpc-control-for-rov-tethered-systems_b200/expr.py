@@ -249,6 +249,8 @@ class ExpressionModel:
         pr = self.program
         if X.ndim != 3 or X.shape[2] != pr.n_features:
             raise ValueError(f"X must be (T,{pr.n_features}) or (n,T,{pr.n_features})")
+        if self.mean is not None:                        # the model's StandardScaler applies to integration too
+            X = (X - self.mean) / self.scale
         X = np.ascontiguousarray(X)
         n, T = X.shape[0], X.shape[1]
         time = np.ascontiguousarray(time, np.float64)

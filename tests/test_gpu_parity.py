@@ -532,7 +532,10 @@ def test_shapes_config2_distribution_all_curves(cb, sweep_L):
     (o0, o1, o2, o3), Co, vo = orc.transform_catenary_batch(A, B, L, th, ga)
     curves, C, valid = cb.catenary_shapes(A, B, L, th, ga, which=15)
     assert np.array_equal(valid, vo)
-    assert (vo[:n // 100] & 1 == 0).all() and (vo & 1).mean() > (0.5 if sweep_L else 0.9)
+    if not sweep_L:
+        assert (vo[:n // 100] & 1 == 0).all()               # d > L = 3: taut, no root
+    # (slack spans whose C = 2u/l exceeds the reference's bracket end 10 are outside the solve domain too)
+    assert 0.4 < (vo & 1).mean() < 0.95 and (vo == 3).mean() > 0.4
     assert_close(C, Co, RTOL64, 0, "C")
     for j, want in enumerate((o0, o1, o2, o3)):
         assert_close(curves[j], want, RTOL64, 1e-12, f"output {j}, all {n} curves")
@@ -621,10 +624,11 @@ def test_cold_path_counters(cb):
     ctx.stats(enable=True, reset=True)
     cb.mpc_sample_step(p, _controls(K, H, 3), cb.circle_reference(H, p["dt"]), return_costs=False)
     quiet = ctx.stats(enable=True, reset=True)
-    assert quiet["solve_cold"] == 0 and quiet["sine_cold"] == 0, quiet
+    # every warp iterates once, on its first step (the record it starts from is a guess, not a root)
+    assert quiet["solve_cold"] <= K // 32 and quiet["sine_cold"] == 0, quiet
     p5 = cb.default_mpc_params(dt=0.05)
     cb.mpc_sample_step(p5, _controls(K, H, 3) * 4.0, cb.circle_reference(H, 0.05), return_costs=False)
     loud = ctx.stats(enable=False, reset=True)
-    assert loud["solve_cold"] > 0 or loud["sine_cold"] > 0, loud
+    assert loud["solve_cold"] > 4 * (K // 32) and loud["sine_cold"] > 0, loud
     warp_steps = (K // 32) * H
     assert loud["solve_cold"] <= warp_steps and loud["sine_cold"] <= 4 * warp_steps
