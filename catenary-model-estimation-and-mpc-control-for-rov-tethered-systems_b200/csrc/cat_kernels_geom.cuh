@@ -44,16 +44,11 @@ __global__ void __launch_bounds__(256) k_solve_param(long long n, const T* __res
 //         cosh/sinh evaluations and idle lanes give back
 //   fp32: 16 lanes 0.28 ms vs 32 lanes 0.33 ms (each half-warp still writes a 192-byte run)
 template <typename T> struct CatShapeGroup { static constexpr int lanes = sizeof(T) == 4 ? 16 : 32; };
-// 16-byte stores: the lanes of a warp park their (x, y, z) samples in shared memory and write them back out as
-// consecutive float4 / double2 -- a hop of 32 points is one contiguous 384-byte (fp32) or 768-byte (fp64) run of
-// the AoS output, so 24 (48) vector stores replace 96 scalar ones.  Needs n_pts * 3 * sizeof(T) and the output base
-// to be multiples of 16 bytes (true for the 100-point curves of every BASELINE config); otherwise the scalar form
-// runs.  A/B switch: -DCAT_SHAPE_VEC=0.
-#ifndef CAT_SHAPE_VEC
-#define CAT_SHAPE_VEC 1
-#endif
-template <typename T> struct CatVec16 { typedef double2 type; };
-template <> struct CatVec16<float> { typedef float4 type; };
+// Stores stay scalar (three 8- or 4-byte stores per lane at a 24- or 12-byte stride).  Round 2 measured the
+// alternative -- park the warp's samples in shared memory and write each 32-point hop as consecutive float4 / double2
+// -- on one B200 (profiles/r2_ab_shape_vec_stores.txt): fp64 final curve 0.744 vs 0.449 ms, fp32 0.469 vs 0.268 ms.
+// The two warp barriers and the staging traffic per hop cost far more than the narrower stores save; L2 already
+// merges the strided stores into full sectors (DRAM write bytes == algorithmic bytes in the ncu capture).
 #define CAT_SHAPE_RESEED 16    // (power of two) re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
 
 template <typename T> struct CatShapeSpan {
@@ -272,9 +267,6 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
 
   const int n_here = (int)((n - base < CAT_SHAPE_TILE) ? (n - base) : CAT_SHAPE_TILE);
   const int lane = tid & 31, warp = tid >> 5, n_warps = CAT_SHAPE_TILE / 32;
-  __shared__ __align__(16) T s_stage[CAT_SHAPE_VEC ? CAT_SHAPE_TILE / 32 : 1][CAT_SHAPE_VEC ? 96 : 1];
-  const bool vec = CAT_SHAPE_VEC != 0 && ((long long)n_pts * 3 * sizeof(T)) % 16 == 0 &&
-                   (reinterpret_cast<unsigned long long>(out) & 15ull) == 0;
   const long long blk = n * (long long)n_pts * 3;   // elements per output block
   // output-block offset and record offset of each requested map (slot = rank of m among the requested ones)
   long long m_out[4];
@@ -339,7 +331,7 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
           sh = sn;
         }
         const T zoff = ok ? (cm - cm_low) * inv_C : T(0);   // chord fallback: spans outside the solve domain
-        if (!vec && (pt >= n_pts || !have)) continue;
+        if (pt >= n_pts || !have) continue;
         // sample = A + s a + zoff b as two FMAs per coordinate
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
@@ -355,36 +347,10 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
             p1 = mp[1];
             p2 = mp[2];
           }
-          const T x = M::fma_(zoff, p1.y, M::fma_(s, p0.x, A0));
-          const T y = M::fma_(zoff, p2.x, M::fma_(s, p0.y, A1));
-          const T z = M::fma_(zoff, p2.y, M::fma_(s, p1.x, A2));
-          if (!vec) {
-            T* om = o + m_out[m];
-            om[0] = x;
-            om[1] = y;
-            om[2] = z;
-          } else {
-            // every lane of the warp is here (uniform trip counts): park, then write the group's run as 16-byte vectors
-            typedef typename CatVec16<T>::type V16;
-            constexpr int VEC = 16 / (int)sizeof(T);
-            T* st = s_stage[warp];
-            st[3 * lane] = x;
-            st[3 * lane + 1] = y;
-            st[3 * lane + 2] = z;
-            __syncwarp();
-            const int left = n_pts - G * hop;
-            const int nv = have ? 3 * (left < G ? left : G) : 0;   // values of this group in this hop
-            T* og = out + m_out[m] + ((base + ci) * (long long)n_pts + G * hop) * 3;
-            const T* sg = st + 3 * G * grp;
-            for (int v = gl * VEC; v < nv; v += G * VEC) {
-              if (v + VEC <= nv) {
-                *reinterpret_cast<V16*>(og + v) = *reinterpret_cast<const V16*>(sg + v);
-              } else {
-                for (int j = v; j < nv; ++j) og[j] = sg[j];
-              }
-            }
-            __syncwarp();
-          }
+          T* om = o + m_out[m];
+          om[0] = M::fma_(zoff, p1.y, M::fma_(s, p0.x, A0));
+          om[1] = M::fma_(zoff, p2.x, M::fma_(s, p0.y, A1));
+          om[2] = M::fma_(zoff, p2.y, M::fma_(s, p1.x, A2));
         }
       }
     }

@@ -117,6 +117,7 @@ int shape_host(CatCtx* c, int64_t n, const T* A, const T* B, const T* L, int64_t
   int rc = bind(c);
   if (rc) return rc;
   const int nout = popcount4(which);
+  CatNvtxRange range(c, "cat_shape (host): chunked H2D / k_shape / D2H");
   // chunked two-lane pipeline: lane j owns its own scratch; H2D, kernel, D2H are in-order per lane and the
   // two lanes overlap each other (copy engine of one with the SMs of the other).
   const int64_t chunk = 65536;
@@ -497,6 +498,7 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     // winners fold on the device in candidate order (same total order as one launch: lowest cost, then lowest
     // global index).
     const int NC = 8;
+    CatNvtxRange r_up(c, "cat: chunked H2D of the candidates + rollouts");
     long long* d_pairs;
     SCRATCH(SLOT_F, (size_t)NC * 16, d_pairs);
     const bool aos = (p->flags & CAT_MPC_CONTROLS_AOS) != 0;
@@ -564,7 +566,10 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   }
   if (costs)
     CU(cudaMemcpyAsync(costs, d_costs, np * (size_t)p->K * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  {
+    CatNvtxRange r_wait(c, x ? "cat: wait for the job-wide winner (in-kernel exchange)" : "cat: wait for the winner");
+    CU(cudaStreamSynchronize(c->stream));
+  }
   if (staged) {   // the winners are already in host memory (written through the mapping before the kernel ended)
     std::memcpy(best_cost, c->h_stage, np * sizeof(double));
     std::memcpy(best_idx, c->h_stage + np * sizeof(double), np * sizeof(long long));
