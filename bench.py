@@ -306,6 +306,23 @@ def run_ours(args):
     if pipe is not None:
         launches += args.steps                                  # k_reduce_winners, one per step, on the side stream
     ms_total = allmax(e0.elapsed_time(e1))
+    # the same loop with programmatic dependent launch switched off: every step waits for the previous one to retire
+    ctx.set_overlap(False)
+    for i in range(3):
+        one(i)
+    barrier()
+    g0, g1 = _events(torch)
+    g0.record()
+    for i in range(args.steps):
+        one(i)
+    if fused is not None:
+        fused.flush()
+    if pipe is not None:
+        torch.cuda.current_stream().wait_stream(pipe.side)
+    g1.record()
+    barrier()
+    ms_serial = allmax(g0.elapsed_time(g1)) / args.steps
+    ctx.set_overlap(True)
     exchange_check = None
     if world > 1:
         # the in-kernel exchange (lock-step, and pipelined + flush) must agree with the plain NCCL all-gather + host fold
@@ -528,8 +545,14 @@ def run_ours(args):
                                    "throughput loop pipelined (each step folds the previous step's winners), latency "
                                    "loop lock-step" if fused is not None else
                                    "nccl all_gather 16 B/rank + device fold on a side stream, double-buffered"),
+                      "launch": "one stream, back-to-back launches with programmatic stream serialization: a step's "
+                                "candidates start on the SMs its predecessor's early finishers leave idle; each step "
+                                "touches its outputs only after the predecessor has completed",
                       "l2": "3 rotating control sets (236 MB) > 126 MB L2"},
            "p50_ms": lat[len(lat) // 2], "p99_ms": lat[int(len(lat) * 0.99)], "latency_samples": len(lat),
+           "value_no_overlap": {"value": world * K * H / (ms_serial * 1e-3), "ms_per_step": ms_serial,
+                                "what": "the same loop with programmatic dependent launch off (cat_set_overlap(0)): each "
+                                        "rollout starts after the previous one has retired -- the round-1 launch mode"},
            "clocks": clocks, "e2e": e2e, "configs": configs, "gpu_launches": int(launches),
            "exchange_check": exchange_check, "fused_lockstep": lock_cmp, "nccl_exchange": nccl_cmp}
     if world == 1:

@@ -66,6 +66,7 @@ SIGNATURES = {
     "cat_mpc_workspace_create": (_int, [_vp, _i64, _i32, C.POINTER(_vp)]),
     "cat_mpc_workspace_destroy": (_int, [_vp, _vp]),
     "cat_set_workspace": (_int, [_vp, _vp]),
+    "cat_set_overlap": (_int, [_vp, _int]),
     "cat_mpc_stats": (_int, [_vp, _int, _int, _vp]),
     "cat_timer_start": (_int, [_vp]),
     "cat_timer_stop_ms": (_int, [_vp, C.POINTER(C.c_float)]),

@@ -56,6 +56,10 @@ class Context:
         else:
             self.check(self.lib.cat_set_stream(self.handle, C.c_void_p(int(cuda_stream)), 0))
 
+    def set_overlap(self, on):
+        """Programmatic dependent launch of the rollout kernels (cat_set_overlap; default on)."""
+        self.check(self.lib.cat_set_overlap(self.handle, 1 if on else 0))
+
     def timer_start(self):
         self.check(self.lib.cat_timer_start(self.handle))
 

@@ -36,6 +36,7 @@ struct CatCtx {
   unsigned char* h_stage;
   unsigned char* d_stage;   // device alias of h_stage
   void* ws;                 // CatMpcWs* selected by cat_set_workspace; null = the shared scratch slots
+  int overlap;              // rollouts launch with programmatic stream serialization (cat_set_overlap; default on)
   int nvtx;                 // CAT_NVTX=1: NVTX ranges around step / exchange / host copies
   CatHostReg reg[64];
   int n_reg;

@@ -51,8 +51,9 @@ __global__ void __launch_bounds__(256) k_ctrl_mppi(const CatMpcDev<T> q, const C
                                                    const long long* __restrict__ best_idx,
                                                    double* __restrict__ partial) {
   typedef CatMath<T> M;
-  __shared__ CatIcdfSmem<T> s_icdf;
-  cat_icdf_stage<T>(s_icdf);
+  __shared__ CatIcdfSmem<T> s_icdf_tab;
+  cat_icdf_stage<T>(s_icdf_tab);
+  const CatIcdfRef s_icdf = cat_icdf_ref_of<T>(s_icdf_tab);
   const int h = blockIdx.x, prob = blockIdx.y, z = blockIdx.z;
   const unsigned long long seed_eff = q.seed + (unsigned long long)(*q.step);
   const double jmin = best_cost[prob];
@@ -176,8 +177,9 @@ __global__ void __launch_bounds__(64) k_ctrl_advance(const CatMpcDev<T> q, const
                                                      unsigned int* __restrict__ ticket) {
   typedef CatMath<T> M;
   extern __shared__ double s_u[];   // [H][3]
-  __shared__ CatIcdfSmem<T> s_icdf;
-  if (x.mode != CAT_CTRL_MPPI) cat_icdf_stage<T>(s_icdf);   // block-uniform
+  __shared__ CatIcdfSmem<T> s_icdf_tab;
+  if (x.mode != CAT_CTRL_MPPI) cat_icdf_stage<T>(s_icdf_tab);   // block-uniform
+  const CatIcdfRef s_icdf = cat_icdf_ref_of<T>(s_icdf_tab);
   const int prob = blockIdx.x;
   const int t = *step;
   const unsigned long long seed_eff = q.seed + (unsigned long long)t;

@@ -67,6 +67,7 @@ template <typename T> struct CatMpcDev {
   const int2* prog;
   const double* prog_consts;
   int n_ops_t, n_ops_g, n_c_t, n_c_g;
+  int ref_smem_off;   // byte offset of the staged reference window in the dynamic shared memory
   CatP2PDev p2p;
 };
 
@@ -82,11 +83,6 @@ template <typename T> struct CatMpcVm {
 // shared-memory slot of the sampler table: the real thing in the sampling kernels, one byte elsewhere
 template <typename T, bool RNG> struct CatIcdfSlot { typedef CatIcdfSmem<T> type; };
 template <typename T> struct CatIcdfSlot<T, false> { typedef char type; };
-template <typename T, bool RNG>
-__device__ __forceinline__ const CatIcdfSmem<T>& cat_icdf_ref(const typename CatIcdfSlot<T, RNG>::type& s) {
-  return *reinterpret_cast<const CatIcdfSmem<T>*>(&s);   // never dereferenced when RNG is false
-}
-
 // Asynchronous control prefetch (cp.async, global -> shared, no register in between): thread t owns column t of a
 // ring s[slot][axis][t] and keeps CAT_MPC_PF horizon steps in flight.  A ring held in REGISTERS does not work: the
 // moves that rotate it need the loaded data, so the warp waits on step h+3's load at step h+1 (round-2 ncu of the
@@ -118,7 +114,7 @@ template <int N> __device__ __forceinline__ void cat_cp_async_wait() {
 // global candidate 0 carries no noise (oracle ctrl_candidates)
 template <typename T, typename M>
 __device__ __forceinline__ void cat_nominal_control(const CatMpcDev<T>& q, unsigned long long seed_eff, int prob,
-                                                    long long kglob, int h, const CatIcdfSmem<T>& icdf, T out[3]) {
+                                                    long long kglob, int h, CatIcdfRef icdf, T out[3]) {
   cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)kglob, (uint32_t)h, q.sigma,
                            q.clip, icdf, out);
   const double* un = q.u_nom + ((long long)prob * q.H + h) * 3;
@@ -347,17 +343,21 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   typedef CatMath<T> M;
   // inverse-CDF table of the device sampler (hot octaves), staged once per block
   __shared__ typename CatIcdfSlot<T, RNG>::type s_icdf;
-  if constexpr (RNG) cat_icdf_stage<T>(s_icdf);
+  CatIcdfRef icdf = 0;
+  if constexpr (RNG) {
+    cat_icdf_stage<T>(s_icdf);
+    icdf = cat_icdf_ref_of<T>(s_icdf);
+  }
   constexpr bool ASYNC = !RNG && (sizeof(T) == 4 || CAT_MPC_ASYNC_F64 != 0);
   __shared__ __align__(16) CatRing<S, ASYNC> s_ring;
+  // dynamic shared memory: [theta ops | gamma ops | constants] of the run-time programs (VM), then the reference window
+  extern __shared__ __align__(16) unsigned char cat_mpc_smem[];
   CatMpcVm<T> vm;
   if constexpr (VM) {   // stage both programs into shared memory once per block
-    extern __shared__ __align__(16) unsigned char cat_mpc_smem[];
     int2* s_ops = reinterpret_cast<int2*>(cat_mpc_smem);
     T* s_c = reinterpret_cast<T*>(s_ops + q.n_ops_t + q.n_ops_g);
     for (int i = threadIdx.x; i < q.n_ops_t + q.n_ops_g; i += blockDim.x) s_ops[i] = q.prog[i];
     for (int i = threadIdx.x; i < q.n_c_t + q.n_c_g; i += blockDim.x) s_c[i] = T(q.prog_consts[i]);
-    __syncthreads();
     vm.ops_t = s_ops;
     vm.ops_g = s_ops + q.n_ops_t;
     vm.c_t = s_c;
@@ -398,6 +398,16 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   const unsigned long long seed_eff = q.seed + (unsigned long long)(q.step ? *q.step : 0);
   const int ref_rem = q.ref_len - t0;   // rows left in the reference trajectory; the last one is held
   const double* pr = p_ref + ((long long)prob * q.ref_len + t0) * 3;
+  // The H reference points of this launch, in the compute type, staged once per block: the loop reads them with a
+  // broadcast LDS.  (Fetched from global memory one step ahead into loop-carried registers, the move that rotates the
+  // register waits for the load: round-2 ncu of the fp32 kernel, 60% of its long-scoreboard samples.)
+  T* const s_ref = reinterpret_cast<T*>(cat_mpc_smem + q.ref_smem_off);
+  for (int i = threadIdx.x; i < 3 * q.H; i += blockDim.x) {
+    const int hh = i / 3;
+    const int row = hh < ref_rem ? hh : ref_rem - 1;
+    s_ref[i] = T(pr[3 * row + (i - 3 * hh)]);
+  }
+  __syncthreads();   // programs (VM) and reference window are in place
 
   // Scaled features and stage-1 slopes of the CURRENT state.  They are carried across steps: the
   // stage-4 feature row of step h equals the stage-1 row of step h+1 except for the theta/gamma
@@ -423,8 +433,6 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   // issued ~40% into the step) does NOT (~1,000 cycles of DRAM latency at the natural clock; round-1 ncu: 3.2
   // long-scoreboard stall cycles per issued instruction): it keeps CAT_MPC_PF steps in flight through cp.async.
   S Vq[3] = {S(0), S(0), S(0)};
-  double Rnext[3];   // as loaded: the fp32 kernel converts at USE, one step later (a conversion next to the load
-                     // waits for it: round-2 ncu, 55% of that kernel's remaining long-scoreboard samples)
   int slot = 0;          // ASYNC: ring slot of step h
   int slot_in = 0;       // ASYNC: ring slot the next prefetch lands in
   if constexpr (ASYNC) {
@@ -447,18 +455,15 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     Vq[2] = uc[2 * q.sa];
     uc += q.sh;
   }
-  Rnext[0] = pr[0];
-  Rnext[1] = pr[1];
-  Rnext[2] = pr[2];
 
   for (int h = 0; h < q.H; ++h) {
     T Vn[3];
     if constexpr (RNG) {
       if (q.u_nom)
-        cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + kk, h, cat_icdf_ref<T, RNG>(s_icdf), Vn);
+        cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + kk, h, icdf, Vn);
       else
         cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
-                                 (uint32_t)h, q.sigma, q.clip, cat_icdf_ref<T, RNG>(s_icdf), Vn);
+                                 (uint32_t)h, q.sigma, q.clip, icdf, Vn);
     } else if constexpr (ASYNC) {
       // the group of step h is the oldest of the CAT_MPC_PF in flight
       cat_cp_async_wait<CAT_MPC_PF - 1>();
@@ -472,16 +477,8 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       Vn[1] = T(Vq[1]);
       Vn[2] = T(Vq[2]);
     }
-    const T Rh[3] = {T(Rnext[0]), T(Rnext[1]), T(Rnext[2])};
-    if constexpr (RNG) {
-      // unconditional (the last step re-reads its own row): no branch at the top of the loop body.  Measured
-      // on one box (tools/ab.sh): 0.1693 -> 0.1677 ms here, but 0.1054 -> 0.1088 ms with the control loads
-      // of the explicit form below, which therefore keeps its branch.
-      pr += (h + 1 < q.H && h + 1 < ref_rem) ? 3 : 0;
-      Rnext[0] = pr[0];
-      Rnext[1] = pr[1];
-      Rnext[2] = pr[2];
-    } else if constexpr (ASYNC) {
+    const T Rh[3] = {s_ref[3 * h], s_ref[3 * h + 1], s_ref[3 * h + 2]};
+    if constexpr (ASYNC) {
       if (h + CAT_MPC_PF < q.H) {   // step h + PF into the slot that was read PF + 1 steps ago
         S* d = reinterpret_cast<S*>(s_ring.v) + threadIdx.x + (slot_in * 3) * CAT_MPC_BLOCK;
         cat_cp_async<S>(d, uc);
@@ -491,22 +488,12 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       }
       cat_cp_async_commit();
       slot_in = slot_in == CAT_MPC_PF ? 0 : slot_in + 1;
+    } else if constexpr (!RNG) {
       if (h + 1 < q.H) {
-        if (h + 1 < ref_rem) pr += 3;
-        Rnext[0] = pr[0];
-        Rnext[1] = pr[1];
-        Rnext[2] = pr[2];
-      }
-    } else {
-      if (h + 1 < q.H) {   // one branch for both fetches (the form the fp64 kernel was tuned with)
         Vq[0] = uc[0];
         Vq[1] = uc[q.sa];
         Vq[2] = uc[2 * q.sa];
         uc += q.sh;
-        if (h + 1 < ref_rem) pr += 3;
-        Rnext[0] = pr[0];
-        Rnext[1] = pr[1];
-        Rnext[2] = pr[2];
       }
     }
     T Pn[3], An[3];
@@ -596,6 +583,15 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     }
   }
 
+  // Programmatic dependent launch (the host launches with cudaLaunchAttributeProgrammaticStreamSerialization): once
+  // every block of this grid is past its horizon loop, the NEXT rollout on the stream may start filling the SMs that
+  // this grid's early finishers leave idle (65,536 candidates are 3.46 blocks per SM: the 3-block SMs wait ~20% of
+  // the launch for the 4-block ones) and runs under this grid's reduction / exchange tail.  Before a block touches
+  // anything the previous grid may still be using -- cost vector, per-block winner slots, tickets, result buffers --
+  // it waits for that grid to have completed; by then (a whole horizon later) it has, so the wait is free.
+  // Both instructions are no-ops in a launch without the attribute.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   if (live && costs) costs[(long long)prob * q.K + k] = J;
 
   // ---- argmin over the candidates of this problem ----
@@ -658,7 +654,7 @@ __global__ void __launch_bounds__(256) k_sample_controls(const CatMpcDev<T> q, T
   const int h = blockIdx.y, prob = blockIdx.z;
   T v[3];
   cat_sample_control<T, M>(q.seed, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + k), (uint32_t)h,
-                           q.sigma, q.clip, s_icdf, v);
+                           q.sigma, q.clip, cat_icdf_ref_of<T>(s_icdf), v);
   T* o = out + (((long long)prob * q.H + h) * 3) * q.K + k;
   o[0] = v[0];
   o[q.K] = v[1];

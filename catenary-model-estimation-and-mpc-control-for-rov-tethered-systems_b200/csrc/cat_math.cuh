@@ -762,6 +762,13 @@ __device__ __forceinline__ void cat_icdf_stage(CatIcdfSmem<T>& sm) {
   __syncthreads();
 }
 
+// The table is addressed through its 32-bit shared-window offset, taken ONCE per kernel: with a generic pointer the
+// compiler re-derived the window base (S2UR + UMOV + ULEA) in front of every lookup -- three issue slots per normal.
+typedef unsigned CatIcdfRef;
+template <typename T> __device__ __forceinline__ CatIcdfRef cat_icdf_ref_of(const CatIcdfSmem<T>& sm) {
+  return (unsigned)__cvta_generic_to_shared(sm.tab);
+}
+
 // lanes below the shared-memory octaves when the caller's clip reaches past them: the full table in global memory.
 // Kept out of line so that the common path carries one predicated call, not the predicated-off loads and FMAs
 // (round-2 ncu: ~32 of the sampler's instructions per warp-step were this never-taken block, if-converted).
@@ -773,7 +780,7 @@ __device__ __noinline__ T cat_icdf_deep(int seg, T t) {
 
 // clip(z(r), +-clip);  deep: clip > CAT_ICDF_SMEM_ZMAX (warp-uniform)
 template <typename T, typename M>
-__device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& sm, T clip, bool deep) {
+__device__ __forceinline__ T cat_icdf_normal(uint32_t r, CatIcdfRef tab, T clip, bool deep) {
   const uint32_t flip = (uint32_t)((int)r >> 31);          // 0xffffffff for r >= 2^31
   uint32_t rp = r ^ flip;                                   // r' = r < 2^31 ? r : ~r
   rp = rp < 32u ? 32u : rp;
@@ -796,14 +803,13 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& s
   // row of the shared table: 1 + segment above the first hot octave; everything below lands on row 0, whose constant
   // 4 exceeds every clip the shared table serves, so the clamp below turns it into +-clip without a select here
   const int row = seg - ((CAT_ICDF_SMEM_E_LO - CAT_ICDF_E_LO) * 32 - 1);
-  const T* c = sm.tab + 4 * (row < 0 ? 0 : row);
-  T c0, c1, c2, c3;
+  const unsigned at = tab + (unsigned)(row < 0 ? 0 : row) * (unsigned)(4 * sizeof(T));
+  T c0, c1, c2, c3;   // volatile: must stay behind the barrier that ends the table's staging
   if constexpr (sizeof(T) == 8) {
-    const double2 a = *reinterpret_cast<const double2*>(c), b2 = *reinterpret_cast<const double2*>(c + 2);
-    c0 = a.x; c1 = a.y; c2 = b2.x; c3 = b2.y;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(c0), "=d"(c1) : "r"(at));
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+16];" : "=d"(c2), "=d"(c3) : "r"(at));
   } else {
-    const float4 a = *reinterpret_cast<const float4*>(c);
-    c0 = a.x; c1 = a.y; c2 = a.z; c3 = a.w;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(c0), "=f"(c1), "=f"(c2), "=f"(c3) : "r"(at));
   }
   T y = M::fma_(M::fma_(M::fma_(c3, t, c2), t, c1), t, c0);
   if (deep) {               // warp-uniform; false in every BASELINE config
@@ -821,7 +827,7 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, const CatIcdfSmem<T>& s
 // three clipped normals scaled by sigma, keyed by (seed, problem, global k, h): Philox words 0..2 -> axes x, y, z
 template <typename T, typename M>
 __device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t problem, uint64_t k, uint32_t h,
-                                                   const T sigma[3], T clip, const CatIcdfSmem<T>& sm, T out[3]) {
+                                                   const T sigma[3], T clip, CatIcdfRef sm, T out[3]) {
   uint32_t r[4];
   cat_philox4x32_10((uint32_t)k, (uint32_t)(k >> 32), h, problem, (uint32_t)seed, (uint32_t)(seed >> 32), r);
   const bool deep = clip > T(CAT_ICDF_SMEM_ZMAX);

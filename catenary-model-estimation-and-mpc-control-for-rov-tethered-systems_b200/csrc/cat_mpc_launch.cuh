@@ -13,6 +13,7 @@ struct CatMpcLaunchArgs {
   cudaStream_t stream;
   bool rng;          // controls drawn on the device
   bool controls_f32; // explicit controls stored as float while T = double
+  bool pdl;          // programmatic stream serialization: may start under the tail of the preceding rollout
 };
 
 // one launch of k_mpc_rollout<T, S, ...>; returns the cudaError_t of the launch

@@ -282,6 +282,7 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.prog = nullptr;
   q.prog_consts = nullptr;
   q.n_ops_t = q.n_ops_g = q.n_c_t = q.n_c_g = 0;
+  q.ref_smem_off = 0;
   q.p2p.peers = nullptr;
   q.p2p.rank = 0;
   q.p2p.n_ranks = 1;
@@ -315,6 +316,12 @@ int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, 
   a.stream = c->stream;
   a.rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
   a.controls_f32 = (q.flags & CAT_MPC_CONTROLS_F32) != 0;
+  a.pdl = false;
+  if (c->overlap) {   // not inside a stream capture (the controller's graph): plain kernel nodes there
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(c->stream, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone) a.pdl = true;
+    else cudaGetLastError();
+  }
   NEED(q.p2p.peers == nullptr || q.p2p.n_ranks <= a.block);
   const size_t n_bb = (size_t)a.grid.x * a.grid.y;
   if (!bb && c->ws) {
@@ -333,14 +340,21 @@ int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, 
     tk = (unsigned int*)pp;
   }
   const bool shipped = (q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED);
-  a.smem = q.prog ? (size_t)(q.n_ops_t + q.n_ops_g) * sizeof(int2) + (size_t)(q.n_c_t + q.n_c_g + 2) * sizeof(T) : 0;
+  // dynamic shared memory: run-time programs (if any), then the H reference points in the compute type
+  const size_t b_prog =
+      q.prog ? (size_t)(q.n_ops_t + q.n_ops_g) * sizeof(int2) + (size_t)(q.n_c_t + q.n_c_g + 2) * sizeof(T) : 0;
+  CatMpcDev<T> ql = q;
+  ql.ref_smem_off = (int)((b_prog + 15) & ~(size_t)15);
+  a.smem = (size_t)ql.ref_smem_off + (size_t)q.H * 3 * sizeof(T);
+  if (a.smem > 48 * 1024)
+    return fail(c, CAT_EINVAL, "horizon (and equation programs) do not fit the rollout's 48 KB of shared memory");
   int e;
   if (q.prog)   // run-time equation programs
-    e = cat_mpc_launch_inst<T, CAT_KIND_VM>(a, q, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
+    e = cat_mpc_launch_inst<T, CAT_KIND_VM>(a, ql, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
   else if (shipped)
-    e = cat_mpc_launch_inst<T, CAT_KIND_SHIPPED>(a, q, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
+    e = cat_mpc_launch_inst<T, CAT_KIND_SHIPPED>(a, ql, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
   else
-    e = cat_mpc_launch_inst<T, CAT_KIND_GENERIC>(a, q, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
+    e = cat_mpc_launch_inst<T, CAT_KIND_GENERIC>(a, ql, problems, controls, p_ref, costs, bb, tk, best_cost, best_idx);
   ++c->launches;
   if (e != (int)cudaSuccess) return fail(c, CAT_ECUDA, "kernel launch (k_mpc_rollout)", (cudaError_t)e);
   return CAT_OK;
@@ -972,6 +986,8 @@ int cat_init(int device, void** ctx) {
   c->mpc_block = 0;
   c->h_stage = c->d_stage = nullptr;
   c->ws = nullptr;
+  c->overlap = 1;
+  if (const char* e = std::getenv("CAT_MPC_OVERLAP")) c->overlap = std::atoi(e) != 0;
   c->n_reg = 0;
   c->nvtx = 0;
   if (const char* e = std::getenv("CAT_NVTX")) c->nvtx = std::atoi(e) != 0;
@@ -1139,6 +1155,12 @@ int cat_mpc_workspace_destroy(void* ctx, void* ws) {
 int cat_set_workspace(void* ctx, void* ws_or_null) {
   CTX();
   c->ws = ws_or_null;
+  return CAT_OK;
+}
+
+int cat_set_overlap(void* ctx, int on) {
+  CTX();
+  c->overlap = on ? 1 : 0;
   return CAT_OK;
 }
 

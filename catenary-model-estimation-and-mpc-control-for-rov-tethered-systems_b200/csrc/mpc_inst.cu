@@ -18,16 +18,28 @@ int cat_mpc_launch_inst<InstT, CAT_INST_KIND>(const CatMpcLaunchArgs& a, const C
                                               const CatMpcProblem* problems, const void* controls,
                                               const double* p_ref, InstT* costs, CatBest* bb, unsigned int* tk,
                                               double* best_cost, long long* best_idx) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = a.grid;
+  cfg.blockDim = dim3((unsigned)a.block, 1, 1);
+  cfg.dynamicSmemBytes = a.smem;
+  cfg.stream = a.stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = a.pdl ? 1 : 0;
+  cudaError_t e;
   if (a.rng) {
-    k_mpc_rollout<InstT, InstT, kGen, kVm, true><<<a.grid, a.block, a.smem, a.stream>>>(
-        q, problems, (const InstT*)nullptr, p_ref, costs, bb, tk, best_cost, best_idx);
+    e = cudaLaunchKernelEx(&cfg, k_mpc_rollout<InstT, InstT, kGen, kVm, true>, q, problems, (const InstT*)nullptr, p_ref,
+                           costs, bb, tk, best_cost, best_idx);
   } else if (sizeof(InstT) == 8 && a.controls_f32) {
-    k_mpc_rollout<InstT, float, kGen, kVm, false><<<a.grid, a.block, a.smem, a.stream>>>(
-        q, problems, (const float*)controls, p_ref, costs, bb, tk, best_cost, best_idx);
+    e = cudaLaunchKernelEx(&cfg, k_mpc_rollout<InstT, float, kGen, kVm, false>, q, problems, (const float*)controls,
+                           p_ref, costs, bb, tk, best_cost, best_idx);
   } else {
-    k_mpc_rollout<InstT, InstT, kGen, kVm, false><<<a.grid, a.block, a.smem, a.stream>>>(
-        q, problems, (const InstT*)controls, p_ref, costs, bb, tk, best_cost, best_idx);
+    e = cudaLaunchKernelEx(&cfg, k_mpc_rollout<InstT, InstT, kGen, kVm, false>, q, problems, (const InstT*)controls,
+                           p_ref, costs, bb, tk, best_cost, best_idx);
   }
+  if (e != cudaSuccess) return (int)e;
   return (int)cudaGetLastError();
 }
 

@@ -138,6 +138,12 @@ CAT_API int cat_host_unregister(void* ctx, void* p);
 CAT_API int cat_mpc_workspace_create(void* ctx, int64_t max_candidates, int32_t max_problems, void** ws);
 CAT_API int cat_mpc_workspace_destroy(void* ctx, void* ws);
 CAT_API int cat_set_workspace(void* ctx, void* ws_or_null);
+/* Rollout kernels are launched with programmatic stream serialization (default on; env CAT_MPC_OVERLAP=0 or on = 0
+ * turns it off): back-to-back steps on one stream overlap -- the next step's candidates start on the SMs the previous
+ * step's early finishers leave idle and run under its reduction / exchange tail.  Stream order is kept for everything a
+ * caller can observe: a step touches its outputs and the shared scratch only after the preceding step has completed,
+ * and a step that follows any other kind of work on the stream (a copy, another library's kernel) starts after it. */
+CAT_API int cat_set_overlap(void* ctx, int on);
 /* cold-path counters of the rollout kernel (bench.py "sensitivity"): enable != 0 switches counting on, 0 off;
  * out (may be NULL) receives, summed over every rollout launched by this process since the last reset:
  * [0] warp-level entries into the catenary solve's iteration loop (the warm Halley step did not suffice),

@@ -632,3 +632,47 @@ def test_cold_path_counters(cb):
     assert loud["solve_cold"] > 4 * (K // 32) and loud["sine_cold"] > 0, loud
     warp_steps = (K // 32) * H
     assert loud["solve_cold"] <= warp_steps and loud["sine_cold"] <= 4 * warp_steps
+
+
+def test_back_to_back_steps_overlap_safely(cb):
+    """Programmatic dependent launch (cat_set_overlap, default on): a run of steps enqueued on one stream without a
+    host sync overlaps -- each winner lands in its own buffer, and the SHARED cost vector, winner slots and tickets
+    are touched by a step only after its predecessor has completed.  Same results as with the overlap switched off."""
+    import importlib
+    import torch
+    dev = importlib.import_module(cb.__name__ + ".device")
+    K, H = 30_000, 25
+    p = cb.default_mpc_params()
+    pref = cb.circle_reference(H, p["dt"])
+    ctx = cb.Context(0)
+    sets = [torch.from_numpy(np.ascontiguousarray(_controls(K, H, 70 + i).transpose(1, 2, 0))).cuda() for i in range(3)]
+    st = dev.MpcDeviceStep(p, pref, K, controls=sets[0].cpu().numpy(), keep_costs=True, ctx=ctx)
+    ctx.set_overlap(False)
+    want, want_costs = [], []
+    for U in sets:
+        st.set_controls(U)
+        st.launch()
+        i, c = st.result()
+        want.append((int(i[0]), float(c[0])))
+        want_costs.append(st.costs.cpu().numpy().copy())
+    ctx.set_overlap(True)
+    n = 60
+    wins = [torch.zeros(2, dtype=torch.int64, device="cuda") for _ in range(n)]
+    for j in range(n):
+        st.set_controls(sets[j % 3])
+        st.launch(winner=wins[j])
+    torch.cuda.synchronize()
+    for j in range(n):
+        w = wins[j].cpu().numpy()
+        assert (int(w[1]), float(w[:1].view(np.float64)[0])) == want[j % 3], j
+    assert np.array_equal(st.costs.cpu().numpy(), want_costs[(n - 1) % 3])
+    # a different kind of work between two steps: plain stream order
+    for j in range(6):
+        st.set_controls(sets[j % 3])
+        st.launch(winner=wins[j])
+        wins[j + 10].copy_(wins[j])
+    torch.cuda.synchronize()
+    for j in range(6):
+        assert torch.equal(wins[j + 10], wins[j])
+        assert int(wins[j].cpu()[1]) == want[j % 3][0]
+    st.close()
