@@ -341,6 +341,12 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
               unsigned int* __restrict__ tickets, double* __restrict__ best_cost,
               long long* __restrict__ best_idx) {
   typedef CatMath<T> M;
+  // Programmatic dependent launch (the host launches with cudaLaunchAttributeProgrammaticStreamSerialization): as
+  // soon as every block of this grid is resident, the NEXT rollout on the stream may start on whatever the grid
+  // leaves free -- 65,536 candidates are 512 blocks on 592 slots, and the 3-block SMs finish ~20% before the 4-block
+  // ones -- and it runs under this grid's reduction / exchange tail.  Inputs of consecutive steps are independent;
+  // everything shared is guarded by the griddepcontrol.wait behind the horizon loop.  No-ops without the attribute.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   // inverse-CDF table of the device sampler (hot octaves), staged once per block
   __shared__ typename CatIcdfSlot<T, RNG>::type s_icdf;
   CatIcdfRef icdf = 0;
@@ -583,14 +589,9 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     }
   }
 
-  // Programmatic dependent launch (the host launches with cudaLaunchAttributeProgrammaticStreamSerialization): once
-  // every block of this grid is past its horizon loop, the NEXT rollout on the stream may start filling the SMs that
-  // this grid's early finishers leave idle (65,536 candidates are 3.46 blocks per SM: the 3-block SMs wait ~20% of
-  // the launch for the 4-block ones) and runs under this grid's reduction / exchange tail.  Before a block touches
-  // anything the previous grid may still be using -- cost vector, per-block winner slots, tickets, result buffers --
-  // it waits for that grid to have completed; by then (a whole horizon later) it has, so the wait is free.
-  // Both instructions are no-ops in a launch without the attribute.
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // Before a block touches anything the previous grid on the stream may still be using -- cost vector, per-block
+  // winner slots, tickets, result buffers -- it waits for that grid to have completed (programmatic dependent
+  // launch, see the top of the kernel); a whole horizon after its own start it has, so the wait is free.
   asm volatile("griddepcontrol.wait;" ::: "memory");
   if (live && costs) costs[(long long)prob * q.K + k] = J;
 
