@@ -555,12 +555,22 @@ def run_ours(args):
                                         "rollout starts after the previous one has retired -- the round-1 launch mode"},
            "clocks": clocks, "e2e": e2e, "configs": configs, "gpu_launches": int(launches),
            "exchange_check": exchange_check, "fused_lockstep": lock_cmp, "nccl_exchange": nccl_cmp}
+    def add_steady(o):
+        # the same executed-work accounting over the timed region of `value`: with programmatic dependent launch the
+        # launches overlap, so a step costs ms_per_step of the pipe's time, not a lone launch's duration
+        r = o["roofline"]
+        fpw = r["executed"]["fp64_inst_per_warp_step"]
+        rate = (K / 32.0) * H / (ms_per_step * 1e-3) * 32.0 * fpw
+        r["steady_state"] = {"ms_per_step": ms_per_step, "achieved": rate / 1e12, "frac": rate / (r["peak"] * 1e12),
+                             "what": "FP64 thread-instructions per second of ONE GPU over the back-to-back loop that "
+                                     "`value` times, against the same measured DFMA rate"}
+        return o
     if world == 1:
-        out.update(single_gpu_legs(torch, cb, devmod, ctx, step, p, pref, sigma, host_sets, host32, dev_sets, clocks,
-                                   hbm_peak, hbm_src, value, local))
+        out.update(add_steady(single_gpu_legs(torch, cb, devmod, ctx, step, p, pref, sigma, host_sets, host32, dev_sets, clocks,
+                                   hbm_peak, hbm_src, value, local)))
     else:
         # the roofline of the dominant kernel still belongs on every line; the long single-GPU legs do not
-        out.update(roofline_leg(torch, ctx, step, dev_sets, clocks, hbm_peak, hbm_src))
+        out.update(add_steady(roofline_leg(torch, ctx, step, dev_sets, clocks, hbm_peak, hbm_src)))
         out["cpu_baseline"] = None
     emit(json.dumps(out))
     if world > 1:

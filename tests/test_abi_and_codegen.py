@@ -121,3 +121,29 @@ def test_product_never_imports_oracle():
                 with open(os.path.join(dp, f)) as fh:
                     src = fh.read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+
+
+def test_sampler_table_definition_and_header():
+    """The tabulated inverse normal CDF that DEFINES the device sampler: the oracle's evaluation against
+    scipy.special.ndtri, the first moments of the sampled controls, and the generated CUDA header carrying exactly
+    the numbers of artifacts/icdf_table.json."""
+    from scipy.special import ndtri
+    from oracle import catenary_oracle as orc
+    e_lo, m, coef = orc.icdf_table()
+    assert (e_lo, m) == (5, 5) and coef.shape == (26 * 32, 4)
+    rng = np.random.default_rng(0)
+    r = rng.integers(0, 2 ** 32, size=400_000, dtype=np.uint64).astype(np.uint32)
+    r[:8] = [0, 1, 31, 32, 2 ** 31 - 1, 2 ** 31, 2 ** 32 - 33, 2 ** 32 - 1]            # both tails and the centre
+    z = orc.icdf_normal(r)
+    rp = np.maximum(np.where(r >= 2 ** 31, ~r, r).astype(np.int64), 32)               # the definition clamps r' at 32
+    want = np.where(r >= 2 ** 31, 1.0, -1.0) * -ndtri((rp + 0.5) / 2.0 ** 32)
+    assert np.abs(z - want).max() < 1e-9
+    assert z[5] > 0 > z[4] and abs(z[4] + z[5]) < 1e-12                                # antisymmetric about 2^31
+    assert abs(z.mean()) < 0.01 and abs(z.std() - 1) < 0.01
+    U = orc.sample_controls(77, np.arange(20_000), 12, [108.0, 16.0, 63.0])
+    assert np.abs(U).max(axis=(0, 1)).tolist() == [324.0, 48.0, 189.0]                # clipped at 3 sigma exactly
+    assert np.allclose(U.std(axis=(0, 1)) / [108.0, 16.0, 63.0], 0.9975, atol=0.01)   # std of a normal clipped at 3 sigma
+    cg = importlib.import_module(PKG + ".codegen")
+    text = open(cg.generate_icdf()).read()
+    nums = [float(x) for x in text.split("{", 1)[1].split("}", 1)[0].replace("\n", " ").split(",") if x.strip()]
+    assert np.array_equal(np.array(nums).reshape(-1, 4), coef)
