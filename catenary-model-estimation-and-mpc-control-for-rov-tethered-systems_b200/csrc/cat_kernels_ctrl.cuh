@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(256) k_ctrl_mppi(const CatMpcDev<T> q, const C
   if (!(jmin == jmin)) {   // NaN winner: fall back to the best candidate itself (weight 1 in slice 0)
     if (threadIdx.x == 0) {
       T u[3] = {T(0), T(0), T(0)};
-      if (z == 0) cat_nominal_control<T, M>(q, seed_eff, prob, best_idx[prob], h, s_icdf, u);
+      if (z == 0) cat_nominal_control<T, M>(q, seed_eff, prob, best_idx[prob], h, s_icdf, q.clip, u);
       out[0] = (double)u[0];
       out[1] = (double)u[1];
       out[2] = (double)u[2];
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(256) k_ctrl_mppi(const CatMpcDev<T> q, const C
     double w = exp((j - jmin) * inv_l);
     if (!(j == j)) w = 0.0;
     T u[3];
-    cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + k, h, s_icdf, u);
+    cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + k, h, s_icdf, q.clip, u);
     acc[0] += w * (double)u[0];
     acc[1] += w * (double)u[1];
     acc[2] += w * (double)u[2];
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(64) k_ctrl_advance(const CatMpcDev<T> q, const
       s_u[3 * h + 2] = a2 / aw;
     } else {
       T u[3];
-      cat_nominal_control<T, M>(q, seed_eff, prob, bi, h, s_icdf, u);
+      cat_nominal_control<T, M>(q, seed_eff, prob, bi, h, s_icdf, q.clip, u);
       s_u[3 * h + 0] = (double)u[0];
       s_u[3 * h + 1] = (double)u[1];
       s_u[3 * h + 2] = (double)u[2];

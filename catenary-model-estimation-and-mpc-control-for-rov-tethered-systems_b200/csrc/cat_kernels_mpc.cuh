@@ -114,9 +114,9 @@ template <int N> __device__ __forceinline__ void cat_cp_async_wait() {
 // global candidate 0 carries no noise (oracle ctrl_candidates)
 template <typename T, typename M>
 __device__ __forceinline__ void cat_nominal_control(const CatMpcDev<T>& q, unsigned long long seed_eff, int prob,
-                                                    long long kglob, int h, CatIcdfRef icdf, T out[3]) {
+                                                    long long kglob, int h, CatIcdfRef icdf, T clip, T out[3]) {
   cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)kglob, (uint32_t)h, q.sigma,
-                           q.clip, icdf, out);
+                           clip, icdf, out);
   const double* un = q.u_nom + ((long long)prob * q.H + h) * 3;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
@@ -352,8 +352,9 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   CatIcdfRef icdf = 0;
   if constexpr (RNG) {
     cat_icdf_stage<T>(s_icdf);
-    icdf = cat_icdf_ref_of<T>(s_icdf);
+    icdf = cat_pin(cat_icdf_ref_of<T>(s_icdf));
   }
+  const T clip_r = RNG ? cat_pin(q.clip) : q.clip;
   constexpr bool ASYNC = !RNG && (sizeof(T) == 4 || CAT_MPC_ASYNC_F64 != 0);
   __shared__ __align__(16) CatRing<S, ASYNC> s_ring;
   // dynamic shared memory: [theta ops | gamma ops | constants] of the run-time programs (VM), then the reference window
@@ -466,10 +467,10 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     T Vn[3];
     if constexpr (RNG) {
       if (q.u_nom)
-        cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + kk, h, icdf, Vn);
+        cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + kk, h, icdf, clip_r, Vn);
       else
         cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
-                                 (uint32_t)h, q.sigma, q.clip, icdf, Vn);
+                                 (uint32_t)h, q.sigma, clip_r, icdf, Vn);
     } else if constexpr (ASYNC) {
       // the group of step h is the oldest of the CAT_MPC_PF in flight
       cat_cp_async_wait<CAT_MPC_PF - 1>();

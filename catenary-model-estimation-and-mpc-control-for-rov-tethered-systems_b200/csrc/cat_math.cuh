@@ -778,9 +778,9 @@ __device__ __noinline__ T cat_icdf_deep(int seg, T t) {
   return M::fma_(M::fma_(M::fma_(T(__ldg(g + 3)), t, T(__ldg(g + 2))), t, T(__ldg(g + 1))), t, T(__ldg(g)));
 }
 
-// clip(z(r), +-clip);  deep: clip > CAT_ICDF_SMEM_ZMAX (warp-uniform)
-template <typename T, typename M>
-__device__ __forceinline__ T cat_icdf_normal(uint32_t r, CatIcdfRef tab, T clip, bool deep) {
+// clip(z(r), +-clip);  DEEP: clip > CAT_ICDF_SMEM_ZMAX, lanes below the hot octaves read the full table
+template <typename T, typename M, bool DEEP>
+__device__ __forceinline__ T cat_icdf_normal(uint32_t r, CatIcdfRef tab, T clip) {
   const uint32_t flip = (uint32_t)((int)r >> 31);          // 0xffffffff for r >= 2^31
   uint32_t rp = r ^ flip;                                   // r' = r < 2^31 ? r : ~r
   rp = rp < 32u ? 32u : rp;
@@ -812,7 +812,7 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, CatIcdfRef tab, T clip,
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(c0), "=f"(c1), "=f"(c2), "=f"(c3) : "r"(at));
   }
   T y = M::fma_(M::fma_(M::fma_(c3, t, c2), t, c1), t, c0);
-  if (deep) {               // warp-uniform; false in every BASELINE config
+  if constexpr (DEEP) {
     if (row <= 0) y = cat_icdf_deep<T, M>(seg, t);
   }
   // |z| clipped BEFORE the sign goes on (y >= 0, never NaN: one compare and two selects), then z = r >= 2^31 ? y : -y
@@ -824,13 +824,43 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, CatIcdfRef tab, T clip,
     return __int_as_float(__float_as_int(y) ^ (int)(~flip & 0x80000000u));
 }
 
-// three clipped normals scaled by sigma, keyed by (seed, problem, global k, h): Philox words 0..2 -> axes x, y, z
+template <typename T, typename M>
+__device__ __noinline__ T cat_icdf_normal_deep(uint32_t r, CatIcdfRef tab, T clip) {   // out of line: rare, and small
+  return cat_icdf_normal<T, M, true>(r, tab, clip);
+}
+
+// three clipped normals scaled by sigma, keyed by (seed, problem, global k, h): Philox words 0..2 -> axes x, y, z.
+// The deep-tail form (clip beyond the shared octaves; no BASELINE config) is a separate instance behind ONE
+// warp-uniform branch per call, so the common one carries no per-normal test, branch or reconvergence point.
 template <typename T, typename M>
 __device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t problem, uint64_t k, uint32_t h,
                                                    const T sigma[3], T clip, CatIcdfRef sm, T out[3]) {
   uint32_t r[4];
   cat_philox4x32_10((uint32_t)k, (uint32_t)(k >> 32), h, problem, (uint32_t)seed, (uint32_t)(seed >> 32), r);
-  const bool deep = clip > T(CAT_ICDF_SMEM_ZMAX);
+  if (clip > T(CAT_ICDF_SMEM_ZMAX)) {
 #pragma unroll
-  for (int a = 0; a < 3; ++a) out[a] = cat_icdf_normal<T, M>(r[a], sm, clip, deep) * sigma[a];
+    for (int a = 0; a < 3; ++a) out[a] = cat_icdf_normal_deep<T, M>(r[a], sm, clip) * sigma[a];
+  } else {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) out[a] = cat_icdf_normal<T, M, false>(r[a], sm, clip) * sigma[a];
+  }
+}
+
+// A loop-invariant the compiler must not re-derive inside the loop: the value goes through an opaque move, so it
+// occupies registers instead of being rebuilt from the constant bank / special registers at every use (the sampler's
+// table address cost S2UR + UMOV + ULEA per lookup, its clip two LDCU per normal).
+__device__ __forceinline__ unsigned cat_pin(unsigned v) {
+  unsigned o;
+  asm volatile("mov.u32 %0, %1;" : "=r"(o) : "r"(v));
+  return o;
+}
+__device__ __forceinline__ double cat_pin(double v) {
+  double o;
+  asm volatile("mov.f64 %0, %1;" : "=d"(o) : "d"(v));
+  return o;
+}
+__device__ __forceinline__ float cat_pin(float v) {
+  float o;
+  asm volatile("mov.f32 %0, %1;" : "=f"(o) : "f"(v));
+  return o;
 }
