@@ -463,6 +463,12 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     uc += q.sh;
   }
 
+#ifndef CAT_MPC_UNROLL
+#define CAT_MPC_UNROLL 1   // A/B switch: 2 removes the ~38 loop-carried register moves per step, at twice the loop body
+#endif
+#define CAT_PRAGMA_(x) _Pragma(#x)
+#define CAT_UNROLL_(n) CAT_PRAGMA_(unroll n)
+  CAT_UNROLL_(CAT_MPC_UNROLL)
   for (int h = 0; h < q.H; ++h) {
     T Vn[3];
     if constexpr (RNG) {

@@ -65,6 +65,10 @@ __constant__ double CAT_LN2_C[4] = {
 // |x| < 1e3); beyond that, and for inf/nan, ONE cold branch per batch to the CUDA routine.  The N Horner
 // chains are interleaved, so each coefficient is fetched once per batch and the DFMA latency of one chain
 // hides behind the others.
+// full-range sine of one argument, out of line: the rollout reaches it only for |x| >= 1e5, inf or NaN, and four
+// inlined copies of the library routine's range logic made up a third of the loop's code
+static __device__ __noinline__ double cat_sin_cold_f64(double x) { return sin(x); }
+
 template <int N>
 __device__ __forceinline__ void cat_sin_vec_f64(double (&a)[N]) {
   double r[N], z[N], p[N];
@@ -97,7 +101,7 @@ __device__ __forceinline__ void cat_sin_vec_f64(double (&a)[N]) {
     cat_dbg_count(1);
 #pragma unroll
     for (int n = 0; n < N; ++n)
-      if ((__double2hiint(a[n]) & 0x7fffffff) >= 0x40F86A00) r[n] = sin(a[n]);
+      if ((__double2hiint(a[n]) & 0x7fffffff) >= 0x40F86A00) r[n] = cat_sin_cold_f64(a[n]);
   }
 #pragma unroll
   for (int n = 0; n < N; ++n) a[n] = r[n];
@@ -391,6 +395,28 @@ template <typename T> struct CatSolve {
   CatWarm<T> rec;    // record to hand to the next solve of the same span
 };
 
+// the iteration loop of the rollout's solve (cold starts, fast-moving spans), out of line: it keeps the loop body of
+// the rollout small, and its cost does not matter where it runs
+template <typename T> struct CatIter {
+  T u, sm, cm, sh, du;
+};
+template <typename T, typename M>
+__device__ __noinline__ CatIter<T> cat_solve_iterate(T u, T N, T D, bool more) {
+  CatIter<T> r;
+  r.u = u;
+  r.sm = r.cm = r.sh = r.du = T(0);
+  int it = 1;
+  // at least one evaluation: the caller's (sm, cm, sh) belong to the point before its last step
+  do {
+    cat_hyp<T, M>(r.u, r.sm, r.cm, r.sh);
+    r.du = cat_halley_step<T, M>(r.u, N, D, r.sm, r.cm, r.sh);
+    r.u -= r.du;
+    more = M::abs_(r.du) > M::step_tol() * (r.u < T(1) ? r.u : T(1));
+    ++it;
+  } while (more && it < 60);
+  return r;
+}
+
 template <typename T, typename M, bool FULL_WARP = false>
 __device__ __forceinline__ CatSolve<T> cat_solve_u(T N, T D, const CatWarm<T>& w) {
   T u;
@@ -420,14 +446,25 @@ __device__ __forceinline__ CatSolve<T> cat_solve_u(T N, T D, const CatWarm<T>& w
   if constexpr (FULL_WARP) again = __any_sync(0xffffffffu, more);   // every lane of the warp is here
   else again = more;
   if (again) {
-    if constexpr (FULL_WARP) cat_dbg_count(0);
-    int it = 1;
-    while (more && it < 60) {
-      cat_hyp<T, M>(u, sm, cm, sh);
-      du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
-      u -= du;
-      more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1));
-      ++it;
+    if constexpr (FULL_WARP) {
+      cat_dbg_count(0);
+      if (more) {   // only the lanes that need it iterate (out of line); the others keep their evaluation
+        const CatIter<T> r = cat_solve_iterate<T, M>(u, N, D, more);
+        u = r.u;
+        sm = r.sm;
+        cm = r.cm;
+        sh = r.sh;
+        du = r.du;
+      }
+    } else {
+      int it = 1;
+      while (more && it < 60) {
+        cat_hyp<T, M>(u, sm, cm, sh);
+        du = cat_halley_step<T, M>(u, N, D, sm, cm, sh);
+        u -= du;
+        more = M::abs_(du) > M::step_tol() * (u < T(1) ? u : T(1));
+        ++it;
+      }
     }
   }
   // (sm, cm, sh) are values at u + du, the point of the last evaluation; |du| <= step_tol * min(u, 1).
