@@ -49,6 +49,10 @@ template <typename T> struct CatShapeGroup { static constexpr int lanes = sizeof
 // -- on one B200 (profiles/r2_ab_shape_vec_stores.txt): fp64 final curve 0.744 vs 0.449 ms, fp32 0.469 vs 0.268 ms.
 // The two warp barriers and the staging traffic per hop cost far more than the narrower stores save; L2 already
 // merges the strided stores into full sectors (DRAM write bytes == algorithmic bytes in the ncu capture).
+// A second form without staging -- each lane owns two consecutive points (the second by a one-sample shift of
+// cosh/sinh) and writes its 48 / 24 bytes as three vectors, half the hops -- lost as well
+// (profiles/r2_ab_shape_pair_stores.txt: fp64 0.618 vs 0.447 ms, fp32 0.296 vs 0.268 ms): every vector store then
+// covers 16 of each 48 bytes of a 1.5 KB window, all sectors partial, and the L2 write path is the bound.
 #define CAT_SHAPE_RESEED 16    // (power of two) re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
 
 template <typename T> struct CatShapeSpan {

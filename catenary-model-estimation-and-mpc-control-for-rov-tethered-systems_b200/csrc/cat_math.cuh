@@ -189,9 +189,6 @@ template <> struct CatMath<double> {
     return __hiloint2double(hi < 0 ? 0 : hi, hi < 0 ? 0 : __double2loint(x));
   }
   static __device__ __forceinline__ void sincos_(double x, double* s, double* c) { sincos(x, s, c); }
-  // sin/cos(2 pi u), u in [0,1): exact argument reduction, no Payne-Hanek path (the Box-Muller angles)
-  static __device__ __forceinline__ void sincos2pi_(double u, double* s, double* c) { sincospi(2.0 * u, s, c); }
-  static __device__ __forceinline__ double cos2pi_(double u) { return cospi(2.0 * u); }
   static __device__ __forceinline__ double tanh_(double x) { return tanh(x); }
   static __device__ __forceinline__ double exp_(double x) { return exp(x); }
   static __device__ __forceinline__ double log_(double x) { return log(x); }
@@ -235,8 +232,6 @@ template <> struct CatMath<float> {
   }
   static __device__ __forceinline__ float pos_(float x) { return x > 0.0f ? x : 0.0f; }
   static __device__ __forceinline__ void sincos_(float x, float* s, float* c) { __sincosf(x, s, c); }
-  static __device__ __forceinline__ void sincos2pi_(float u, float* s, float* c) { __sincosf(6.283185307179586f * u, s, c); }
-  static __device__ __forceinline__ float cos2pi_(float u) { return __cosf(6.283185307179586f * u); }
   static __device__ __forceinline__ float tanh_(float x) {
     float r;
     asm("tanh.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -594,20 +589,6 @@ __device__ __forceinline__ CatSpan<T> cat_span_from(const CatSpanPrep<T>& p, T l
 template <typename T, typename M, bool NEED_C = true, bool FULL_WARP = false>
 __device__ __forceinline__ CatSpan<T> cat_span(T l, T dH, T L, T c_lo, T c_hi, const CatWarm<T>& warm) {
   return cat_span_from<T, M, NEED_C, FULL_WARP>(cat_span_prep<T, M>(l, dH, L), l, dH, L, c_lo, c_hi, warm);
-}
-
-// a span given by its components (rel = B - A): fp64 as cat_span; fp32 with the exact N (see cat_span_prep_exact)
-template <typename T, typename M>
-__device__ __forceinline__ CatSpan<T> cat_span_rel(T rx, T ry, T rz, T L, T c_lo, T c_hi, T& l_out) {
-  const T l = M::sqrt_(rx * rx + ry * ry);
-  l_out = l;
-  if constexpr (sizeof(T) == 4) {
-    const double l2 = (double)rx * (double)rx + (double)ry * (double)ry;
-    return cat_span_from<T, M>(cat_span_prep_exact<M>(l, l2, (double)rz, (double)L), l, rz, L, c_lo, c_hi,
-                               cat_cold<T>());
-  } else {
-    return cat_span<T, M>(l, rz, L, c_lo, c_hi, cat_cold<T>());
-  }
 }
 
 // a span given by (l, dH) as main_fun.solve_catenary takes it
