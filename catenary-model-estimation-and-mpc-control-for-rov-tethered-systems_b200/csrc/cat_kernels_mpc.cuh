@@ -53,6 +53,7 @@ template <typename T> struct CatMpcDev {
   int H, n_problems, flags, problem_offset;
   int eq_theta, eq_gamma;
   int carry_t, carry_g;   // equation reads neither column 14 nor 15: k1 of the next step == k4 of this one
+  int deep_clip;          // clip > CAT_ICDF_SMEM_ZMAX: the sampler's tail lanes read the full table (set by the host)
   T dt, dt_mm, dt6, L, w_trk, w_du, w_len, w_sag, w_ang, rhoL, rhoL2, z_thr, c_lo, c_hi, pen, clip;
   T L2;   // L^2 (sag-term bound)
   T sigma[3];
@@ -116,7 +117,7 @@ template <typename T, typename M>
 __device__ __forceinline__ void cat_nominal_control(const CatMpcDev<T>& q, unsigned long long seed_eff, int prob,
                                                     long long kglob, int h, CatIcdfRef icdf, T clip, T out[3]) {
   cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)kglob, (uint32_t)h, q.sigma,
-                           clip, icdf, out);
+                           clip, q.deep_clip != 0, icdf, out);
   const double* un = q.u_nom + ((long long)prob * q.H + h) * 3;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
@@ -402,7 +403,15 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   // controller mode: the step counter lives in HBM so that one captured graph serves every control step
   int t0 = 0;
   if (q.step) t0 = min(*q.step, q.ref_len - 1);
-  const unsigned long long seed_eff = q.seed + (unsigned long long)(q.step ? *q.step : 0);
+  unsigned long long seed_eff = q.seed + (unsigned long long)(q.step ? *q.step : 0);
+  if constexpr (RNG) {
+    // the key is the same in every lane, but a value loaded from HBM lives in a vector register: the ten Philox round
+    // keys were then re-derived with one integer add per round and lane.  A warp reduction returns it in a uniform
+    // register, and the round keys fold into the uniform operand of the xor.  (All lanes are here: no lane has exited.)
+    const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)seed_eff);
+    const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(seed_eff >> 32));
+    seed_eff = ((unsigned long long)hi << 32) | lo;
+  }
   const int ref_rem = q.ref_len - t0;   // rows left in the reference trajectory; the last one is held
   const double* pr = p_ref + ((long long)prob * q.ref_len + t0) * 3;
   // The H reference points of this launch, in the compute type, staged once per block: the loop reads them with a
@@ -476,7 +485,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
         cat_nominal_control<T, M>(q, seed_eff, prob, q.k_offset + kk, h, icdf, clip_r, Vn);
       else
         cat_sample_control<T, M>(seed_eff, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + kk),
-                                 (uint32_t)h, q.sigma, clip_r, icdf, Vn);
+                                 (uint32_t)h, q.sigma, clip_r, q.deep_clip != 0, icdf, Vn);
     } else if constexpr (ASYNC) {
       // the group of step h is the oldest of the CAT_MPC_PF in flight
       cat_cp_async_wait<CAT_MPC_PF - 1>();
@@ -662,7 +671,7 @@ __global__ void __launch_bounds__(256) k_sample_controls(const CatMpcDev<T> q, T
   const int h = blockIdx.y, prob = blockIdx.z;
   T v[3];
   cat_sample_control<T, M>(q.seed, (uint32_t)(q.problem_offset + prob), (uint64_t)(q.k_offset + k), (uint32_t)h,
-                           q.sigma, q.clip, cat_icdf_ref_of<T>(s_icdf), v);
+                           q.sigma, q.clip, q.deep_clip != 0, cat_icdf_ref_of<T>(s_icdf), v);
   T* o = out + (((long long)prob * q.H + h) * 3) * q.K + k;
   o[0] = v[0];
   o[q.K] = v[1];

@@ -798,10 +798,12 @@ __device__ __noinline__ T cat_icdf_deep(int seg, T t) {
 
 // clip(z(r), +-clip);  DEEP: clip > CAT_ICDF_SMEM_ZMAX, lanes below the hot octaves read the full table
 template <typename T, typename M, bool DEEP>
-__device__ __forceinline__ T cat_icdf_normal(uint32_t r, CatIcdfRef tab, T clip) {
+__device__ __forceinline__ T cat_icdf_normal(uint32_t r, CatIcdfRef tab, T clip, unsigned one_hi = 0x3ff00000u) {
   const uint32_t flip = (uint32_t)((int)r >> 31);          // 0xffffffff for r >= 2^31
   uint32_t rp = r ^ flip;                                   // r' = r < 2^31 ? r : ~r
-  rp = rp < 32u ? 32u : rp;
+  // the clamp to 32 matters where the segment indexes the full table; on the shared table every r' below the hot
+  // octaves (0 included: its exponent field is 0) lands on row 0 through the row clamp further down
+  if constexpr (DEEP) rp = rp < 32u ? 32u : rp;
   int seg;
   T t;
   if constexpr (sizeof(T) == 8) {
@@ -810,7 +812,8 @@ __device__ __forceinline__ T cat_icdf_normal(uint32_t r, CatIcdfRef tab, T clip)
     const unsigned lo = (unsigned)__double2loint(x);
     seg = (hi >> 15) - ((1023 + CAT_ICDF_E_LO) << 5);
     // mantissa bits below the top five, as 1.t - 1
-    const unsigned mh = (__funnelshift_l(lo, (unsigned)hi, 5) & 0x000fffffu) | 0x3ff00000u;
+    unsigned mh;   // (funnel & 0x000fffff) | 0x3ff00000 as ONE three-input logic op (the compiler emits two)
+    asm("lop3.b32 %0, %1, 0x000fffff, %2, 0xea;" : "=r"(mh) : "r"(__funnelshift_l(lo, (unsigned)hi, 5)), "r"(one_hi));
     t = __hiloint2double((int)mh, (int)(lo << 5)) - 1.0;
   } else {
     int b = __float_as_int((float)rp);   // 24-bit rounding moves the sample by < 1e-6 ...
@@ -852,10 +855,10 @@ __device__ __noinline__ T cat_icdf_normal_deep(uint32_t r, CatIcdfRef tab, T cli
 // warp-uniform branch per call, so the common one carries no per-normal test, branch or reconvergence point.
 template <typename T, typename M>
 __device__ __forceinline__ void cat_sample_control(uint64_t seed, uint32_t problem, uint64_t k, uint32_t h,
-                                                   const T sigma[3], T clip, CatIcdfRef sm, T out[3]) {
+                                                   const T sigma[3], T clip, bool deep, CatIcdfRef sm, T out[3]) {
   uint32_t r[4];
   cat_philox4x32_10((uint32_t)k, (uint32_t)(k >> 32), h, problem, (uint32_t)seed, (uint32_t)(seed >> 32), r);
-  if (clip > T(CAT_ICDF_SMEM_ZMAX)) {
+  if (deep) {   // clip > CAT_ICDF_SMEM_ZMAX, decided by the host: a uniform integer test the compiler keeps out of the loop
 #pragma unroll
     for (int a = 0; a < 3; ++a) out[a] = cat_icdf_normal_deep<T, M>(r[a], sm, clip) * sigma[a];
   } else {

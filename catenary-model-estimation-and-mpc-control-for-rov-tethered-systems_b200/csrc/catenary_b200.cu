@@ -277,6 +277,7 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.c_hi = T(p->c_hi);
   q.pen = T(p->nan_penalty);
   q.clip = T(p->clip);
+  q.deep_clip = q.clip > T(CAT_ICDF_SMEM_ZMAX);
   for (int a = 0; a < 3; ++a) q.sigma[a] = T(p->sigma[a]);
   q.seed = p->seed;
   q.prog = nullptr;
