@@ -18,6 +18,7 @@ P2P_LOCKSTEP, P2P_PIPELINED = 0, 1
 ABI_VERSION = 3
 CTRL_ARGMIN, CTRL_MPPI = 0, 1
 CTRL_LOG_W = 16
+STATIC_MAX_BLOCKS, STATIC_MAX_PROBLEMS = 32768, 4096   # cat_mpc_step_static_dev_f64 (fixed device scratch)
 
 
 class CatMpcParams(C.Structure):
@@ -93,6 +94,7 @@ SIGNATURES = {
     "cat_mpc_step_f32": (_int, [_vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cat_mpc_step_dev_f64": (_int, [_vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cat_mpc_step_dev_f32": (_int, [_vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cat_mpc_step_static_dev_f64": (_int, [_vp, _PP, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cat_sample_controls_dev_f64": (_int, [_vp, _PP, _vp]),
     "cat_reduce_winners_f64": (_int, [_int, _vp, _vp, _vp, _vp]),
     "cat_reduce_winners_dev_f64": (_int, [_vp, _int, _vp, _vp]),

@@ -4,6 +4,8 @@
 // host-pointer entry points, kernel launches.  No CPU fallback anywhere: every compute entry point
 // launches a CUDA kernel or fails with CAT_ECUDA.
 #include <cuda_runtime.h>
+
+#include <mutex>
 #include <nvtx3/nvToolsExt.h>
 
 #include <cstdio>
@@ -1975,3 +1977,68 @@ int cat_measure_peak(void* ctx, int kind, double* ops_per_s) {
 }
 
 }  // extern "C"
+
+// =============================================================================================
+// Allocation-free sampling-MPC step (cat_mpc_step_static_dev_f64).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  The rollout's scratch -- one winner slot per thread block and one ticket per problem --
+// lives in a file-scope device array of fixed size instead of the context's grow-on-demand slots; every GPU that
+// loads the library holds its 528 KB until exit.  Every call on a device shares the array: calls that overlap on
+// the GPU (two streams, two contexts) race on it, so they must be ordered by the caller.
+// =============================================================================================
+#define CAT_STR_(x) #x
+#define CAT_STR(x) CAT_STR_(x)
+constexpr int kStaticMaxBlocks = CAT_STATIC_MAX_BLOCKS;       // winner slots: blocks of 128 candidates x problems
+constexpr int kStaticMaxProblems = CAT_STATIC_MAX_PROBLEMS;   // tickets
+constexpr size_t kStaticTicketsAt = (size_t)kStaticMaxBlocks * sizeof(CatBest);
+constexpr size_t kStaticBytes = kStaticTicketsAt + (size_t)kStaticMaxProblems * sizeof(unsigned int);
+static __device__ __align__(256) unsigned char cat_static_scratch[kStaticBytes];
+
+namespace {
+// The array's name is a host-side stand-in in host code, not a device address: the address is resolved once per
+// device, with that device current, and cached.
+std::mutex g_static_mu;
+unsigned char* g_static_addr[64] = {};
+
+int static_scratch_addr(CatCtx* c, unsigned char** out) {
+  NEED(c->device >= 0 && c->device < 64);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_addr[c->device]) {
+    void* p = nullptr;
+    CU(cudaGetSymbolAddress(&p, cat_static_scratch));   // the caller has made c->device current (bind)
+    if (!p) return fail(c, CAT_ECUDA, "cudaGetSymbolAddress(cat_static_scratch) returned null");
+    g_static_addr[c->device] = (unsigned char*)p;
+  }
+  *out = g_static_addr[c->device];
+  return CAT_OK;
+}
+}  // namespace
+
+extern "C" int cat_mpc_step_static_dev_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+                                           const double* controls, const double* p_ref, double* best_cost,
+                                           int64_t* best_idx, double* costs) {
+  CTX();
+  int rc = bind(c);
+  if (rc) return rc;
+  CatMpcDev<double> q;
+  rc = mpc_fill<double>(c, p, q);
+  if (rc) return rc;
+  const bool rng = (p->flags & CAT_MPC_RNG_CONTROLS) != 0;
+  NEED(problems && p_ref && best_cost && best_idx && (rng || controls));
+  const long long n_blocks = (long long)nblk(q.K, mpc_block_size(c, q.K, q.n_problems)) * q.n_problems;
+  if (n_blocks > kStaticMaxBlocks || q.n_problems > kStaticMaxProblems)
+    return fail(c, CAT_EINVAL,
+                "cat_mpc_step_static_dev_f64: step exceeds the static scratch (at most " CAT_STR(CAT_STATIC_MAX_BLOCKS)
+                " thread blocks of 128 candidates summed over the problems, at most " CAT_STR(CAT_STATIC_MAX_PROBLEMS)
+                " problems); use cat_mpc_step_dev_f64");
+  unsigned char* base = nullptr;
+  rc = static_scratch_addr(c, &base);
+  if (rc) return rc;
+  CatBest* bb = reinterpret_cast<CatBest*>(base);
+  unsigned int* tk = reinterpret_cast<unsigned int*>(base + kStaticTicketsAt);
+  // the array keeps the last call's contents: the tickets must start at zero (the winner slots are written before
+  // they are read).  Stream-ordered, so the rollout below sees them cleared.
+  CU(cudaMemsetAsync(tk, 0, (size_t)q.n_problems * sizeof(unsigned int), c->stream));
+  CatNvtxRange r(c, "cat_mpc_step_static_dev");
+  return mpc_launch<double>(c, q, problems, controls, p_ref, best_cost, (long long*)best_idx, costs, bb, tk);
+}

@@ -243,6 +243,20 @@ CAT_API int cat_mpc_step_dev_f64(void* ctx, const CatMpcParams* p, const CatMpcP
 CAT_API int cat_mpc_step_dev_f32(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
                          const float* controls, const double* p_ref,
                          double* best_cost, int64_t* best_idx, float* costs);
+/* Allocation-free variant of cat_mpc_step_dev_f64 (same arguments, same results).  It has NO counterpart in the
+ * reference: it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The rollout's scratch (one winner slot per
+ * thread block, one ticket per problem) lives in a fixed file-scope device array of 528 KB that every GPU loading the
+ * library holds until exit; the call makes no cudaMalloc / cudaFree and ignores cat_set_workspace.
+ * Limits: ceil(K / 128) * n_problems <= CAT_STATIC_MAX_BLOCKS and n_problems <= CAT_STATIC_MAX_PROBLEMS, else
+ * CAT_EINVAL with a message in cat_last_error (run-time equation programs are not offered here).
+ * All calls on one device share the array: calls that overlap on the GPU (different streams or contexts) race on it
+ * and must be ordered by the caller; back-to-back calls on one stream are safe. */
+#define CAT_STATIC_MAX_BLOCKS 32768
+#define CAT_STATIC_MAX_PROBLEMS 4096
+CAT_API int cat_mpc_step_static_dev_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
+                                const double* controls, const double* p_ref,
+                                double* best_cost, int64_t* best_idx, double* costs);
 /* materialise the on-device RNG controls ([n_problems][H][3][K], device pointer) */
 CAT_API int cat_sample_controls_dev_f64(void* ctx, const CatMpcParams* p, double* controls);
 /* deterministic reduce of per-shard winners gathered from G ranks (cost[g], idx[g]):
