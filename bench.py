@@ -478,6 +478,14 @@ def run_ours(args):
             barrier()
             c4["fused_ms_per_step"] = allmax(a.elapsed_time(b)) / n4
             c4["best_idx"] = win[0]
+            barrier()
+            a, b = _events(torch)
+            a.record()
+            for _ in range(n4):
+                fx4.launch()                                     # winners stay on the device: no host round trip
+            b.record()
+            barrier()
+            c4["fused_back_to_back_ms_per_step"] = allmax(a.elapsed_time(b)) / n4
         for _ in range(2):
             st4.launch()
             want4 = dist_mod.exchange_winner(st4.winner)
