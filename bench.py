@@ -569,9 +569,16 @@ def run_ours(args):
         r = o["roofline"]
         fpw = r["executed"]["fp64_inst_per_warp_step"]
         rate = (K / 32.0) * H / (ms_per_step * 1e-3) * 32.0 * fpw
+        ipw = r["executed"]["inst_per_warp_step"]
+        sm_mhz = (clocks or {}).get("sm_mhz") or 0
         r["steady_state"] = {"ms_per_step": ms_per_step, "achieved": rate / 1e12, "frac": rate / (r["peak"] * 1e12),
+                             "issue_slot_frac": (K / 32.0) * H / (ms_per_step * 1e-3) * (ipw + fpw)
+                                                / (148 * 4 * sm_mhz * 1e6) if sm_mhz else None,
                              "what": "FP64 thread-instructions per second of ONE GPU over the back-to-back loop that "
-                                     "`value` times, against the same measured DFMA rate"}
+                                     "`value` times, against the same measured DFMA rate; issue_slot_frac = issue-port "
+                                     "cycles (one per instruction, two per FP64 instruction) over the cycles of the "
+                                     "592 schedulers: at ~1.0 the loop is bound by its instruction count, and more "
+                                     "resident warps do not help (profiles/r2_ab_minb5.txt)"}
         return o
     if world == 1:
         out.update(add_steady(single_gpu_legs(torch, cb, devmod, ctx, step, p, pref, sigma, host_sets, host32, dev_sets, clocks,

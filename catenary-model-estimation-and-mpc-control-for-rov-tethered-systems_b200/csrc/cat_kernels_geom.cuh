@@ -53,7 +53,7 @@ template <typename T> struct CatShapeGroup { static constexpr int lanes = sizeof
 // cosh/sinh) and writes its 48 / 24 bytes as three vectors, half the hops -- lost as well
 // (profiles/r2_ab_shape_pair_stores.txt: fp64 0.618 vs 0.447 ms, fp32 0.296 vs 0.268 ms): every vector store then
 // covers 16 of each 48 bytes of a 1.5 KB window, all sectors partial, and the L2 write path is the bound.
-#define CAT_SHAPE_RESEED 16    // (power of two) re-evaluate cosh/sinh directly every 8 hops (bounds the recurrence drift)
+#define CAT_SHAPE_RESEED 16    // (power of two) re-evaluate cosh/sinh directly every 16 hops (bounds the recurrence drift)
 
 template <typename T> struct CatShapeSpan {
   T two_u;      // C * l

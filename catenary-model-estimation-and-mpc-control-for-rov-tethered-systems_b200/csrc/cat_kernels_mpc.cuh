@@ -336,7 +336,10 @@ __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int pro
 // PCIe and HBM at 12 B per rollout-step instead of 24 and are widened on load -- the oracle is fed the same
 // rounded values, so parity is untouched).  RNG = true draws the controls on the device instead (S unused).
 template <typename T, typename S, bool GENERIC, bool VM = false, bool RNG = false>
-__global__ void __launch_bounds__(CAT_MPC_BLOCK, 4)   // <= 128 registers: config 3 needs 3.5 blocks per SM resident
+#ifndef CAT_MPC_MINB
+#define CAT_MPC_MINB 4   // resident blocks per SM the register budget is cut for (A/B switch)
+#endif
+__global__ void __launch_bounds__(CAT_MPC_BLOCK, CAT_MPC_MINB)   // <= 128 registers: config 3 needs 3.5 blocks per SM resident
 k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, const S* __restrict__ controls,
               const double* __restrict__ p_ref, T* __restrict__ costs, CatBest* __restrict__ block_best,
               unsigned int* __restrict__ tickets, double* __restrict__ best_cost,
