@@ -11,7 +11,7 @@
 
 #include "../../include/catenary_b200.h"
 
-enum { SLOT_A = 0, SLOT_B, SLOT_C, SLOT_D, SLOT_E, SLOT_F, SLOT_G, SLOT_H, SLOT_BEST, SLOT_TICKET, N_SLOTS };
+enum { SLOT_A = 0, SLOT_B, SLOT_C, SLOT_D, SLOT_E, SLOT_F, SLOT_G, SLOT_H, SLOT_BEST, SLOT_TICKET, SLOT_ARRIVE, N_SLOTS };
 
 struct CatHostReg {   // one cudaHostRegister'ed caller range (cat_host_register)
   void* p;
@@ -40,6 +40,10 @@ struct CatCtx {
   int nvtx;                 // CAT_NVTX=1: NVTX ranges around step / exchange / host copies
   CatHostReg reg[64];
   int n_reg;
+  int streamed;               // host MPC step: candidates stream in under the running rollout (CAT_MPC_STREAMED=0: off)
+  unsigned int arrive_epoch;  // value the streamed upload's arrival words take in the current call
+  void* write_value32;        // cuStreamWriteValue32 (driver entry point, resolved in cat_init) or null
+  int stream_split[8];        // CAT_MPC_STREAM_SPLIT=a,b,c: row-group sizes in horizon steps (tuning only); [0] = 0: rule
 };
 constexpr size_t kStageWin = 4096, kStageBytes = 65536;
 

@@ -47,6 +47,7 @@ struct CatP2PDev {
 
 // Kernel-side parameters in the compute type.  Derived constants are formed on the host in
 // double exactly as the oracle forms them (dt/1000, dt/6, rho*L, z_floor+margin).
+#define CAT_ARRIVE_MAX 8   // row groups of the streamed upload
 template <typename T> struct CatMpcDev {
   long long K, k_offset;
   long long sk, sh, sa, sp;   // control strides in elements: candidate, step, axis, problem
@@ -54,6 +55,14 @@ template <typename T> struct CatMpcDev {
   int eq_theta, eq_gamma;
   int carry_t, carry_g;   // equation reads neither column 14 nor 15: k1 of the next step == k4 of this one
   int deep_clip;          // clip > CAT_ICDF_SMEM_ZMAX: the sampler's tail lanes read the full table (set by the host)
+  // streamed upload (host step, STREAM kernels): the candidates arrive over PCIe WHILE the rollout runs.  The host
+  // copies the [H][3][K] rows in groups of whole horizon steps and, after each group, copies `arrive_epoch` into
+  // arrive[group] on the same stream; the kernel reads the controls of step h only after it has seen that word.
+  // Group g holds the steps [arrive_end[g - 1], arrive_end[g]); the last end is H.
+  const unsigned int* arrive;
+  unsigned int* arrive_err;    // set to 1 when a group did not arrive in time (the costs are then junk)
+  unsigned int arrive_epoch;
+  int arrive_end[CAT_ARRIVE_MAX];
   T dt, dt_mm, dt6, L, w_trk, w_du, w_len, w_sag, w_ang, rhoL, rhoL2, z_thr, c_lo, c_hi, pen, clip;
   T L2;   // L^2 (sag-term bound)
   T sigma[3];
@@ -332,10 +341,52 @@ __device__ __forceinline__ void cat_grid_argmin(double jc, long long ji, int pro
   cat_p2p_finish(s_mine[0], s_mine[1], p2p, best_cost + prob, best_idx + prob);
 }
 
+// ---- streamed upload: wait for the row group that holds the controls of a horizon step ----
+struct CatArrive {
+  int g, end;   // last group waited for; first step NOT covered by the groups waited for so far
+};
+// thread 0 of the block polls the group's word in L2 (sleeping between polls: 512 blocks hammering one address would
+// hot-spot its L2 slice under the copy engine's writes), the block follows through a barrier.  Bounded: after ~2 s
+// the block raises *arrive_err and carries on with whatever is in memory; the host reports the failure.
+template <typename T>
+__device__ __forceinline__ void cat_arrive_wait(const CatMpcDev<T>& q, int g) {
+  if (threadIdx.x == 0) {
+    const unsigned int* f = q.arrive + g;
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+    if (v != q.arrive_epoch) {
+      unsigned long long t0, t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      for (;;) {
+        __nanosleep(400);
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        if (v == q.arrive_epoch) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 2000000000ull) {
+          atomicExch(q.arrive_err, 1u);
+          break;
+        }
+      }
+    }
+  }
+  __syncthreads();
+}
+// the controls of step hh are about to be requested (hh never decreases): block-uniform
+template <typename T>
+__device__ __forceinline__ void cat_arrive_need(const CatMpcDev<T>& q, CatArrive& st, int hh) {
+  while (hh >= st.end) {
+    ++st.g;
+    cat_arrive_wait<T>(q, st.g);
+    st.end = q.arrive_end[st.g];
+  }
+}
+// a control value of the streamed upload: L2 only (the line was written by the copy engine during this kernel)
+template <typename S> __device__ __forceinline__ S cat_ld_streamed(const S* p) { return __ldcg(p); }
+
 // T = compute type, S = storage type of the explicit controls (S = float with T = double: the candidates cross
 // PCIe and HBM at 12 B per rollout-step instead of 24 and are widened on load -- the oracle is fed the same
 // rounded values, so parity is untouched).  RNG = true draws the controls on the device instead (S unused).
-template <typename T, typename S, bool GENERIC, bool VM = false, bool RNG = false>
+template <typename T, typename S, bool GENERIC, bool VM = false, bool RNG = false, bool STREAM = false>
 #ifndef CAT_MPC_MINB
 #define CAT_MPC_MINB 4   // resident blocks per SM the register budget is cut for (A/B switch)
 #endif
@@ -454,11 +505,13 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
   S Vq[3] = {S(0), S(0), S(0)};
   int slot = 0;          // ASYNC: ring slot of step h
   int slot_in = 0;       // ASYNC: ring slot the next prefetch lands in
+  CatArrive arrived = {-1, 0};
   if constexpr (ASYNC) {
     S* const mine = reinterpret_cast<S*>(s_ring.v) + threadIdx.x;
 #pragma unroll
     for (int i = 0; i < CAT_MPC_PF; ++i) {
       if (i < q.H) {
+        if constexpr (STREAM) cat_arrive_need<T>(q, arrived, i);
         S* d = mine + (i * 3) * CAT_MPC_BLOCK;
         cat_cp_async<S>(d, uc);
         cat_cp_async<S>(d + CAT_MPC_BLOCK, uc + q.sa);
@@ -469,9 +522,16 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     }
     slot_in = CAT_MPC_PF;
   } else if constexpr (!RNG) {
-    Vq[0] = uc[0];
-    Vq[1] = uc[q.sa];
-    Vq[2] = uc[2 * q.sa];
+    if constexpr (STREAM) {
+      cat_arrive_need<T>(q, arrived, 0);
+      Vq[0] = cat_ld_streamed<S>(uc);
+      Vq[1] = cat_ld_streamed<S>(uc + q.sa);
+      Vq[2] = cat_ld_streamed<S>(uc + 2 * q.sa);
+    } else {
+      Vq[0] = uc[0];
+      Vq[1] = uc[q.sa];
+      Vq[2] = uc[2 * q.sa];
+    }
     uc += q.sh;
   }
 
@@ -505,6 +565,7 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
     const T Rh[3] = {s_ref[3 * h], s_ref[3 * h + 1], s_ref[3 * h + 2]};
     if constexpr (ASYNC) {
       if (h + CAT_MPC_PF < q.H) {   // step h + PF into the slot that was read PF + 1 steps ago
+        if constexpr (STREAM) cat_arrive_need<T>(q, arrived, h + CAT_MPC_PF);
         S* d = reinterpret_cast<S*>(s_ring.v) + threadIdx.x + (slot_in * 3) * CAT_MPC_BLOCK;
         cat_cp_async<S>(d, uc);
         cat_cp_async<S>(d + CAT_MPC_BLOCK, uc + q.sa);
@@ -515,9 +576,16 @@ k_mpc_rollout(const CatMpcDev<T> q, const CatMpcProblem* __restrict__ problems, 
       slot_in = slot_in == CAT_MPC_PF ? 0 : slot_in + 1;
     } else if constexpr (!RNG) {
       if (h + 1 < q.H) {
-        Vq[0] = uc[0];
-        Vq[1] = uc[q.sa];
-        Vq[2] = uc[2 * q.sa];
+        if constexpr (STREAM) {
+          cat_arrive_need<T>(q, arrived, h + 1);
+          Vq[0] = cat_ld_streamed<S>(uc);
+          Vq[1] = cat_ld_streamed<S>(uc + q.sa);
+          Vq[2] = cat_ld_streamed<S>(uc + 2 * q.sa);
+        } else {
+          Vq[0] = uc[0];
+          Vq[1] = uc[q.sa];
+          Vq[2] = uc[2 * q.sa];
+        }
         uc += q.sh;
       }
     }

@@ -14,6 +14,7 @@ struct CatMpcLaunchArgs {
   bool rng;          // controls drawn on the device
   bool controls_f32; // explicit controls stored as float while T = double
   bool pdl;          // programmatic stream serialization: may start under the tail of the preceding rollout
+  bool streamed;     // controls arrive while the kernel runs (q.arrive; shipped equations, explicit controls only)
 };
 
 // one launch of k_mpc_rollout<T, S, ...>; returns the cudaError_t of the launch

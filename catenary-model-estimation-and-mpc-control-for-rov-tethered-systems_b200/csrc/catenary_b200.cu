@@ -280,6 +280,10 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.pen = T(p->nan_penalty);
   q.clip = T(p->clip);
   q.deep_clip = q.clip > T(CAT_ICDF_SMEM_ZMAX);
+  q.arrive = nullptr;
+  q.arrive_err = nullptr;
+  q.arrive_epoch = 0;
+  for (int i = 0; i < CAT_ARRIVE_MAX; ++i) q.arrive_end[i] = 0;
   for (int a = 0; a < 3; ++a) q.sigma[a] = T(p->sigma[a]);
   q.seed = p->seed;
   q.prog = nullptr;
@@ -320,6 +324,7 @@ int mpc_launch(CatCtx* c, const CatMpcDev<T>& q, const CatMpcProblem* problems, 
   a.rng = (q.flags & CAT_MPC_RNG_CONTROLS) != 0;
   a.controls_f32 = (q.flags & CAT_MPC_CONTROLS_F32) != 0;
   a.pdl = false;
+  a.streamed = q.arrive != nullptr;
   if (c->overlap) {   // not inside a stream capture (the controller's graph): plain kernel nodes there
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(c->stream, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone) a.pdl = true;
@@ -507,9 +512,80 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   }
   // the shared scratch slots serve the host call (it synchronises before it returns); a workspace selected for
   // *_dev launches on other streams is left alone
+  // Streamed upload (one problem, explicit SoA candidates, shipped equations, a grid that is resident at once): ONE
+  // rollout is launched right away and the candidates follow over PCIe in row groups of whole horizon steps, each
+  // followed by a stream write of this call's epoch into the group's arrival word; the kernel reads the controls of a
+  // step only after it has seen the word (cat_arrive_need).  The rollout then trails the copy by one step, where the
+  // chunked form below ends with the whole rollout of its last chunk (~35 us: 50 serial steps at one warp per
+  // scheduler) and takes nine launches.  Config 3 on one B200: 0.816 -> 0.776 ms (float32 on the wire), 1.528 ->
+  // 1.484 ms (fp64); at most 1 GB of candidates, so that a group cannot outlast the kernel's 2 s patience.
+  const bool aos_ctl = (p->flags & CAT_MPC_CONTROLS_AOS) != 0;
+  const bool shipped_eq = q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED;
+  // Rows must start on 128-byte lines: a line that straddles two row groups could be fetched (into L1 by the fp32
+  // kernel's cp.async) before its second half has arrived.
+  const bool streamed = c->streamed && !rng && np == 1 && p->K >= 32768 && !aos_ctl && !hp && shipped_eq && staged &&
+                        ((size_t)p->K * esz) % 128 == 0 && n_ctl * esz <= ((size_t)1 << 30) &&
+                        nblk(p->K, mpc_block_size(c, p->K, 1)) <= (unsigned)c->sm_count * CAT_MPC_MINB;
+  unsigned int* d_arrive = nullptr;
+  if (streamed) {
+    void* pp = nullptr;
+    rc = scratch(c, SLOT_ARRIVE, 64 * sizeof(unsigned int), &pp, true);
+    if (rc) return rc;
+    d_arrive = (unsigned int*)pp;
+  }
+  unsigned int* const h_epoch = (unsigned int*)(c->h_stage ? c->h_stage + 4000 : nullptr);
+  unsigned int* const h_err = (unsigned int*)(c->h_stage ? c->h_stage + 4008 : nullptr);
   void* const ws_saved = c->ws;
   c->ws = nullptr;
-  if (!rng && np == 1 && p->K >= 32768) {
+  if (streamed) {
+    CatNvtxRange r_up(c, "cat: streamed H2D of the candidates under the rollout");
+    // Row groups.  Every boundary between two copies costs ~9 us on the link (measured: profiles/r2_ab_streamed_upload.txt),
+    // a step of the rollout ~1.7 us and its row 15-30 us of copy, so the groups shrink towards the end by about the
+    // ratio of the two: [the rest, H/10 steps, 1 step] -- the rollout of each group finishes under the next copy and
+    // one step is left when the last byte lands.
+    const int H = p->H;
+    int sizes[CAT_ARRIVE_MAX] = {0}, ng = 0, sum = 0;
+    for (int i = 0; i < CAT_ARRIVE_MAX && c->stream_split[i] > 0; ++i) sum += (sizes[ng++] = c->stream_split[i]);
+    if (ng == 0 || sum != H) {
+      const int last = H >= 2 ? 1 : 0, mid = H >= 12 ? (H + 5) / 10 : 0;
+      ng = 0;
+      sizes[ng++] = H - mid - last;
+      if (mid) sizes[ng++] = mid;
+      if (last) sizes[ng++] = last;
+    }
+    if (++c->arrive_epoch == 0) ++c->arrive_epoch;         // 0 is what freshly allocated words hold
+    *h_epoch = c->arrive_epoch;
+    *h_err = 0;
+    q.arrive = d_arrive;
+    q.arrive_err = (unsigned int*)(c->d_stage + 4008);
+    q.arrive_epoch = c->arrive_epoch;
+    for (int i = 0, end = 0; i < CAT_ARRIVE_MAX; ++i) q.arrive_end[i] = i < ng ? (end += sizes[i]) : H;
+    const size_t row = (size_t)p->K * esz * 3;             // bytes of one horizon step of [H][3][K]
+    const unsigned char* h_ctl = (const unsigned char*)controls;
+    cudaError_t e = cudaSuccess;
+    for (int g = 0, h0 = 0; g < ng && e == cudaSuccess; ++g) {
+      const int h1 = h0 + sizes[g];
+      e = cudaMemcpyAsync(d_ctl + (size_t)h0 * row, h_ctl + (size_t)h0 * row, (size_t)(h1 - h0) * row,
+                          cudaMemcpyHostToDevice, c->aux_stream);
+      if (e == cudaSuccess) {
+        typedef int (*WriteValue32)(cudaStream_t, unsigned long long, unsigned int, unsigned int);
+        if (c->write_value32) {
+          if (((WriteValue32)c->write_value32)(c->aux_stream, (unsigned long long)(uintptr_t)(d_arrive + g),
+                                               c->arrive_epoch, 0u) != 0)
+            e = cudaErrorUnknown;
+        } else {
+          e = cudaMemcpyAsync(d_arrive + g, h_epoch, sizeof(unsigned int), cudaMemcpyHostToDevice, c->aux_stream);
+        }
+      }
+      h0 = h1;
+    }
+    if (e != cudaSuccess) rc = fail(c, CAT_ECUDA, "streamed control upload", e);
+    if (rc == CAT_OK) {
+      if (x) p2p_arm(x, q.p2p);
+      rc = mpc_launch<T>(c, q, d_prob, d_ctl, d_ref, d_bc, d_bi, d_costs, nullptr, nullptr);
+      if (rc == CAT_OK && x) ++x->seq;
+    }
+  } else if (!rng && np == 1 && p->K >= 32768) {
     // One problem, explicit controls (config 3: 78.6 MB in fp64, 39.3 MB as float): the step is PCIe-bound, so
     // the candidates go up in 8 chunks on the aux stream and chunk i's rollout overlaps chunk i+1's copy; the chunk
     // winners fold on the device in candidate order (same total order as one launch: lowest cost, then lowest
@@ -586,6 +662,10 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   {
     CatNvtxRange r_wait(c, x ? "cat: wait for the job-wide winner (in-kernel exchange)" : "cat: wait for the winner");
     CU(cudaStreamSynchronize(c->stream));
+  }
+  if (streamed && *h_err) {
+    cudaStreamSynchronize(c->aux_stream);
+    return fail(c, CAT_ECUDA, "streamed control upload: a row group did not reach the device within 2 s");
   }
   if (staged) {   // the winners are already in host memory (written through the mapping before the kernel ended)
     std::memcpy(best_cost, c->h_stage, np * sizeof(double));
@@ -994,6 +1074,32 @@ int cat_init(int device, void** ctx) {
   c->n_reg = 0;
   c->nvtx = 0;
   if (const char* e = std::getenv("CAT_NVTX")) c->nvtx = std::atoi(e) != 0;
+  c->streamed = 1;
+  if (const char* e = std::getenv("CAT_MPC_STREAMED")) c->streamed = std::atoi(e) != 0;
+  c->arrive_epoch = 0;
+  for (int i = 0; i < 8; ++i) c->stream_split[i] = 0;
+  if (const char* e = std::getenv("CAT_MPC_STREAM_SPLIT")) {
+    int i = 0;
+    for (const char* s = e; *s && i < 8; ++i) {
+      c->stream_split[i] = std::atoi(s);
+      while (*s && *s != ',') ++s;
+      if (*s == ',') ++s;
+    }
+  }
+  // arrival words are written with a stream memory operation (a semaphore release in the command stream) rather than
+  // a 4-byte copy, which costs a DMA set-up between every two row groups; resolved at run time, nothing is linked
+  c->write_value32 = nullptr;
+  {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+        qr == cudaDriverEntryPointSuccess)
+      c->write_value32 = fn;
+    else
+      cudaGetLastError();
+    if (const char* e = std::getenv("CAT_MPC_STREAM_MEMOP"))
+      if (std::atoi(e) == 0) c->write_value32 = nullptr;
+  }
   if (const char* e = std::getenv("CAT_MPC_BLOCK_SIZE")) {
     const int v = std::atoi(e);
     if (v == 32 || v == 64 || v == 128) c->mpc_block = v;

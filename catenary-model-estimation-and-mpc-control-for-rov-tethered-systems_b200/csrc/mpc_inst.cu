@@ -29,7 +29,21 @@ int cat_mpc_launch_inst<InstT, CAT_INST_KIND>(const CatMpcLaunchArgs& a, const C
   cfg.attrs = attr;
   cfg.numAttrs = a.pdl ? 1 : 0;
   cudaError_t e;
-  if (a.rng) {
+  if (a.streamed) {
+    // the streamed-upload form exists for the shipped equation pair only (the host step falls back to the chunked
+    // upload for every other equation source)
+#if CAT_INST_KIND == 0
+    if (a.rng) return (int)cudaErrorInvalidValue;
+    if (sizeof(InstT) == 8 && a.controls_f32)
+      e = cudaLaunchKernelEx(&cfg, k_mpc_rollout<InstT, float, false, false, false, true>, q, problems,
+                             (const float*)controls, p_ref, costs, bb, tk, best_cost, best_idx);
+    else
+      e = cudaLaunchKernelEx(&cfg, k_mpc_rollout<InstT, InstT, false, false, false, true>, q, problems,
+                             (const InstT*)controls, p_ref, costs, bb, tk, best_cost, best_idx);
+#else
+    return (int)cudaErrorInvalidValue;
+#endif
+  } else if (a.rng) {
     e = cudaLaunchKernelEx(&cfg, k_mpc_rollout<InstT, InstT, kGen, kVm, true>, q, problems, (const InstT*)nullptr, p_ref,
                            costs, bb, tk, best_cost, best_idx);
   } else if (sizeof(InstT) == 8 && a.controls_f32) {

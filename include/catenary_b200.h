@@ -230,6 +230,12 @@ CAT_API int cat_features_f64(void* ctx, int64_t T, const double* P0, const doubl
  * NULL with CAT_MPC_RNG_CONTROLS.  p_ref: [n_problems][H][3] (m).
  * best_cost / best_idx: n_problems values (best_idx is GLOBAL: k_offset + local index; lowest cost, ties -> lowest
  * index, a NaN cost ranks with +inf so that a failed rollout is never selected).  costs: [n_problems][K] or NULL. */
+/* Host-pointer step with one problem and >= 32,768 explicit candidates: the upload overlaps the rollout.  SoA
+ * candidates of the shipped equation pair whose grid is resident at once (K <= 4 * 128 * SMs = 75,776 on B200, rows
+ * of K values a multiple of 128 bytes, <= 1 GB in all) are STREAMED: one rollout is launched at once and reads each
+ * horizon step's rows after their row group has landed (arrival words written with a stream memory operation);
+ * everything else goes up in 8 candidate chunks with one rollout each.  Identical results either way.
+ * Env CAT_MPC_STREAMED=0 (read in cat_init) forces the chunked form. */
 CAT_API int cat_mpc_step_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
                      const double* controls, const double* p_ref,
                      double* best_cost, int64_t* best_idx, double* costs);
