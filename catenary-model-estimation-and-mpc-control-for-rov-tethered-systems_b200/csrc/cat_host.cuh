@@ -43,6 +43,8 @@ struct CatCtx {
   int streamed;               // host MPC step: candidates stream in under the running rollout (CAT_MPC_STREAMED=0: off)
   unsigned int arrive_epoch;  // value the streamed upload's arrival words take in the current call
   void* write_value32;        // cuStreamWriteValue32 (driver entry point, resolved in cat_init) or null
+  int chunk_n;                // chunked upload: equal chunks ahead of the last one (CAT_MPC_CHUNK_N, tuning only)
+  long long chunk_last;       // ... candidates in the last chunk, 0 = one block per SM (CAT_MPC_CHUNK_LAST)
   int stream_split[8];        // CAT_MPC_STREAM_SPLIT=a,b,c: row-group sizes in horizon steps (tuning only); [0] = 0: rule
 };
 constexpr size_t kStageWin = 4096, kStageBytes = 65536;

@@ -517,8 +517,8 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   // followed by a stream write of this call's epoch into the group's arrival word; the kernel reads the controls of a
   // step only after it has seen the word (cat_arrive_need).  The rollout then trails the copy by one step, where the
   // chunked form below ends with the whole rollout of its last chunk (~35 us: 50 serial steps at one warp per
-  // scheduler) and takes nine launches.  Config 3 on one B200: 0.816 -> 0.776 ms (float32 on the wire), 1.528 ->
-  // 1.484 ms (fp64); at most 1 GB of candidates, so that a group cannot outlast the kernel's 2 s patience.
+  // scheduler).  Config 3 on one B200: 0.794 (two chunks; 0.816 with the eight of round 1) -> 0.773 ms (float32 on
+  // the wire), 1.505 -> 1.482 ms (fp64); at most 1 GB of candidates, so that a group cannot outlast the kernel's 2 s patience.
   const bool aos_ctl = (p->flags & CAT_MPC_CONTROLS_AOS) != 0;
   const bool shipped_eq = q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED;
   // Rows must start on 128-byte lines: a line that straddles two row groups could be fetched (into L1 by the fp32
@@ -587,9 +587,13 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     }
   } else if (!rng && np == 1 && p->K >= 32768) {
     // One problem, explicit controls (config 3: 78.6 MB in fp64, 39.3 MB as float): the step is PCIe-bound, so
-    // the candidates go up in 8 chunks on the aux stream and chunk i's rollout overlaps chunk i+1's copy; the chunk
+    // the candidates go up in chunks on the aux stream and chunk i's rollout overlaps chunk i+1's copy; the chunk
     // winners fold on the device in candidate order (same total order as one launch: lowest cost, then lowest
     // global index).
+    // Chunk boundaries.  The step ends one whole rollout after the last copy, and a rollout of up to one block per SM
+    // takes the same ~35 us (50 serial steps at one warp per scheduler) however few candidates it has; every extra
+    // copy costs ~9 us of link time (profiles/r2_ab_streamed_upload.txt).  So: a last chunk of one block per SM, and
+    // the rest in `chunk_n` equal chunks (1: its rollout runs under the last copy, which is 9x longer).
     const int NC = 8;
     CatNvtxRange r_up(c, "cat: chunked H2D of the candidates + rollouts");
     long long* d_pairs;
@@ -597,11 +601,22 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     const bool aos = (p->flags & CAT_MPC_CONTROLS_AOS) != 0;
     const long long K = p->K, H3 = 3LL * p->H;
     const unsigned char* h_ctl = (const unsigned char*)controls;
+    long long kb[NC + 1];
+    int nc = 0;
+    {
+      long long last = c->chunk_last > 0 ? c->chunk_last : (long long)c->sm_count * 128;
+      last = (last + 127) / 128 * 128;
+      if (last > K / 2) last = (K / 2 + 127) / 128 * 128;
+      const int n_head = c->chunk_n >= 1 && c->chunk_n < NC ? c->chunk_n : 1;
+      const long long head = K - last;
+      kb[0] = 0;
+      for (int i = 1; i <= n_head; ++i) kb[i] = i == n_head ? head : (head * i / n_head + 127) / 128 * 128;
+      kb[n_head + 1] = K;
+      nc = n_head + 1;
+    }
     int used = 0;
-    for (int i = 0; i < NC && rc == CAT_OK; ++i) {
-      const long long k0 = ((K * i / NC) + 127) / 128 * 128;
-      long long k1 = (i == NC - 1) ? K : ((K * (i + 1) / NC) + 127) / 128 * 128;
-      if (k1 > K) k1 = K;
+    for (int i = 0; i < nc && rc == CAT_OK; ++i) {
+      const long long k0 = kb[i], k1 = kb[i + 1];
       if (k1 <= k0) continue;
       cudaError_t e;
       if (aos)
@@ -1077,6 +1092,10 @@ int cat_init(int device, void** ctx) {
   c->streamed = 1;
   if (const char* e = std::getenv("CAT_MPC_STREAMED")) c->streamed = std::atoi(e) != 0;
   c->arrive_epoch = 0;
+  c->chunk_n = 1;
+  c->chunk_last = 0;
+  if (const char* e = std::getenv("CAT_MPC_CHUNK_N")) c->chunk_n = std::atoi(e);
+  if (const char* e = std::getenv("CAT_MPC_CHUNK_LAST")) c->chunk_last = std::atoll(e);
   for (int i = 0; i < 8; ++i) c->stream_split[i] = 0;
   if (const char* e = std::getenv("CAT_MPC_STREAM_SPLIT")) {
     int i = 0;

@@ -234,7 +234,8 @@ CAT_API int cat_features_f64(void* ctx, int64_t T, const double* P0, const doubl
  * candidates of the shipped equation pair whose grid is resident at once (K <= 4 * 128 * SMs = 75,776 on B200, rows
  * of K values a multiple of 128 bytes, <= 1 GB in all) are STREAMED: one rollout is launched at once and reads each
  * horizon step's rows after their row group has landed (arrival words written with a stream memory operation);
- * everything else goes up in 8 candidate chunks with one rollout each.  Identical results either way.
+ * everything else goes up in two candidate chunks (the last one block per SM) with one rollout each.  Identical
+ * results either way.
  * Env CAT_MPC_STREAMED=0 (read in cat_init) forces the chunked form. */
 CAT_API int cat_mpc_step_f64(void* ctx, const CatMpcParams* p, const CatMpcProblem* problems,
                      const double* controls, const double* p_ref,

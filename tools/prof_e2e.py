@@ -36,4 +36,4 @@ for dt in (np.float32, np.float64):
         cb.mpc_sample_step(p, sets[i % 4], pref, **kw)
         ts.append(time.perf_counter() - t0)
     out.append(f"{np.dtype(dt).name} median {np.median(ts) * 1e3:.4f} ms min {np.min(ts) * 1e3:.4f}")
-print(" | ".join(out), "|", {k: v for k, v in os.environ.items() if k.startswith("CAT_MPC_ST")})
+print(" | ".join(out), "|", {k: v for k, v in os.environ.items() if k.startswith("CAT_MPC_")})
