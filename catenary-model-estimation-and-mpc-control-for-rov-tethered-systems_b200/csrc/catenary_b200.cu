@@ -569,13 +569,13 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
                           cudaMemcpyHostToDevice, c->aux_stream);
       if (e == cudaSuccess) {
         typedef int (*WriteValue32)(cudaStream_t, unsigned long long, unsigned int, unsigned int);
-        if (c->write_value32) {
-          if (((WriteValue32)c->write_value32)(c->aux_stream, (unsigned long long)(uintptr_t)(d_arrive + g),
-                                               c->arrive_epoch, 0u) != 0)
-            e = cudaErrorUnknown;
-        } else {
+        // a device or driver without stream memory operations refuses the call: 4-byte copies from then on
+        if (c->write_value32 &&
+            ((WriteValue32)c->write_value32)(c->aux_stream, (unsigned long long)(uintptr_t)(d_arrive + g),
+                                             c->arrive_epoch, 0u) != 0)
+          c->write_value32 = nullptr;
+        if (!c->write_value32)
           e = cudaMemcpyAsync(d_arrive + g, h_epoch, sizeof(unsigned int), cudaMemcpyHostToDevice, c->aux_stream);
-        }
       }
       h0 = h1;
     }

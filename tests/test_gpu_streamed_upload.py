@@ -13,18 +13,21 @@ pytestmark = pytest.mark.gpu
 SIGMA = np.array(orc.load_model()["scaler_scale"][3:6])
 
 
-def _ctx(cb, streamed):
+def _ctx(cb, streamed, **env):
+    """A context whose library switches (read once, in cat_init) are set for this context only."""
     import importlib
     Context = importlib.import_module(cb.__name__ + ".context").Context
-    old = os.environ.get("CAT_MPC_STREAMED")
-    os.environ["CAT_MPC_STREAMED"] = "1" if streamed else "0"     # read once, in cat_init
+    env = dict({"CAT_MPC_STREAMED": "1" if streamed else "0"}, **env)
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
     try:
         return Context(0)
     finally:
-        if old is None:
-            del os.environ["CAT_MPC_STREAMED"]
-        else:
-            os.environ["CAT_MPC_STREAMED"] = old
+        for k, v in old.items():
+            if v is None:
+                del os.environ[k]
+            else:
+                os.environ[k] = v
 
 
 def _controls(K, H, seed):
@@ -64,3 +67,36 @@ def test_streamed_config3_vs_oracle(cb):
         b2, c2, none = cb.mpc_sample_step(p, U, pref, layout="H3K", ctx=ctx, return_costs=False)
         assert none is None and b2 == bi and c2 == bc
         cb.mpc_sample_step(p, None, pref, sigma=SIGMA, K=4096, ctx=ctx)
+
+
+def test_streamed_many_groups_and_copied_arrival_words(cb):
+    """Eight row groups (the most the kernel takes) and arrival words written by 4-byte copies instead of stream
+    memory operations: the fallback for drivers without them."""
+    K, H = 65536, 41
+    U = _controls(K, H, seed=7)
+    p = cb.default_mpc_params()
+    pref = cb.circle_reference(H, p["dt"])
+    want = cb.mpc_sample_step(p, U, pref, layout="H3K", ctx=_ctx(cb, False))
+    for env in (dict(CAT_MPC_STREAM_SPLIT="10,10,10,5,3,1,1,1"), dict(CAT_MPC_STREAM_MEMOP="0"),
+                dict(CAT_MPC_STREAM_SPLIT="40,1", CAT_MPC_STREAM_MEMOP="0")):
+        ctx = _ctx(cb, True, **env)
+        for _ in range(2):
+            got = cb.mpc_sample_step(p, U, pref, layout="H3K", ctx=ctx)
+            assert got[0] == want[0] and got[1] == want[1] and np.array_equal(got[2], want[2]), env
+
+
+def test_streamed_repeated_calls_alternating_shapes(cb):
+    """Sixty calls on one context, two shapes and two wire types in turn: arrival words, epochs and the control
+    buffer are reused call after call."""
+    p = cb.default_mpc_params()
+    cases = []
+    for K, H, kw in ((65536, 50, dict(controls_dtype=np.float32)), (36864, 12, dict())):
+        U = _controls(K, H, seed=K)
+        pref = cb.circle_reference(H, p["dt"])
+        want = cb.mpc_sample_step(p, U, pref, layout="H3K", ctx=_ctx(cb, False), return_costs=False, **kw)
+        cases.append((U, pref, kw, want))
+    ctx = _ctx(cb, True)
+    for i in range(60):
+        U, pref, kw, want = cases[i % 2]
+        got = cb.mpc_sample_step(p, U, pref, layout="H3K", ctx=ctx, return_costs=False, **kw)
+        assert got[0] == want[0] and got[1] == want[1], i
