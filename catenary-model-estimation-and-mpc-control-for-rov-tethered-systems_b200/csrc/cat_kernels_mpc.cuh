@@ -48,6 +48,13 @@ struct CatP2PDev {
 // Kernel-side parameters in the compute type.  Derived constants are formed on the host in
 // double exactly as the oracle forms them (dt/1000, dt/6, rho*L, z_floor+margin).
 #define CAT_ARRIVE_MAX 8   // row groups of the streamed upload
+struct CatArrivePlan {
+  unsigned int epoch;            // value the arrival words take in this call
+  int n_groups;
+  int end[CAT_ARRIVE_MAX];       // group g holds the horizon steps [end[g - 1], end[g]); the last end is H
+  const unsigned int* words;     // arrival words (device memory)
+  unsigned int* err;             // set to 1 when a group did not arrive in time (the costs are then junk)
+};
 template <typename T> struct CatMpcDev {
   long long K, k_offset;
   long long sk, sh, sa, sp;   // control strides in elements: candidate, step, axis, problem
@@ -55,14 +62,6 @@ template <typename T> struct CatMpcDev {
   int eq_theta, eq_gamma;
   int carry_t, carry_g;   // equation reads neither column 14 nor 15: k1 of the next step == k4 of this one
   int deep_clip;          // clip > CAT_ICDF_SMEM_ZMAX: the sampler's tail lanes read the full table (set by the host)
-  // streamed upload (host step, STREAM kernels): the candidates arrive over PCIe WHILE the rollout runs.  The host
-  // copies the [H][3][K] rows in groups of whole horizon steps and, after each group, copies `arrive_epoch` into
-  // arrive[group] on the same stream; the kernel reads the controls of step h only after it has seen that word.
-  // Group g holds the steps [arrive_end[g - 1], arrive_end[g]); the last end is H.
-  const unsigned int* arrive;
-  unsigned int* arrive_err;    // set to 1 when a group did not arrive in time (the costs are then junk)
-  unsigned int arrive_epoch;
-  int arrive_end[CAT_ARRIVE_MAX];
   T dt, dt_mm, dt6, L, w_trk, w_du, w_len, w_sag, w_ang, rhoL, rhoL2, z_thr, c_lo, c_hi, pen, clip;
   T L2;   // L^2 (sag-term bound)
   T sigma[3];
@@ -79,6 +78,12 @@ template <typename T> struct CatMpcDev {
   int n_ops_t, n_ops_g, n_c_t, n_c_g;
   int ref_smem_off;   // byte offset of the staged reference window in the dynamic shared memory
   CatP2PDev p2p;
+  // streamed upload (host step, STREAM kernels): the candidates arrive over PCIe WHILE the rollout runs.  The host
+  // copies the [H][3][K] rows in groups of whole horizon steps and, after each group, writes the call's epoch into
+  // words[group] on the same stream; the kernel reads the controls of step h only after it has seen that word.
+  // The plan of the call sits in device memory: one pointer, LAST in the block, so the offsets every other rollout
+  // reads stay what they were (a field in the middle cost the sampling kernel 6 registers and 1% of its time).
+  const CatArrivePlan* arrive;
 };
 
 // shared-memory view of the staged programs (VM mode)
@@ -347,23 +352,24 @@ struct CatArrive {
 };
 // thread 0 of the block polls the group's word in L2 (sleeping between polls: 512 blocks hammering one address would
 // hot-spot its L2 slice under the copy engine's writes), the block follows through a barrier.  Bounded: after ~2 s
-// the block raises *arrive_err and carries on with whatever is in memory; the host reports the failure.
+// the block raises *err of the plan and carries on with whatever is in memory; the host reports the failure.
 template <typename T>
 __device__ __forceinline__ void cat_arrive_wait(const CatMpcDev<T>& q, int g) {
   if (threadIdx.x == 0) {
-    const unsigned int* f = q.arrive + g;
+    const unsigned int* f = q.arrive->words + g;
+    const unsigned int epoch = q.arrive->epoch;
     unsigned int v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-    if (v != q.arrive_epoch) {
+    if (v != epoch) {
       unsigned long long t0, t1;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
       for (;;) {
         __nanosleep(400);
         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-        if (v == q.arrive_epoch) break;
+        if (v == epoch) break;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
         if (t1 - t0 > 2000000000ull) {
-          atomicExch(q.arrive_err, 1u);
+          atomicExch(q.arrive->err, 1u);
           break;
         }
       }
@@ -377,7 +383,7 @@ __device__ __forceinline__ void cat_arrive_need(const CatMpcDev<T>& q, CatArrive
   while (hh >= st.end) {
     ++st.g;
     cat_arrive_wait<T>(q, st.g);
-    st.end = q.arrive_end[st.g];
+    st.end = q.arrive->end[st.g];
   }
 }
 // a control value of the streamed upload: L2 only (the line was written by the copy engine during this kernel)

@@ -281,9 +281,6 @@ int mpc_fill(CatCtx* c, const CatMpcParams* p, CatMpcDev<T>& q) {
   q.clip = T(p->clip);
   q.deep_clip = q.clip > T(CAT_ICDF_SMEM_ZMAX);
   q.arrive = nullptr;
-  q.arrive_err = nullptr;
-  q.arrive_epoch = 0;
-  for (int i = 0; i < CAT_ARRIVE_MAX; ++i) q.arrive_end[i] = 0;
   for (int a = 0; a < 3; ++a) q.sigma[a] = T(p->sigma[a]);
   q.seed = p->seed;
   q.prog = nullptr;
@@ -529,7 +526,7 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   unsigned int* d_arrive = nullptr;
   if (streamed) {
     void* pp = nullptr;
-    rc = scratch(c, SLOT_ARRIVE, 64 * sizeof(unsigned int), &pp, true);
+    rc = scratch(c, SLOT_ARRIVE, 64 * sizeof(unsigned int) + sizeof(CatArrivePlan), &pp, true);
     if (rc) return rc;
     d_arrive = (unsigned int*)pp;
   }
@@ -556,10 +553,18 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     if (++c->arrive_epoch == 0) ++c->arrive_epoch;         // 0 is what freshly allocated words hold
     *h_epoch = c->arrive_epoch;
     *h_err = 0;
-    q.arrive = d_arrive;
-    q.arrive_err = (unsigned int*)(c->d_stage + 4008);
-    q.arrive_epoch = c->arrive_epoch;
-    for (int i = 0, end = 0; i < CAT_ARRIVE_MAX; ++i) q.arrive_end[i] = i < ng ? (end += sizes[i]) : H;
+    // the plan rides behind the problem record and the reference rows in the staged upload (one more copy of 56 bytes,
+    // ordered ahead of the rollout on its stream)
+    CatArrivePlan plan;
+    plan.epoch = c->arrive_epoch;
+    plan.n_groups = ng;
+    for (int i = 0, end = 0; i < CAT_ARRIVE_MAX; ++i) plan.end[i] = i < ng ? (end += sizes[i]) : H;
+    plan.words = d_arrive;
+    plan.err = (unsigned int*)(c->d_stage + 4008);
+    std::memcpy(c->h_stage + 3840, &plan, sizeof(plan));
+    CatArrivePlan* d_plan = reinterpret_cast<CatArrivePlan*>(d_arrive + 64);
+    CU(cudaMemcpyAsync(d_plan, c->h_stage + 3840, sizeof(plan), cudaMemcpyHostToDevice, c->stream));
+    q.arrive = d_plan;
     const size_t row = (size_t)p->K * esz * 3;             // bytes of one horizon step of [H][3][K]
     const unsigned char* h_ctl = (const unsigned char*)controls;
     cudaError_t e = cudaSuccess;
