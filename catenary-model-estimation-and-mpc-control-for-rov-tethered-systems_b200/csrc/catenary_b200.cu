@@ -520,9 +520,21 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
   const bool shipped_eq = q.eq_theta == CAT_EQ_DTHETA_SHIPPED && q.eq_gamma == CAT_EQ_DGAMMA_SHIPPED;
   // Rows must start on 128-byte lines: a line that straddles two row groups could be fetched (into L1 by the fp32
   // kernel's cp.async) before its second half has arrived.
-  const bool streamed = c->streamed && !rng && np == 1 && p->K >= 32768 && !aos_ctl && !hp && shipped_eq && staged &&
-                        ((size_t)p->K * esz) % 128 == 0 && n_ctl * esz <= ((size_t)1 << 30) &&
-                        nblk(p->K, mpc_block_size(c, p->K, 1)) <= (unsigned)c->sm_count * CAT_MPC_MINB;
+  bool streamed = c->streamed && !rng && np == 1 && p->K >= 32768 && !aos_ctl && !hp && shipped_eq && staged &&
+                  ((size_t)p->K * esz) % 128 == 0 && n_ctl * esz <= ((size_t)1 << 30) &&
+                  nblk(p->K, mpc_block_size(c, p->K, 1)) <= (unsigned)c->sm_count * CAT_MPC_MINB;
+  if (streamed) {
+    // page-locked candidates only: a copy from pageable memory blocks the host while it is staged, so the rollout --
+    // launched after the copies are enqueued -- would start when everything is already on the device; the chunked
+    // form launches between its copies and keeps the overlap
+    cudaPointerAttributes pa;
+    if (cudaPointerGetAttributes(&pa, controls) != cudaSuccess) {
+      cudaGetLastError();
+      streamed = false;
+    } else if (pa.type != cudaMemoryTypeHost) {
+      streamed = false;
+    }
+  }
   unsigned int* d_arrive = nullptr;
   if (streamed) {
     void* pp = nullptr;

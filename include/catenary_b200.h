@@ -232,7 +232,7 @@ CAT_API int cat_features_f64(void* ctx, int64_t T, const double* P0, const doubl
  * index, a NaN cost ranks with +inf so that a failed rollout is never selected).  costs: [n_problems][K] or NULL. */
 /* Host-pointer step with one problem and >= 32,768 explicit candidates: the upload overlaps the rollout.  SoA
  * candidates of the shipped equation pair whose grid is resident at once (K <= 4 * 128 * SMs = 75,776 on B200, rows
- * of K values a multiple of 128 bytes, <= 1 GB in all) are STREAMED: one rollout is launched at once and reads each
+ * of K values a multiple of 128 bytes, <= 1 GB in all, in page-locked host memory) are STREAMED: one rollout is launched at once and reads each
  * horizon step's rows after their row group has landed (arrival words written with a stream memory operation);
  * everything else goes up in two candidate chunks (the last one block per SM) with one rollout each.  Identical
  * results either way.
