@@ -53,6 +53,9 @@ template <typename T> struct CatShapeGroup { static constexpr int lanes = sizeof
 // cosh/sinh) and writes its 48 / 24 bytes as three vectors, half the hops -- lost as well
 // (profiles/r2_ab_shape_pair_stores.txt: fp64 0.618 vs 0.447 ms, fp32 0.296 vs 0.268 ms): every vector store then
 // covers 16 of each 48 bytes of a 1.5 KB window, all sectors partial, and the L2 write path is the bound.
+// What does pay, for the masks that write two or more rotated curves (their stores interleave inside one span loop), is
+// TWO stores per point -- a 2-value vector + a scalar, chosen by the point's parity (template parameter ST2; the host
+// picks it, profiles/r2_ab_shape_two_stores.txt): all four curves 1.87 -> 1.57 ms in fp64, 1.34 -> 0.98 ms in fp32.
 #define CAT_SHAPE_RESEED 16    // (power of two) re-evaluate cosh/sinh directly every 16 hops (bounds the recurrence drift)
 
 template <typename T> struct CatShapeSpan {
@@ -156,7 +159,8 @@ __device__ __forceinline__ void cat_shape_map_set(CatShapeMap<T>& m, const T a[3
 // layout, the per-map tests of the point loop and the map loads are resolved at compile time: the maps of a
 // configuration sit in registers across its points (profiles/r1_ncu_full_k_shape_f64_v3c.csv: the run-time form
 // spends 55 instructions per 32-point hop, of which ~20 are mask tests, offset arithmetic and repeated LDS).
-template <typename T, int W>
+// ST2: two stores per point (one 2-value vector + one scalar) instead of three scalars -- see the store site.
+template <typename T, int W, bool ST2 = false>
 __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long long n, const T* __restrict__ A,
                                                           const T* __restrict__ B, const T* __restrict__ L,
                                                           long long L_stride, const T* __restrict__ theta,
@@ -289,6 +293,9 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
   const int grp = lane / G, gl = lane % G;
   const T lane_f = T(gl);
   const int n_hops = (n_pts + G - 1) / G;
+  // ST2 (host: even n_pts, `out` aligned to two values): G is even, so a lane's points all have the lane's parity,
+  // every curve and every output block starts on a 2-value boundary
+  const bool odd = (gl & 1) != 0;
   for (int c0 = warp * (32 / G); c0 < n_here; c0 += n_warps * (32 / G)) {
     const bool have = c0 + grp < n_here;
     const int ci = have ? c0 + grp : n_here - 1;   // idle groups shadow the last configuration and do not store
@@ -352,9 +359,19 @@ __global__ void __launch_bounds__(CAT_SHAPE_TILE, CAT_SHAPE_MINB) k_shape(long l
             p2 = mp[2];
           }
           T* om = o + m_out[m];
-          om[0] = M::fma_(zoff, p1.y, M::fma_(s, p0.x, A0));
-          om[1] = M::fma_(zoff, p2.x, M::fma_(s, p0.y, A1));
-          om[2] = M::fma_(zoff, p2.y, M::fma_(s, p1.x, A2));
+          const T X = M::fma_(zoff, p1.y, M::fma_(s, p0.x, A0));
+          const T Y = M::fma_(zoff, p2.x, M::fma_(s, p0.y, A1));
+          const T Z = M::fma_(zoff, p2.y, M::fma_(s, p1.x, A2));
+          if constexpr (ST2) {
+            // two stores per point instead of three: the point's 3 values start on a 2-value boundary when its index
+            // is even ((x,y) as one vector, then z) and one value past it when odd (x, then (y,z) as one vector)
+            *reinterpret_cast<CatPair<T>*>(om + (odd ? 1 : 0)) = CatPair<T>{odd ? Y : X, odd ? Z : Y};
+            om[odd ? 0 : 2] = odd ? X : Z;
+          } else {
+            om[0] = X;
+            om[1] = Y;
+            om[2] = Z;
+          }
         }
       }
     }

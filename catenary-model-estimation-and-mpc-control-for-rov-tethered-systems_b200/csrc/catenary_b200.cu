@@ -84,6 +84,8 @@ int solve_param_host(CatCtx* c, int64_t n, const T* l, const T* dH, const T* L, 
   return CAT_OK;
 }
 
+inline int popcount4(int w) { return (w & 1) + ((w >> 1) & 1) + ((w >> 2) & 1) + ((w >> 3) & 1); }
+
 // ---------------------------------------------------------------------------------------------
 template <typename T>
 int shape_dev_on(CatCtx* c, cudaStream_t st, int64_t n, const T* A, const T* B, const T* L, int64_t L_stride,
@@ -98,17 +100,31 @@ int shape_dev_on(CatCtx* c, cudaStream_t st, int64_t n, const T* A, const T* B, 
   // 2.21 ms: the unrolled per-map code spills at the 96-register cap) and in fp32 (0.267 -> 0.278 ms, two
   // configurations per warp), so those take the run-time form.
   const int w = sizeof(T) == 8 ? which : 0;
+  // Two stores per point (a 2-value vector + a scalar) instead of three scalars, in the run-time form, when at least
+  // two of the rotated curves are asked for (they share a span, so their stores interleave): one B200, 1,048,576 x 100
+  // points, all four curves 1.87 -> 1.57 ms in fp64 (0.99 of the HBM peak) and 1.34 -> 0.98 ms in fp32; masks 12 and 14
+  // likewise.  With ONE curve per span it loses (final curve fp32 0.268 -> 0.309 ms, original + final fp64 0.885 ->
+  // 0.991 ms), so those keep the scalar stores (profiles/r2_ab_shape_two_stores.txt).  Needs every curve on a
+  // 2-value boundary: even n_pts, aligned `out`.  CAT_SHAPE_ST2=0/1 forces it off/on (A/B).
+  static const int st2_env = [] { const char* e = std::getenv("CAT_SHAPE_ST2"); return e ? std::atoi(e) : -1; }();
+  const bool st2_ok = (n_pts % 2 == 0) && (reinterpret_cast<uintptr_t>(out) % (2 * sizeof(T)) == 0);
+  const bool st2 = st2_ok && (st2_env >= 0 ? st2_env != 0 : popcount4(which & 14) >= 2);
   switch (w) {
     case CAT_OUT_ORIGINAL: CAT_SHAPE_LAUNCH(1); break;     // Catenary.__call__ alone (catenary.py:25)
     case CAT_OUT_FINAL: CAT_SHAPE_LAUNCH(8); break;        // fully augmented curve (main_fun.py:111, [3])
-    default: CAT_SHAPE_LAUNCH(0); break;
+    default:
+      if (st2)
+        k_shape<T, 0, true><<<nblk(n, CAT_SHAPE_TILE), CAT_SHAPE_TILE, smem, st>>>(
+            n, A, B, L, L_stride, theta, gamma, n_pts, which, T(kCLo), T(kCHi), out, C_out, valid);
+      else
+        CAT_SHAPE_LAUNCH(0);
+      break;
   }
 #undef CAT_SHAPE_LAUNCH
   LAUNCHED();
   return CAT_OK;
 }
 
-inline int popcount4(int w) { return (w & 1) + ((w >> 1) & 1) + ((w >> 2) & 1) + ((w >> 3) & 1); }
 
 template <typename T>
 int shape_host(CatCtx* c, int64_t n, const T* A, const T* B, const T* L, int64_t L_stride, const T* theta,

@@ -676,3 +676,23 @@ def test_back_to_back_steps_overlap_safely(cb):
         assert torch.equal(wins[j + 10], wins[j])
         assert int(wins[j].cpu()[1]) == want[j % 3][0]
     st.close()
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_shapes_every_mask_and_odd_point_counts(cb, dtype):
+    """Every output mask (the masks with two or more rotated curves take the two-stores-per-point form of k_shape when
+    the point count is even, the others and odd point counts the scalar form): each curve equals, bit for bit, the same
+    curve asked for alone."""
+    n = 1000 + 37
+    A, B, L, th, ga = (x.astype(dtype) for x in _config2_batch(n, 3, True))
+    for n_pts in (100, 7, 2):
+        alone = {}
+        for bit in (1, 2, 4, 8):
+            (alone[bit],), C1, v1 = cb.catenary_shapes(A, B, L, th, ga, which=bit, n_pts=n_pts, dtype=dtype)
+        for mask in range(1, 16):
+            curves, C, valid = cb.catenary_shapes(A, B, L, th, ga, which=mask, n_pts=n_pts, dtype=dtype)
+            bits = [b for b in (1, 2, 4, 8) if mask & b]
+            assert len(curves) == len(bits)
+            for cv, b in zip(curves, bits):
+                assert cv.shape == (n, n_pts, 3)
+                assert np.array_equal(cv, alone[b], equal_nan=True), (n_pts, mask, b)
