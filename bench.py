@@ -814,8 +814,12 @@ def single_gpu_legs(torch, cb, devmod, ctx, step, p, pref, sigma, host_sets, hos
                                             tth.data_ptr(), tga.data_ptr(), 100, which, o2.data_ptr(), C2.data_ptr(),
                                             v2.data_ptr()))
     s_ms = _median_launch_ms(torch, shape_launch, 10)
-    ctx.set_stream(None)
     valid_frac = float((v2 == 3).float().mean())
+    # all four transform_catenary outputs (what the reference's call returns): 4 x 2,400 B written per configuration
+    del o2
+    o2 = torch.empty((4, n2, 100, 3), dtype=torch.float64, device=dev)
+    s4_ms = _median_launch_ms(torch, lambda: shape_launch(15), 10)
+    ctx.set_stream(None)
     del o2, tA, tB, tth, tga
     out_h = None
     t0 = time.perf_counter()
@@ -837,6 +841,10 @@ def single_gpu_legs(torch, cb, devmod, ctx, step, p, pref, sigma, host_sets, hos
         "inputs": "SURVEY 8(d) config 2: 1% taut, 1% near-vertical, theta, gamma ~ U[-30, 30] deg, L = 3",
         "roofline": {"bound": "hbm", "achieved": ach2, "peak": hbm_peak, "unit": "GB/s", "frac": ach2 / hbm_peak,
                      "traffic": tr2, "bytes_per_config": BYTES_PER_SHAPE_CONFIG, "peak_source": hbm_src},
+        "all_four_curves": {"kernel": "k_shape<double, run-time mask, two stores per point>", "kernel_ms": s4_ms,
+                            "configs_per_s": n2 / (s4_ms * 1e-3), "bytes_per_config": BYTES_PER_SHAPE_CONFIG + 7200.0,
+                            "achieved_gbs": n2 * (BYTES_PER_SHAPE_CONFIG + 7200.0) / (s4_ms * 1e-3) / 1e9,
+                            "hbm_frac": n2 * (BYTES_PER_SHAPE_CONFIG + 7200.0) / (s4_ms * 1e-3) / 1e9 / hbm_peak},
         "e2e": {"ms": e2e2 * 1e3, "first_call_ms": first * 1e3, "configs_per_s": n2 / e2e2,
                 "h2d_bytes": int(A2.nbytes + B2.nbytes + th2.nbytes + ga2.nbytes + 8),
                 "d2h_bytes": int(fin.nbytes + Ch.nbytes + vh.nbytes),
