@@ -591,11 +591,10 @@ int mpc_step_host(CatCtx* c, const CatMpcParams* p, const CatMpcProblem* problem
     plan.err = (unsigned int*)(c->d_stage + 4008);
     std::memcpy(c->h_stage + 3840, &plan, sizeof(plan));
     CatArrivePlan* d_plan = reinterpret_cast<CatArrivePlan*>(d_arrive + 64);
-    CU(cudaMemcpyAsync(d_plan, c->h_stage + 3840, sizeof(plan), cudaMemcpyHostToDevice, c->stream));
+    cudaError_t e = cudaMemcpyAsync(d_plan, c->h_stage + 3840, sizeof(plan), cudaMemcpyHostToDevice, c->stream);
     q.arrive = d_plan;
     const size_t row = (size_t)p->K * esz * 3;             // bytes of one horizon step of [H][3][K]
     const unsigned char* h_ctl = (const unsigned char*)controls;
-    cudaError_t e = cudaSuccess;
     for (int g = 0, h0 = 0; g < ng && e == cudaSuccess; ++g) {
       const int h1 = h0 + sizes[g];
       e = cudaMemcpyAsync(d_ctl + (size_t)h0 * row, h_ctl + (size_t)h0 * row, (size_t)(h1 - h0) * row,
