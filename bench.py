@@ -577,8 +577,10 @@ def run_ours(args):
                              "what": "FP64 thread-instructions per second of ONE GPU over the back-to-back loop that "
                                      "`value` times, against the same measured DFMA rate; issue_slot_frac = issue-port "
                                      "cycles (one per instruction, two per FP64 instruction) over the cycles of the "
-                                     "592 schedulers: at ~1.0 the loop is bound by its instruction count, and more "
-                                     "resident warps do not help (profiles/r2_ab_minb5.txt)"}
+                                     "592 schedulers -- a MODEL of the issue port, not a counter (a value a little "
+                                     "above 1 says the two-cycle charge is slightly high); at ~1.0 the loop is bound by "
+                                     "its instruction count, and more resident warps do not help "
+                                     "(profiles/r2_ab_minb5.txt)"}
         return o
     if world == 1:
         out.update(add_steady(single_gpu_legs(torch, cb, devmod, ctx, step, p, pref, sigma, host_sets, host32, dev_sets, clocks,
